@@ -1,0 +1,382 @@
+#!/usr/bin/env python
+"""bench.py -- GCUPS of the database-search hot path on N B200s (BASELINE.json metric).
+
+Workload (config 2 of BASELINE.json): Swiss-Prot-shaped synthetic database
+(570k proteins, ~2.04e8 residues, 32 planted giants up to 35213 aa), BLOSUM62,
+gap open 11 / extend 1, Smith-Waterman score mode, queries of 100, 300, 1000,
+2000 and 5000 aa.  One STEP = the five queries searched one after the other
+against the whole database.  N > 1: the database is sharded by cumulative
+cell count over the ranks (one process per GPU), each rank scores its shard
+and the per-shard score arrays are gathered with NCCL -- the total work is
+fixed, so scaling is "strong".
+
+GCUPS = 1e-9 * sum_q Lq * total residues * steps / seconds  (algorithmic cells).
+"""
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+QUERY_LENGTHS = (100, 300, 1000, 2000, 5000)
+GAP_OPEN, GAP_EXTEND, MATRIX = 11, 1, "BLOSUM62"
+METRIC = "GCUPS (whole box, device-timed) at 1/2/4/8 B200 vs PyOpal CPU"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--targets", type=int, default=570_000, help="database size (config 2: 570000)")
+    ap.add_argument("--algorithm", default="sw", choices=["sw", "nw", "hw", "ov"])
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the CPU baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def workload(args):
+    import numpy as np
+    import synthetic
+
+    db = synthetic.config2(args.targets, giants=32 if args.targets >= 10_000 else 0)
+    queries = synthetic.config2_queries(db, QUERY_LENGTHS)
+    return db, [np.ascontiguousarray(q) for q in queries]
+
+
+def config_dict(args, db, extra=None):
+    residues, offsets, lengths = db
+    cfg = {
+        "workload": f"config2: Swiss-Prot-shaped synthetic db, {len(lengths)} proteins, {int(lengths.sum())} residues, "
+                    f"{args.algorithm.upper()} score mode, {MATRIX} open {GAP_OPEN} ext {GAP_EXTEND}, "
+                    f"queries {list(QUERY_LENGTHS)} aa per step",
+        "targets": int(len(lengths)),
+        "residues": int(lengths.sum()),
+        "query_lengths": list(QUERY_LENGTHS),
+        "cells_per_step": int(sum(QUERY_LENGTHS)) * int(lengths.sum()),
+        "l2": "inputs (>= 400 MB pair-interleaved residue stream per step at N=1) exceed the 126 MB L2",
+    }
+    if extra:
+        cfg.update(extra)
+    return cfg
+
+
+# --------------------------------------------------------------------------
+# CPU arm: the oracle port (the reference's own Opal sources are absent from
+# /root/reference, so it cannot be compiled: kind = "port").
+
+
+def cpu_sample(db, queries, algorithm, budget_s, threads):
+    """Time the scalar oracle on a bounded sample: query 300 aa against the first targets of the db."""
+    import array
+    import oracle
+    import pyopal_b200 as pyopal
+
+    oracle.build()
+    residues, offsets, lengths = db
+    q = queries[1].tobytes()
+    M = pyopal.Aligner(MATRIX)._int_matrix
+    # probe the rate on a small slice, then size the sample for the budget
+    def run(n):
+        n = min(n, len(lengths))
+        off = array.array("q", offsets[:n].tolist())
+        ln = array.array("i", lengths[:n].tolist())
+        buf = residues[: int(offsets[n - 1] + lengths[n - 1])].tobytes() + b"\0"
+        t0 = time.perf_counter()
+        oracle.search_flat(q, buf, off, ln, M, 24, GAP_OPEN, GAP_EXTEND, algorithm, "score", threads)
+        dt = time.perf_counter() - t0
+        return len(q) * int(lengths[:n].sum()), dt, n
+
+    cells, dt, n = run(2000)
+    rate = cells / max(dt, 1e-6)
+    n_budget = int(min(len(lengths), max(2000, rate * budget_s / (len(q) * float(lengths.mean())))))
+    cells, dt, n = run(n_budget)
+    return cells / dt / 1e9, f"oracle port, query 300 aa x first {n} targets ({cells:.3g} cells in {dt:.1f} s)"
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    db, queries = workload(args)
+    threads = os.cpu_count() or 1
+    per_step = max(2.0, min(args.cpu_seconds, 150.0 / max(1, args.steps + args.warmup)))
+    vals = []
+    sample = ""
+    t_total = 0.0
+    for i in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        v, sample = cpu_sample(db, queries, args.algorithm, per_step, threads)
+        if i >= args.warmup:
+            vals.append(v)
+            t_total += time.perf_counter() - t0
+    value = sum(vals) / len(vals)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "GCUPS", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_total / max(1, args.steps),
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int64 (scalar)",
+        "data": "synthetic", "config": config_dict(args, db),
+        "cpu_baseline": {"value": value, "unit": "GCUPS", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "GCUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "CPU restatement (scalar C oracle, pthreads over contiguous chunks as _align.py:151-170), "
+                "not Opal SIMD: the Opal sources are absent from /root/reference (vendor/opal submodule empty)",
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------
+
+
+class ClockSampler(threading.Thread):
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index
+        self.samples = []
+        self.reasons = set()
+        self.stop_flag = threading.Event()
+        self.proc = None
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i", str(self.index), "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            return
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for line in self.proc.stdout:
+            if self.stop_flag.is_set():
+                break
+            parts = [p.strip() for p in line.split(",")]
+            try:
+                self.samples.append((float(parts[0]), float(parts[1])))
+            except (ValueError, IndexError):
+                continue
+            for nm, val in zip(names, parts[2:]):
+                if val.lower().startswith("active"):
+                    self.reasons.add(nm)
+
+    def finish(self):
+        self.stop_flag.set()
+        if self.proc:
+            self.proc.terminate()
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        sm = sorted(s[0] for s in self.samples)
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": self.samples[0][1], "reasons": sorted(self.reasons),
+                "samples": len(sm)}
+
+
+def shard_indices(lengths, world, rank):
+    """Cell-balanced sharding: length-sorted targets dealt round-robin, alternating direction
+    (snake) so every rank gets the same length mix and the giants spread out."""
+    import numpy as np
+
+    order = np.argsort(-lengths.astype(np.int64), kind="stable")
+    pos = np.arange(len(order))
+    rnd, k = pos // world, pos % world
+    owner = np.where(rnd % 2 == 0, k, world - 1 - k)
+    return np.sort(order[owner == rank])
+
+
+def run_b200(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import pyopal_b200 as pyopal
+    from pyopal_b200.platform import cuda
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    db, queries = workload(args)
+    residues, offsets, lengths = db
+    total_res = int(lengths.sum())
+    n_all = len(lengths)
+    mine = shard_indices(lengths, world, rank) if world > 1 else np.arange(n_all)
+    # pack this rank's shard
+    if world == 1:
+        sr, so, sl = residues, offsets, lengths
+    else:
+        sl = lengths[mine]
+        so = np.zeros(len(mine), dtype=np.int64)
+        np.cumsum(sl[:-1], out=so[1:])
+        # gather the shard's residues: source position of every destination byte
+        src = np.repeat(offsets[mine] - so, sl) + np.arange(int(sl.sum()), dtype=np.int64)
+        sr = residues[src]
+    store = cuda.DeviceStore(sr, so, np.ascontiguousarray(sl), 24, device=local)
+    aligner = pyopal.Aligner(MATRIX, GAP_OPEN, GAP_EXTEND)
+    M = aligner._int_matrix
+    algo = {"nw": 0, "hw": 1, "ov": 2, "sw": 3}[args.algorithm]
+    qbytes = [q.tobytes() for q in queries]
+
+    n_mine = len(mine)
+    n_pad = (n_all + world - 1) // world + 1
+    stream = torch.cuda.current_stream()
+    d_scores = [torch.zeros(n_pad, dtype=torch.int32, device="cuda") for _ in qbytes]
+    gathered = [torch.empty(world * n_pad, dtype=torch.int32, device="cuda") for _ in qbytes] if world > 1 else None
+    # global index of every gathered slot -> un-permute on rank 0
+    if world > 1:
+        idx = torch.full((n_pad,), -1, dtype=torch.int64, device="cuda")
+        idx[:n_mine] = torch.from_numpy(mine).cuda()
+        all_idx = torch.empty(world * n_pad, dtype=torch.int64, device="cuda")
+        dist.all_gather_into_tensor(all_idx, idx)
+        valid = (all_idx >= 0).nonzero().squeeze(1)
+        dest = all_idx[valid]
+        final = [torch.zeros(n_all, dtype=torch.int32, device="cuda") for _ in qbytes]
+
+    launches = [0]
+    k16_us = [0.0]
+    k16_n = [0]
+
+    def step(collect=False):
+        for qi, q in enumerate(qbytes):
+            store.search_scores_device(q, GAP_OPEN, GAP_EXTEND, M, algo, d_scores[qi].data_ptr(), stream.cuda_stream)
+            if collect:
+                stream.synchronize()
+                st = store.stats()
+                launches[0] += st["launches"]
+                k16_us[0] += st["k16_us"]
+                k16_n[0] += 1
+                step.last = st
+            if world > 1:
+                dist.all_gather_into_tensor(gathered[qi], d_scores[qi])
+                if rank == 0:
+                    final[qi][dest] = gathered[qi][valid]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    time.sleep(0.3)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.finish()
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    cells_step = sum(QUERY_LENGTHS) * total_res
+    value = cells_step * args.steps / (ms * 1e-3) / 1e9
+
+    # per-kernel pass (outside the timed region): CUDA events around the 16-bit kernel of each search
+    step(collect=True)
+    barrier()
+    per_q = []
+    for qi, q in enumerate(qbytes):
+        store.search_scores_device(q, GAP_OPEN, GAP_EXTEND, M, algo, d_scores[qi].data_ptr(), stream.cuda_stream)
+        stream.synchronize()
+        st = store.stats()
+        per_q.append({"Lq": len(q), "G": st["G"], "K": st["K"], "passes": st["passes"], "k16_us": st["k16_us"],
+                      "k32_us": st["k32_us"], "rescore_us": st["rescore_us"], "escalated": None,
+                      "gcups_k16": round(len(q) * int(sl.sum()) / max(st["k16_us"], 1) / 1e3, 1)})
+
+    # end-to-end: the public C-ABI call with HOST buffers (query H2D + scores D2H inside the timed region)
+    e2e_value = None
+    h2d = d2h = 0
+    if rank == 0 or world > 1:
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            for q in qbytes:
+                store.search(q, GAP_OPEN, GAP_EXTEND, M, 0, algo)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        tt = torch.tensor([dt], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e_value = cells_step * args.steps / float(tt.item()) / 1e9
+        h2d = sum(len(q) for q in qbytes) + len(qbytes) * (24 * 24 * 4 + 64)
+        d2h = len(qbytes) * n_mine * 4
+
+    if rank == 0:
+        # integer-issue roofline: measured 6.5-instruction cell mix
+        rate = None
+        try:
+            import ctypes
+            r, c = ctypes.c_double(0), ctypes.c_double(0)
+            if cuda.load_library().pyopal_cuda_int_issue_rate(local, ctypes.byref(r), ctypes.byref(c)) == 0:
+                rate = r.value
+        except Exception:
+            rate = None
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        # dominant kernel = the 16-bit search kernel; weight by time over the five queries
+        tot_us = sum(p["k16_us"] for p in per_q) or 1
+        cells_k = sum(p["Lq"] for p in per_q) * int(sl.sum())
+        gcups_k = cells_k / tot_us / 1e3
+        bytes_k = sum(p["passes"] * int(store.device_bytes()) for p in per_q)
+        roof_gcups = rate * 2 / 6.5 / 1e9 if rate else None
+        line = {
+            "metric": METRIC, "value": value, "unit": "GCUPS", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "s16x2 (s32 rescore)", "data": "synthetic",
+            "config": config_dict(args, db, {"parallelism": f"db sharded by cells over {world} GPU(s), NCCL all-gather of scores"}),
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": "GCUPS", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "api": "pyopal_cuda_search (host query in, host scores out), wall clock"},
+            "roofline": {"bound": "hbm", "achieved": bytes_k / tot_us / 1e3, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": bytes_k / tot_us / 1e3 / hbm_peak, "traffic": None,
+                         "note": "residue stream of the 16-bit kernel; HBM is NOT the binding roof of this path, "
+                                 "see roofline_alu (SURVEY.md 8(d))",
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback"},
+            "roofline_alu": {"bound": "int_alu_issue", "achieved": gcups_k, "peak": roof_gcups, "unit": "GCUPS",
+                             "frac": (gcups_k / roof_gcups) if roof_gcups else None,
+                             "thread_instr_per_s": rate,
+                             "note": "peak = measured issue rate of the 6.5-instruction s16x2 cell mix x 2 cells / 6.5"},
+            "kernels": per_q,
+        }
+        # launches inside the timed region: counted from the library's own counter
+        line["gpu_launches"] = int(launches[0]) * args.steps
+        if not args.no_cpu_baseline and world == 1:
+            v, sample = cpu_sample(db, queries, args.algorithm, args.cpu_seconds, os.cpu_count() or 1)
+            line["cpu_baseline"] = {"value": v, "unit": "GCUPS", "cores": os.cpu_count() or 1, "kind": "port",
+                                    "sample": sample}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,155 @@
+/*
+ * include/pyopal_cuda.h -- C-ABI of the B200 (sm_100a) database-search backend.
+ *
+ * This is the drop-in boundary for PyOpal's hot path.  Everything here is
+ * extern "C", plain pointers and sizes; no C++/torch types, no exceptions, and
+ * every entry point may be called without the GIL from several host threads.
+ *
+ * Reference interfaces replaced (paths relative to /root/reference/):
+ *   - opalSearchDatabase + OpalSearchResult + OPAL_* constants
+ *         src/pyopal/opal.pxd:3-54         (the C declarations Cython binds)
+ *         src/pyopal/lib.pxd:40-54         (searchfn_t: the plugin fn pointer)
+ *         src/pyopal/platform/pyx.in:77-91 (the single call site)
+ *   - opalInitSearchResult / opalSearchResultIsEmpty / opalSearchResultSetScore
+ *         src/pyopal/opal.pxd:36-38        (declared, never called by pyopal)
+ *   - the per-sequence heap store the call reads through
+ *         src/pyopal/lib.pxd:95-98, src/pyopal/lib.pyx:501-508
+ *     becomes the device-resident, length-sorted, pair-interleaved store
+ *     behind pyopal_cuda_db_* below.
+ *
+ * Numeric values of the OPAL_* constants: upstream opal.h is not in the
+ * reference tree (vendor/opal is an empty submodule); only the alignment ops
+ * are pinned (M=0 D=1 I=2 X=3, lib.pyx:991-996).  The rest follow upstream
+ * Opal as recalled in SURVEY.md App. A.2 and only need to be self-consistent,
+ * because PyOpal never exposes them.
+ */
+#ifndef PYOPAL_CUDA_H
+#define PYOPAL_CUDA_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- opal.pxd:5-24 ------------------------------------------------------ */
+#define OPAL_ERR_OVERFLOW 1
+#define OPAL_ERR_NO_SIMD_SUPPORT 2 /* here: "no usable CUDA device" -> RuntimeError, pyx.in:102-103 */
+#define OPAL_ERR_INVALID_MODE 3
+/* additions of this backend; pyx.in:106-107 maps any other non-zero code to RuntimeError */
+#define PYOPAL_CUDA_ERR_CUDA 16     /* a CUDA runtime call failed; see pyopal_cuda_last_error() */
+#define PYOPAL_CUDA_ERR_NOMEM 17    /* host or device allocation failed -> MemoryError */
+#define PYOPAL_CUDA_ERR_ARGUMENT 18 /* NULL / out-of-range argument */
+#define PYOPAL_CUDA_ERR_INTERNAL 19 /* self-check failed (e.g. traceback score mismatch) */
+
+#define OPAL_MODE_NW 0
+#define OPAL_MODE_HW 1
+#define OPAL_MODE_OV 2
+#define OPAL_MODE_SW 3
+
+#define OPAL_OVERFLOW_SIMPLE 0
+#define OPAL_OVERFLOW_BUCKETS 1
+
+#define OPAL_SEARCH_SCORE 0
+#define OPAL_SEARCH_SCORE_END 1
+#define OPAL_SEARCH_ALIGNMENT 2
+
+#define OPAL_ALIGN_MATCH 0
+#define OPAL_ALIGN_DEL 1
+#define OPAL_ALIGN_INS 2
+#define OPAL_ALIGN_MISMATCH 3
+
+/* ---- opal.pxd:26-34, field for field ------------------------------------ */
+typedef struct {
+    int scoreSet;
+    int score;
+    int endLocationTarget;
+    int endLocationQuery;
+    int startLocationTarget;
+    int startLocationQuery;
+    unsigned char* alignment; /* malloc()ed by the callee in ALIGNMENT mode, as upstream Opal does */
+    int alignmentLength;
+} OpalSearchResult;
+
+/* opal.pxd:36-38 */
+void opalInitSearchResult(OpalSearchResult* result);
+int opalSearchResultIsEmpty(const OpalSearchResult result);
+void opalSearchResultSetScore(OpalSearchResult* result, int score);
+
+/* opal.pxd:40-54 / lib.pxd:40-54.  Generic path: host pointers in, results
+ * out; the database is staged to the current device for the duration of the
+ * call, so it works for any BaseDatabase subclass (lib.pyx:337-346). */
+int opalSearchDatabase(unsigned char query[], int queryLength, unsigned char* db[], int dbLength,
+                       int dbSeqLengths[], int gapOpen, int gapExt, int* scoreMatrix, int alphabetLength,
+                       OpalSearchResult* results[], const int searchType, int mode, int overflowMethod);
+
+/* ---- device-resident store (replaces lib.pxd:95-98 for the search) ------ */
+typedef struct pyopal_cuda_db pyopal_cuda_db;
+
+int pyopal_cuda_device_count(void);
+/* name (<= cap bytes), SM count, total memory of `device`. */
+int pyopal_cuda_device_info(int device, char* name, int cap, int* sm_count, int64_t* total_mem);
+/* thread-local message of the last failing call on this thread */
+const char* pyopal_cuda_last_error(void);
+
+/* Build the store on `device` from a packed host residue buffer:
+ * sequence k is residues[offsets[k] .. offsets[k]+lengths[k]).  Residues are
+ * alphabet indices < alphabetLength <= 32 (lib.pxd:28-32). */
+int pyopal_cuda_db_create(int device, const unsigned char* residues, const int64_t* offsets,
+                          const int32_t* lengths, int64_t n, int alphabetLength, pyopal_cuda_db** out);
+/* Same, from the reference's own layout: an array of per-sequence pointers
+ * (BaseDatabase.get_sequences / get_lengths, lib.pxd:90-92). */
+int pyopal_cuda_db_create_from_pointers(int device, const unsigned char* const* sequences,
+                                        const int32_t* lengths, int64_t n, int alphabetLength,
+                                        pyopal_cuda_db** out);
+void pyopal_cuda_db_destroy(pyopal_cuda_db* db);
+int64_t pyopal_cuda_db_size(const pyopal_cuda_db* db);
+int64_t pyopal_cuda_db_total_length(const pyopal_cuda_db* db);
+int64_t pyopal_cuda_db_device_bytes(const pyopal_cuda_db* db);
+
+/* One query against targets [start, end) of the store (lib.pyx:1364-1383).
+ * Output arrays are HOST buffers of (end - start) entries, in database order.
+ * endQ/endT may be NULL in SCORE mode; startQ/startT/ops* may be NULL unless
+ * ALIGNMENT.  In ALIGNMENT mode `ops` receives target k's operations at
+ * ops[ops_offsets[k] ..) (caller sizes slot k as queryLength + length_k, the
+ * upper bound) and ops_len[k] their count. */
+int pyopal_cuda_search(pyopal_cuda_db* db, const unsigned char* query, int queryLength, int gapOpen,
+                       int gapExt, const int* scoreMatrix, int alphabetLength, int searchType, int mode,
+                       int overflowMethod, int64_t start, int64_t end, int32_t* scores, int32_t* endQ,
+                       int32_t* endT, int32_t* startQ, int32_t* startT, unsigned char* ops,
+                       const int64_t* ops_offsets, int32_t* ops_len);
+
+/* SCORE-mode search whose result stays on the device: `d_scores` is a DEVICE
+ * pointer to (end - start) int32.  `stream` is a cudaStream_t (0 = the legacy
+ * default stream); the call returns once the work is enqueued on it.  Used by
+ * the multi-GPU driver to feed the NCCL gather without a host round trip. */
+int pyopal_cuda_search_scores_device(pyopal_cuda_db* db, const unsigned char* query, int queryLength,
+                                     int gapOpen, int gapExt, const int* scoreMatrix, int alphabetLength,
+                                     int mode, int64_t start, int64_t end, int32_t* d_scores, void* stream);
+
+/* Batched SCORE-mode search: nq queries (queries[offsets[i] .. +lengths[i]))
+ * against the whole store; scores is a HOST buffer of nq * size int32,
+ * row-major by query. */
+int pyopal_cuda_search_batch(pyopal_cuda_db* db, const unsigned char* queries, const int64_t* q_offsets,
+                             const int32_t* q_lengths, int nq, int gapOpen, int gapExt,
+                             const int* scoreMatrix, int alphabetLength, int mode, int32_t* scores);
+
+/* Statistics of the last search on this handle (for bench.py / profiles):
+ * stats[0]=kernel launches, [1]=targets scored at 16 bit, [2]=targets scored
+ * at 32 bit (static), [3]=targets escalated 16->32 after overflow,
+ * [4]=device time of the last search in microseconds (CUDA events),
+ * [5]=threads per target group G, [6]=query rows per thread K, [7]=passes,
+ * [8]/[9]/[10]=device microseconds of the 32-bit static kernel / the 16-bit
+ * kernel / the 32-bit rescore kernel of the last search (0 until its stream
+ * has completed), [11]=1 if the query profile was held in shared memory. */
+int pyopal_cuda_last_stats(const pyopal_cuda_db* db, int64_t* stats, int n);
+
+/* Integer-ALU issue microbenchmark used for the cell-update roofline
+ * (SURVEY.md 8(d)): runs the six-instruction 16-bit cell mix dependency-free
+ * on `device` and returns thread-instructions per second. */
+int pyopal_cuda_int_issue_rate(int device, double* thread_instr_per_s, double* sm_clock_mhz);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

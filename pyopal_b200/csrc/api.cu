@@ -1,0 +1,819 @@
+// pyopal_b200/csrc/api.cu -- C-ABI of the sm_100a backend (include/pyopal_cuda.h).
+//
+// Host side of the path that /root/reference/src/pyopal/platform/pyx.in:57-91
+// drives: take the query + the database, run the DP on the device, hand back
+// per-target results.  No PyTorch, no CPU fallback: without a CUDA device every
+// entry point fails with OPAL_ERR_NO_SIMD_SUPPORT (pyx.in:102-103 maps it to
+// RuntimeError, the same class the reference raises when no SIMD backend fits).
+#include "../../include/pyopal_cuda.h"
+#include "kernels.cuh"
+
+#include <algorithm>
+#include <climits>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <numeric>
+#include <string>
+#include <vector>
+
+using namespace pyopal;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string& msg) {
+    g_err = msg;
+    return code;
+}
+
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) {                                                                   \
+            int code_ = (e_ == cudaErrorMemoryAllocation) ? PYOPAL_CUDA_ERR_NOMEM                  \
+                        : (e_ == cudaErrorNoDevice || e_ == cudaErrorInsufficientDriver)           \
+                            ? OPAL_ERR_NO_SIMD_SUPPORT                                             \
+                            : PYOPAL_CUDA_ERR_CUDA;                                                \
+            return fail(code_, std::string(#call) + ": " + cudaGetErrorString(e_));                \
+        }                                                                                          \
+    } while (0)
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t n) {
+        if (n <= cap) return 0;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = n + n / 4 + 64;
+        CU(cudaMalloc(&p, want * sizeof(T)));
+        cap = want;
+        return 0;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+constexpr int PAD_ALIGN_COLS = 8;  // pair streams start on 16-byte boundaries
+
+}  // namespace
+
+struct pyopal_cuda_db {
+    int device = 0;
+    int sm_count = 148;
+    int A = 0;
+    int64_t n = 0;          // sequences
+    int64_t total_len = 0;  // residues
+    int64_t npairs = 0;     // pairs of non-empty targets, sorted by len_a descending
+    int64_t ncols = 0;      // u16 entries in the stream
+    double mean_cols = 0;   // mean len_a
+    // host mirrors of the pair tables (worklists, rung eligibility, fix-ups)
+    std::vector<int64_t> h_pair_off;
+    std::vector<int32_t> h_pair_len, h_pair_idx;
+    std::vector<int32_t> h_lengths;   // database order
+    std::vector<int32_t> h_zero_idx;  // zero-length targets (closed form on the host)
+    // device store
+    uint16_t* d_stream = nullptr;
+    int64_t* d_pair_off = nullptr;
+    int32_t* d_pair_len = nullptr;
+    int32_t* d_pair_idx = nullptr;
+    int32_t* d_identity = nullptr;  // 0..npairs-1
+    // per-search workspace, serialised by `mu`
+    std::mutex mu;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    DevBuf<int32_t> wl16, wl32, ovf, out, fixes;
+    DevBuf<uint8_t> query;
+    DevBuf<int8_t> gprofile;
+    DevBuf<int32_t> wprofile;
+    DevBuf<uint32_t> bndH, bndF;
+    int32_t* d_matrix = nullptr;  // 32*32
+    int32_t* d_counts = nullptr;  // [0..2] list sizes, [4..6] task counters
+    int64_t stats[12] = {0};
+    cudaEvent_t kev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // around k32 / k16 / rescore
+    bool kev_valid[3] = {false, false, false};
+};
+
+// ---------------------------------------------------------------------------
+extern "C" {
+
+void opalInitSearchResult(OpalSearchResult* r) {
+    if (!r) return;
+    r->scoreSet = 0;
+    r->score = 0;
+    r->endLocationTarget = r->endLocationQuery = -1;
+    r->startLocationTarget = r->startLocationQuery = -1;
+    r->alignment = nullptr;
+    r->alignmentLength = 0;
+}
+
+int opalSearchResultIsEmpty(const OpalSearchResult r) { return !r.scoreSet; }
+
+void opalSearchResultSetScore(OpalSearchResult* r, int score) {
+    r->scoreSet = 1;
+    r->score = score;
+}
+
+const char* pyopal_cuda_last_error(void) { return g_err.c_str(); }
+
+int pyopal_cuda_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+int pyopal_cuda_device_info(int device, char* name, int cap, int* sm_count, int64_t* total_mem) {
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    if (name && cap > 0) {
+        strncpy(name, prop.name, (size_t)cap - 1);
+        name[cap - 1] = 0;
+    }
+    if (sm_count) *sm_count = prop.multiProcessorCount;
+    if (total_mem) *total_mem = (int64_t)prop.totalGlobalMem;
+    return 0;
+}
+
+void pyopal_cuda_db_destroy(pyopal_cuda_db* db) {
+    if (!db) return;
+    cudaSetDevice(db->device);
+    cudaFree(db->d_stream);
+    cudaFree(db->d_pair_off);
+    cudaFree(db->d_pair_len);
+    cudaFree(db->d_pair_idx);
+    cudaFree(db->d_identity);
+    cudaFree(db->d_matrix);
+    cudaFree(db->d_counts);
+    db->wl16.release(); db->wl32.release(); db->ovf.release(); db->out.release(); db->fixes.release();
+    db->query.release(); db->gprofile.release(); db->wprofile.release();
+    db->bndH.release(); db->bndF.release();
+    for (int i = 0; i < 6; i++) if (db->kev[i]) cudaEventDestroy(db->kev[i]);
+    if (db->ev0) cudaEventDestroy(db->ev0);
+    if (db->ev1) cudaEventDestroy(db->ev1);
+    if (db->stream) cudaStreamDestroy(db->stream);
+    delete db;
+}
+
+int64_t pyopal_cuda_db_size(const pyopal_cuda_db* db) { return db ? db->n : 0; }
+int64_t pyopal_cuda_db_total_length(const pyopal_cuda_db* db) { return db ? db->total_len : 0; }
+int64_t pyopal_cuda_db_device_bytes(const pyopal_cuda_db* db) {
+    if (!db) return 0;
+    return db->ncols * 2 + db->npairs * (8 + 8 + 8 + 4);
+}
+
+int pyopal_cuda_last_stats(const pyopal_cuda_db* db, int64_t* stats, int n) {
+    if (!db || !stats) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null argument");
+    // resolve the per-kernel events of the last search if they have completed
+    pyopal_cuda_db* m = const_cast<pyopal_cuda_db*>(db);
+    for (int k = 0; k < 3; k++) {
+        m->stats[8 + k] = 0;
+        if (m->kev_valid[k] && cudaEventQuery(m->kev[2 * k + 1]) == cudaSuccess) {
+            float ms = 0;
+            if (cudaEventElapsedTime(&ms, m->kev[2 * k], m->kev[2 * k + 1]) == cudaSuccess)
+                m->stats[8 + k] = (int64_t)(ms * 1000.0f + 0.5f);
+        }
+    }
+    cudaGetLastError();
+    for (int i = 0; i < n && i < 12; i++) stats[i] = db->stats[i];
+    return 0;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------
+// Store construction: sort by length (descending, ties by index), pair
+// neighbours, interleave each pair's residues into one u16 stream.
+template <typename GetSeq>
+static int db_build(int device, GetSeq get_seq, const int32_t* lengths, int64_t n, int A,
+                    pyopal_cuda_db** out) {
+    if (!out) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null output handle");
+    *out = nullptr;
+    if (n < 0 || n > INT32_MAX) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "database size out of range");
+    if (A < 1 || A > 32) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "alphabet length must be in 1..32");
+    if (pyopal_cuda_device_count() <= 0) return fail(OPAL_ERR_NO_SIMD_SUPPORT, "no CUDA device available");
+    CU(cudaSetDevice(device));
+    pyopal_cuda_db* db = new (std::nothrow) pyopal_cuda_db();
+    if (!db) return fail(PYOPAL_CUDA_ERR_NOMEM, "host allocation failed");
+    struct Guard {
+        pyopal_cuda_db* d;
+        ~Guard() { if (d) pyopal_cuda_db_destroy(d); }
+    } guard{db};
+    db->device = device;
+    db->A = A;
+    db->n = n;
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    db->sm_count = prop.multiProcessorCount;
+
+    db->h_lengths.assign(lengths, lengths + n);
+    std::vector<int32_t> order;
+    order.reserve((size_t)n);
+    for (int64_t i = 0; i < n; i++) {
+        if (lengths[i] < 0) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "negative sequence length");
+        db->total_len += lengths[i];
+        if (lengths[i] == 0) db->h_zero_idx.push_back((int32_t)i);
+        else order.push_back((int32_t)i);
+    }
+    std::stable_sort(order.begin(), order.end(),
+                     [&](int32_t a, int32_t b) { return lengths[a] > lengths[b]; });
+    const int64_t m = (int64_t)order.size();
+    const int64_t npairs = (m + 1) / 2;
+    db->npairs = npairs;
+    db->h_pair_off.resize((size_t)npairs);
+    db->h_pair_len.resize((size_t)npairs * 2);
+    db->h_pair_idx.resize((size_t)npairs * 2);
+    int64_t ncols = 0;
+    for (int64_t k = 0; k < npairs; k++) {
+        int32_t a = order[(size_t)(2 * k)];
+        int32_t b = (2 * k + 1 < m) ? order[(size_t)(2 * k + 1)] : -1;
+        db->h_pair_off[(size_t)k] = ncols;
+        db->h_pair_len[(size_t)(2 * k)] = lengths[a];
+        db->h_pair_len[(size_t)(2 * k + 1)] = b >= 0 ? lengths[b] : 0;
+        db->h_pair_idx[(size_t)(2 * k)] = a;
+        db->h_pair_idx[(size_t)(2 * k + 1)] = b;
+        ncols += ((int64_t)lengths[a] + PAD_ALIGN_COLS - 1) / PAD_ALIGN_COLS * PAD_ALIGN_COLS;
+    }
+    db->ncols = ncols;
+    db->mean_cols = npairs ? (double)ncols / (double)npairs : 0.0;
+
+    // interleave on the host into a pinned staging buffer, chunk by chunk
+    if (ncols > 0) {
+        CU(cudaMalloc(&db->d_stream, (size_t)ncols * sizeof(uint16_t)));
+        const size_t CHUNK = (size_t)16 << 20;  // columns per staging chunk
+        uint16_t* stage = nullptr;
+        size_t stage_cols = std::min<size_t>(CHUNK, (size_t)ncols);
+        // a pair never straddles chunks: grow the staging buffer to the longest pair
+        int64_t longest = ((int64_t)db->h_pair_len[0] + PAD_ALIGN_COLS - 1) / PAD_ALIGN_COLS * PAD_ALIGN_COLS;
+        stage_cols = std::max<size_t>(stage_cols, (size_t)longest);
+        CU(cudaMallocHost(&stage, stage_cols * sizeof(uint16_t)));
+        const uint16_t PADPAIR = (uint16_t)(A | (A << 8));
+        int64_t k = 0;
+        int rc = 0;
+        while (k < npairs && rc == 0) {
+            const int64_t base = db->h_pair_off[(size_t)k];
+            int64_t k2 = k;
+            while (k2 < npairs) {
+                int64_t endc = (k2 + 1 < npairs) ? db->h_pair_off[(size_t)(k2 + 1)] : ncols;
+                if ((size_t)(endc - base) > stage_cols) break;
+                k2++;
+            }
+            const int64_t endc = (k2 < npairs) ? db->h_pair_off[(size_t)k2] : ncols;
+            for (int64_t q = k; q < k2; q++) {
+                uint16_t* dst = stage + (db->h_pair_off[(size_t)q] - base);
+                const int la = db->h_pair_len[(size_t)(2 * q)], lb = db->h_pair_len[(size_t)(2 * q + 1)];
+                const unsigned char* sa = get_seq(db->h_pair_idx[(size_t)(2 * q)]);
+                const unsigned char* sb = lb > 0 ? get_seq(db->h_pair_idx[(size_t)(2 * q + 1)]) : nullptr;
+                int c = 0;
+                unsigned bad = 0;  // residues must index the profile: < A
+                for (; c < lb; c++) {
+                    bad |= (unsigned)(sa[c] >= A) | (unsigned)(sb[c] >= A);
+                    dst[c] = (uint16_t)(sa[c] | (sb[c] << 8));
+                }
+                for (; c < la; c++) {
+                    bad |= (unsigned)(sa[c] >= A);
+                    dst[c] = (uint16_t)(sa[c] | (A << 8));
+                }
+                if (bad) rc = fail(PYOPAL_CUDA_ERR_ARGUMENT, "residue code outside the alphabet");
+                const int padded = (la + PAD_ALIGN_COLS - 1) / PAD_ALIGN_COLS * PAD_ALIGN_COLS;
+                for (; c < padded; c++) dst[c] = PADPAIR;
+            }
+            cudaError_t e = cudaMemcpy(db->d_stream + base, stage, (size_t)(endc - base) * sizeof(uint16_t),
+                                       cudaMemcpyHostToDevice);
+            if (e != cudaSuccess) rc = fail(PYOPAL_CUDA_ERR_CUDA, std::string("stream upload: ") + cudaGetErrorString(e));
+            k = k2;
+        }
+        cudaFreeHost(stage);
+        if (rc) return rc;
+    }
+    if (npairs > 0) {
+        CU(cudaMalloc(&db->d_pair_off, (size_t)npairs * sizeof(int64_t)));
+        CU(cudaMalloc(&db->d_pair_len, (size_t)npairs * 2 * sizeof(int32_t)));
+        CU(cudaMalloc(&db->d_pair_idx, (size_t)npairs * 2 * sizeof(int32_t)));
+        CU(cudaMalloc(&db->d_identity, (size_t)npairs * sizeof(int32_t)));
+        CU(cudaMemcpy(db->d_pair_off, db->h_pair_off.data(), (size_t)npairs * sizeof(int64_t), cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(db->d_pair_len, db->h_pair_len.data(), (size_t)npairs * 2 * sizeof(int32_t), cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(db->d_pair_idx, db->h_pair_idx.data(), (size_t)npairs * 2 * sizeof(int32_t), cudaMemcpyHostToDevice));
+        std::vector<int32_t> ident((size_t)npairs);
+        std::iota(ident.begin(), ident.end(), 0);
+        CU(cudaMemcpy(db->d_identity, ident.data(), (size_t)npairs * sizeof(int32_t), cudaMemcpyHostToDevice));
+    }
+    CU(cudaMalloc(&db->d_matrix, 32 * 32 * sizeof(int32_t)));
+    CU(cudaMalloc(&db->d_counts, 16 * sizeof(int32_t)));
+    CU(cudaStreamCreateWithFlags(&db->stream, cudaStreamNonBlocking));
+    CU(cudaEventCreate(&db->ev0));
+    CU(cudaEventCreate(&db->ev1));
+    for (int i = 0; i < 6; i++) CU(cudaEventCreate(&db->kev[i]));
+    guard.d = nullptr;
+    *out = db;
+    return 0;
+}
+
+extern "C" int pyopal_cuda_db_create(int device, const unsigned char* residues, const int64_t* offsets,
+                                     const int32_t* lengths, int64_t n, int alphabetLength,
+                                     pyopal_cuda_db** out) {
+    if (n > 0 && (!residues || !offsets || !lengths)) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null argument");
+    return db_build(device, [&](int32_t i) { return residues + offsets[i]; }, lengths, n, alphabetLength, out);
+}
+
+extern "C" int pyopal_cuda_db_create_from_pointers(int device, const unsigned char* const* sequences,
+                                                   const int32_t* lengths, int64_t n, int alphabetLength,
+                                                   pyopal_cuda_db** out) {
+    if (n > 0 && (!sequences || !lengths)) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null argument");
+    return db_build(device, [&](int32_t i) { return sequences[i]; }, lengths, n, alphabetLength, out);
+}
+
+// ---------------------------------------------------------------------------
+// Search planning
+
+namespace {
+
+struct Plan {
+    int G = 32, logG = 5, K = 32, npass = 1, pitch = 0, padtop = 0;
+    bool psmem = true;
+    size_t smem = 0;
+};
+
+// Pick the tile (G threads x K rows) that minimises issue slots for this query
+// length and the store's mean target length.  Per column step a thread issues
+// about C0 instructions of bookkeeping plus C1 per row; a target of L columns
+// takes L + G - 1 steps per pass.
+Plan make_plan(int Lq, int A, double mean_cols, size_t smem_limit) {
+    const double C0 = 28.0, C1 = 6.5;
+    Plan best;
+    double best_cost = 1e300;
+    for (int logG = 2; logG <= 5; logG++) {
+        const int G = 1 << logG;
+        for (int K = 4; K <= 40; K += 4) {
+            const int T = G * K;
+            const int npass = (Lq + T - 1) / T;
+            const double cost = (double)npass * (mean_cols + G - 1) * (C0 + C1 * K) * (double)G;
+            if (cost < best_cost - 1e-9) {
+                best_cost = cost;
+                best.G = G; best.logG = logG; best.K = K; best.npass = npass;
+            }
+        }
+    }
+    auto finish = [&](Plan& p) {
+        const int T = p.G * p.K;
+        p.pitch = (p.npass * T + 15) / 16 * 16;
+        p.padtop = p.npass * T - Lq;
+        p.smem = (size_t)(A + 1) * (size_t)p.pitch;
+    };
+    finish(best);
+    if (best.smem > smem_limit) {
+        // profile from global memory (L1/L2 resident); only K = 32 is built for it
+        best.G = 32; best.logG = 5; best.K = 32;
+        best.npass = (Lq + 1023) / 1024;
+        finish(best);
+        best.psmem = false;
+        best.smem = 0;
+    }
+    return best;
+}
+
+struct Rung {
+    bool fits8 = false;       // folded scores fit the int8 profile
+    bool ok16 = false;        // the 16-bit rung may be used at all
+    int64_t max_cols16 = 0;   // NW/HW/OV: longest pair (columns) the 16-bit rung is exact for
+    int neg16 = 0, ovf_thresh = 0, pad_score = 0;
+};
+
+Rung make_rung(const int* M, int A, int go, int ge, int mode, int Lp) {
+    Rung r;
+    int smax = INT_MIN, smin = INT_MAX;
+    for (int i = 0; i < A * A; i++) { smax = std::max(smax, M[i]); smin = std::min(smin, M[i]); }
+    // padding rows / letter: 0 keeps a free top border at 0; -max(open, ext)
+    // reproduces NW's penalised border (kernels.cuh, profile_entry)
+    const int pad_raw = (mode == MODE_NW) ? -std::max(go, ge) : 0;
+    r.pad_score = pad_raw + go;
+    const int lo = std::min(smin, pad_raw) + go, hi = std::max(smax, pad_raw) + go;
+    r.fits8 = (lo >= -128 && hi <= 127);
+    r.neg16 = -32768 + ge;
+    r.ovf_thresh = 32767 - 128 - 1;
+    const int64_t slack = 256;
+    r.ok16 = r.fits8 && (3LL * go + 2LL * ge + slack < 16000);
+    if (r.ok16 && mode != MODE_SW) {
+        // lower bound of any live value: -(3*open + (Lp + cols + 2)*ext + 128) must stay above neg16
+        int64_t cap = INT32_MAX;
+        if (ge > 0) cap = (32768LL - ge - slack - 3LL * go) / ge - Lp - 2;
+        // upper bound: min(Lp, cols) * smax + open + 128 must stay below 32767
+        if (smax > 0) {
+            const int64_t lim = (32767LL - slack - go) / smax;
+            if (Lp > lim) cap = std::min(cap, lim);
+        }
+        r.max_cols16 = std::max<int64_t>(cap, 0);
+    } else {
+        r.max_cols16 = INT32_MAX;
+    }
+    return r;
+}
+
+// closed forms for empty query / empty target (oracle/opal_oracle.c dp_end, m == 0 || n == 0)
+int degenerate_score(int mode, int m, int n, int go, int ge) {
+    if (mode == MODE_NW) {
+        if (m == 0 && n == 0) return 0;
+        return -(go + (std::max(m, n) - 1) * ge);
+    }
+    if (mode == MODE_HW) return (m == 0) ? 0 : -(go + (m - 1) * ge);
+    return 0;
+}
+
+__global__ void scatter_fixes_kernel(const int32_t* fixes, int nfix, int32_t* out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nfix) out[fixes[2 * i]] = fixes[2 * i + 1];
+}
+
+search_kernel_t pick_kernel(int K, int W, bool local, bool psmem) {
+    if (W == 16) return local ? get_search_kernel_w16_l1(K, psmem) : get_search_kernel_w16_l0(K, psmem);
+    return local ? get_search_kernel_w32_l1(K, psmem) : get_search_kernel_w32_l0(K, psmem);
+}
+
+int launch_search(pyopal_cuda_db* db, search_kernel_t fn, const KParams& P, size_t smem, int64_t max_tasks,
+                  cudaStream_t st) {
+    const int threads = 256;
+    CU(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, threads, smem));
+    if (per_sm < 1) return fail(PYOPAL_CUDA_ERR_INTERNAL, "kernel does not fit on an SM");
+    int64_t grid = (int64_t)db->sm_count * per_sm;
+    const int64_t need = (max_tasks + (threads / 32) - 1) / (threads / 32);
+    grid = std::max<int64_t>(1, std::min(grid, need));
+    fn<<<(unsigned)grid, threads, smem, st>>>(P);
+    CU(cudaGetLastError());
+    db->stats[0]++;
+    return 0;
+}
+
+// Enqueue a SCORE search of [start, end) on `st`; scores land in d_out (device).
+int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq, int go, int ge,
+                         const int* M, int A, int mode, int64_t start, int64_t end, int32_t* d_out,
+                         cudaStream_t st) {
+    for (int i = 0; i < 12; i++) db->stats[i] = 0;
+    db->kev_valid[0] = db->kev_valid[1] = db->kev_valid[2] = false;
+    const int64_t nout = end - start;
+    if (nout <= 0) return 0;
+    const bool local = (mode == MODE_SW);
+
+    // host-side fix-ups: zero-length targets, or everything when the query is empty
+    std::vector<int32_t> fixes;
+    if (Lq == 0) {
+        // one value per target length; cheap enough to do on the host
+        for (int64_t i = start; i < end; i++) {
+            fixes.push_back((int32_t)(i - start));
+            fixes.push_back(degenerate_score(mode, 0, db->h_lengths[(size_t)i], go, ge));
+        }
+    } else {
+        for (int32_t z : db->h_zero_idx)
+            if (z >= start && z < end) {
+                fixes.push_back((int32_t)(z - start));
+                fixes.push_back(degenerate_score(mode, Lq, 0, go, ge));
+            }
+    }
+    auto apply_fixes = [&]() -> int {
+        if (fixes.empty()) return 0;
+        const int nfix = (int)(fixes.size() / 2);
+        if (db->fixes.reserve(fixes.size())) return PYOPAL_CUDA_ERR_NOMEM;
+        CU(cudaMemcpyAsync(db->fixes.p, fixes.data(), fixes.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+        scatter_fixes_kernel<<<(nfix + 255) / 256, 256, 0, st>>>(db->fixes.p, nfix, d_out);
+        CU(cudaGetLastError());
+        CU(cudaStreamSynchronize(st));  // `fixes` is a stack vector
+        return 0;
+    };
+    if (Lq == 0 || db->npairs == 0) return apply_fixes();
+
+    // plan
+    Plan plan = make_plan(Lq, A, db->mean_cols, (size_t)200 * 1024);
+    const int Lp = plan.npass * plan.G * plan.K;
+    Rung rung = make_rung(M, A, go, ge, mode, Lp);
+    // 32-bit overflow cannot happen below this bound (scores are exact otherwise)
+    {
+        int64_t mag = std::max<int64_t>({(int64_t)go, (int64_t)ge, 1});
+        for (int i = 0; i < A * A; i++) mag = std::max<int64_t>(mag, std::llabs((long long)M[i]));
+        const int64_t longest = db->h_pair_len[0];
+        if (mag * ((int64_t)Lp + longest + 8) >= (1LL << 29))
+            return fail(OPAL_ERR_OVERFLOW, "scores may exceed the 32-bit range");
+    }
+
+    // split the (length-sorted) pairs between the rungs
+    const bool whole = (start == 0 && end >= db->n);
+    int64_t n32pairs = 0;  // leading pairs (longest) that must run at 32 bit
+    if (!rung.ok16) n32pairs = db->npairs;
+    else if (!local) {
+        // first pair whose column count fits the 16-bit rung (lengths are descending)
+        int64_t lo = 0, hi = db->npairs;
+        while (lo < hi) {
+            int64_t mid = (lo + hi) / 2;
+            if (db->h_pair_len[(size_t)(2 * mid)] > rung.max_cols16) lo = mid + 1; else hi = mid;
+        }
+        n32pairs = lo;
+    }
+    std::vector<int32_t> wl16, wl32;
+    const int32_t* d_wl16 = nullptr;
+    int64_t n16 = 0;
+    auto in_range = [&](int32_t idx) { return idx >= start && idx < end; };
+    for (int64_t k = 0; k < n32pairs; k++) {
+        if (in_range(db->h_pair_idx[(size_t)(2 * k)])) wl32.push_back((int32_t)(k << 1));
+        if (db->h_pair_idx[(size_t)(2 * k + 1)] >= 0 && in_range(db->h_pair_idx[(size_t)(2 * k + 1)]))
+            wl32.push_back((int32_t)((k << 1) | 1));
+    }
+    if (whole) {
+        d_wl16 = db->d_identity + n32pairs;
+        n16 = db->npairs - n32pairs;
+    } else {
+        for (int64_t k = n32pairs; k < db->npairs; k++)
+            if (in_range(db->h_pair_idx[(size_t)(2 * k)]) ||
+                (db->h_pair_idx[(size_t)(2 * k + 1)] >= 0 && in_range(db->h_pair_idx[(size_t)(2 * k + 1)])))
+                wl16.push_back((int32_t)k);
+        n16 = (int64_t)wl16.size();
+        if (db->wl16.reserve(wl16.size() + 1)) return PYOPAL_CUDA_ERR_NOMEM;
+        if (n16) CU(cudaMemcpyAsync(db->wl16.p, wl16.data(), wl16.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+        d_wl16 = db->wl16.p;
+    }
+    const int64_t n32 = (int64_t)wl32.size();
+    if (db->wl32.reserve(wl32.size() + 1)) return PYOPAL_CUDA_ERR_NOMEM;
+    if (n32) CU(cudaMemcpyAsync(db->wl32.p, wl32.data(), wl32.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    if (local && n16 && db->ovf.reserve((size_t)(2 * n16))) return PYOPAL_CUDA_ERR_NOMEM;
+
+    // query, matrix, counters
+    if (db->query.reserve((size_t)Lq)) return PYOPAL_CUDA_ERR_NOMEM;
+    CU(cudaMemcpyAsync(db->query.p, query, (size_t)Lq, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(db->d_matrix, M, (size_t)A * A * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    int32_t counts[16] = {0};
+    counts[0] = (int32_t)n16; counts[1] = (int32_t)n32; counts[2] = 0;
+    CU(cudaMemcpyAsync(db->d_counts, counts, sizeof(counts), cudaMemcpyHostToDevice, st));
+    if (plan.npass > 1) {
+        const size_t need = (size_t)db->ncols * 2 + 16;
+        if (db->bndH.reserve(need) || db->bndF.reserve(need)) return PYOPAL_CUDA_ERR_NOMEM;
+    }
+
+    KParams P;
+    memset(&P, 0, sizeof(P));
+    P.stream = db->d_stream; P.pair_off = db->d_pair_off; P.pair_len = db->d_pair_len; P.pair_idx = db->d_pair_idx;
+    P.query = db->query.p; P.matrix = db->d_matrix;
+    P.Lq = Lq; P.A = A; P.go = go; P.ge = ge;
+    P.G = plan.G; P.logG = plan.logG; P.npass = plan.npass; P.pitch = plan.pitch; P.padtop = plan.padtop;
+    P.mode = mode; P.pad_score = rung.pad_score; P.ovf_thresh = rung.ovf_thresh;
+    P.out = d_out; P.out_start = start; P.out_end = end;
+    P.ovf_list = db->ovf.p; P.ovf_count = db->d_counts + 2;
+    P.bndH = db->bndH.p; P.bndF = db->bndF.p;
+
+    const bool wide = !rung.fits8;
+    search_kernel_t k32 = nullptr;
+    if (wide) {
+        // int32 profile in global memory; tile fixed at 32 x 32
+        Plan w; w.G = 32; w.logG = 5; w.K = 32; w.npass = (Lq + 1023) / 1024;
+        w.pitch = (w.npass * 1024 + 15) / 16 * 16; w.padtop = w.npass * 1024 - Lq; w.psmem = false; w.smem = 0;
+        plan = w;
+        P.G = 32; P.logG = 5; P.npass = w.npass; P.pitch = w.pitch; P.padtop = w.padtop;
+        if (w.npass > 1) {
+            const size_t need = (size_t)db->ncols * 2 + 16;
+            if (db->bndH.reserve(need) || db->bndF.reserve(need)) return PYOPAL_CUDA_ERR_NOMEM;
+            P.bndH = db->bndH.p; P.bndF = db->bndF.p;
+        }
+        if (db->wprofile.reserve((size_t)(A + 1) * w.pitch)) return PYOPAL_CUDA_ERR_NOMEM;
+        P.wprofile = db->wprofile.p;
+        build_profile_kernel<<<64, 256, 0, st>>>(P, nullptr, db->wprofile.p);
+        CU(cudaGetLastError());
+        k32 = get_search_kernel_wide(local);
+    } else {
+        if (!plan.psmem) {
+            if (db->gprofile.reserve((size_t)(A + 1) * plan.pitch)) return PYOPAL_CUDA_ERR_NOMEM;
+            P.gprofile = db->gprofile.p;
+            build_profile_kernel<<<64, 256, 0, st>>>(P, db->gprofile.p, nullptr);
+            CU(cudaGetLastError());
+        }
+        k32 = pick_kernel(plan.K, 32, local, plan.psmem);
+    }
+    if (!k32) return fail(PYOPAL_CUDA_ERR_INTERNAL, "no 32-bit kernel for this tile");
+    const int gpw = 32 >> plan.logG;
+
+    // 32-bit rung first: it holds the longest targets (tail latency)
+    if (n32 > 0) {
+        KParams Q = P;
+        Q.worklist = db->wl32.p; Q.nwork = db->d_counts + 1; Q.counter = db->d_counts + 5;
+        Q.neg = -(1 << 29);
+        CU(cudaEventRecord(db->kev[0], st));
+        int rc = launch_search(db, k32, Q, plan.smem, (n32 + gpw - 1) / gpw, st);
+        if (rc) return rc;
+        CU(cudaEventRecord(db->kev[1], st));
+        db->kev_valid[0] = true;
+    }
+    if (n16 > 0) {
+        search_kernel_t k16 = pick_kernel(plan.K, 16, local, plan.psmem);
+        if (!k16) return fail(PYOPAL_CUDA_ERR_INTERNAL, "no 16-bit kernel for this tile");
+        KParams Q = P;
+        Q.worklist = d_wl16; Q.nwork = db->d_counts + 0; Q.counter = db->d_counts + 4;
+        Q.neg = rung.neg16;
+        CU(cudaEventRecord(db->kev[2], st));
+        int rc = launch_search(db, k16, Q, plan.smem, (n16 + gpw - 1) / gpw, st);
+        if (rc) return rc;
+        CU(cudaEventRecord(db->kev[3], st));
+        db->kev_valid[1] = true;
+        if (local) {
+            // rescore what overflowed; the list and its size live on the device
+            KParams R = P;
+            R.worklist = db->ovf.p; R.nwork = db->d_counts + 2; R.counter = db->d_counts + 6;
+            R.neg = -(1 << 29);
+            CU(cudaEventRecord(db->kev[4], st));
+            rc = launch_search(db, k32, R, plan.smem, std::min<int64_t>(2 * n16, (int64_t)db->sm_count * 64), st);
+            if (rc) return rc;
+            CU(cudaEventRecord(db->kev[5], st));
+            db->kev_valid[2] = true;
+        }
+    }
+    db->stats[1] = n16 * 2; db->stats[2] = n32;
+    db->stats[5] = plan.G; db->stats[6] = plan.K; db->stats[7] = plan.npass; db->stats[11] = plan.psmem ? 1 : 0;
+    return apply_fixes();
+}
+
+int check_search_args(pyopal_cuda_db* db, const unsigned char* query, int Lq, int go, int ge, const int* M,
+                      int A, int mode, int64_t* start, int64_t* end) {
+    if (!db || !M || (Lq > 0 && !query)) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null argument");
+    if (mode < MODE_NW || mode > MODE_SW) return fail(OPAL_ERR_INVALID_MODE, "invalid alignment mode");
+    if (A != db->A) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "alphabet length differs from the store's");
+    if (Lq < 0) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "negative query length");
+    if (go < 0 || ge < 0) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "gap penalties must be non-negative");
+    for (int i = 0; i < Lq; i++)
+        if (query[i] >= A) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "query residue code outside the alphabet");
+    if (*start < 0) *start = 0;
+    if (*end > db->n) *end = db->n;
+    if (*end < *start) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "slice end is lower than start");
+    return 0;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------
+// Public search entry points
+
+// end / full modes (endloc.cu)
+int pyopal_end_full_search(pyopal_cuda_db* db, const unsigned char* query, int Lq, int go, int ge, const int* M,
+                           int A, int searchType, int mode, int64_t start, int64_t end, int32_t* scores,
+                           int32_t* endQ, int32_t* endT, int32_t* startQ, int32_t* startT, unsigned char* ops,
+                           const int64_t* ops_offsets, int32_t* ops_len);
+
+extern "C" int pyopal_cuda_search_scores_device(pyopal_cuda_db* db, const unsigned char* query, int queryLength,
+                                                int gapOpen, int gapExt, const int* scoreMatrix,
+                                                int alphabetLength, int mode, int64_t start, int64_t end,
+                                                int32_t* d_scores, void* stream) {
+    int rc = check_search_args(db, query, queryLength, gapOpen, gapExt, scoreMatrix, alphabetLength, mode, &start, &end);
+    if (rc) return rc;
+    if (end > start && !d_scores) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null output");
+    std::lock_guard<std::mutex> lock(db->mu);
+    CU(cudaSetDevice(db->device));
+    return enqueue_score_search(db, query, queryLength, gapOpen, gapExt, scoreMatrix, alphabetLength, mode, start,
+                                end, d_scores, (cudaStream_t)stream);
+}
+
+extern "C" int pyopal_cuda_search(pyopal_cuda_db* db, const unsigned char* query, int queryLength, int gapOpen,
+                                  int gapExt, const int* scoreMatrix, int alphabetLength, int searchType, int mode,
+                                  int overflowMethod, int64_t start, int64_t end, int32_t* scores, int32_t* endQ,
+                                  int32_t* endT, int32_t* startQ, int32_t* startT, unsigned char* ops,
+                                  const int64_t* ops_offsets, int32_t* ops_len) {
+    int rc = check_search_args(db, query, queryLength, gapOpen, gapExt, scoreMatrix, alphabetLength, mode, &start, &end);
+    if (rc) return rc;
+    if (searchType < OPAL_SEARCH_SCORE || searchType > OPAL_SEARCH_ALIGNMENT)
+        return fail(OPAL_ERR_INVALID_MODE, "invalid search type");
+    if (overflowMethod != OPAL_OVERFLOW_SIMPLE && overflowMethod != OPAL_OVERFLOW_BUCKETS)
+        return fail(OPAL_ERR_INVALID_MODE, "invalid overflow method");
+    const int64_t nout = end - start;
+    if (nout <= 0) return 0;
+    if (!scores) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null output");
+    std::lock_guard<std::mutex> lock(db->mu);
+    CU(cudaSetDevice(db->device));
+    if (searchType != OPAL_SEARCH_SCORE)
+        return pyopal_end_full_search(db, query, queryLength, gapOpen, gapExt, scoreMatrix, alphabetLength,
+                                      searchType, mode, start, end, scores, endQ, endT, startQ, startT, ops,
+                                      ops_offsets, ops_len);
+    if (db->out.reserve((size_t)nout)) return PYOPAL_CUDA_ERR_NOMEM;
+    CU(cudaEventRecord(db->ev0, db->stream));
+    rc = enqueue_score_search(db, query, queryLength, gapOpen, gapExt, scoreMatrix, alphabetLength, mode, start, end,
+                              db->out.p, db->stream);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(scores, db->out.p, (size_t)nout * sizeof(int32_t), cudaMemcpyDeviceToHost, db->stream));
+    CU(cudaEventRecord(db->ev1, db->stream));
+    CU(cudaStreamSynchronize(db->stream));
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, db->ev0, db->ev1));
+    db->stats[4] = (int64_t)(ms * 1000.0f);
+    int32_t novf = 0;
+    CU(cudaMemcpy(&novf, db->d_counts + 2, sizeof(int32_t), cudaMemcpyDeviceToHost));
+    db->stats[3] = novf;
+    return 0;
+}
+
+extern "C" int pyopal_cuda_search_batch(pyopal_cuda_db* db, const unsigned char* queries, const int64_t* q_offsets,
+                                        const int32_t* q_lengths, int nq, int gapOpen, int gapExt,
+                                        const int* scoreMatrix, int alphabetLength, int mode, int32_t* scores) {
+    if (!db || nq < 0 || (nq > 0 && (!queries || !q_offsets || !q_lengths || !scores)))
+        return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null argument");
+    const int64_t n = db->n;
+    if (n == 0) return 0;
+    std::lock_guard<std::mutex> lock(db->mu);
+    CU(cudaSetDevice(db->device));
+    // double-buffer the score rows so the D2H of query i overlaps the kernels of query i+1
+    int32_t* d_rows[2] = {nullptr, nullptr};
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t done[2] = {nullptr, nullptr}, copied[2] = {nullptr, nullptr};
+    int rc = 0;
+    auto cleanup = [&]() {
+        for (int b = 0; b < 2; b++) {
+            if (d_rows[b]) cudaFree(d_rows[b]);
+            if (done[b]) cudaEventDestroy(done[b]);
+            if (copied[b]) cudaEventDestroy(copied[b]);
+        }
+        if (copy_stream) cudaStreamDestroy(copy_stream);
+    };
+#define CUB(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { cleanup(); return fail(PYOPAL_CUDA_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } } while (0)
+    CUB(cudaStreamCreateWithFlags(&copy_stream, cudaStreamNonBlocking));
+    for (int b = 0; b < 2; b++) {
+        CUB(cudaMalloc(&d_rows[b], (size_t)n * sizeof(int32_t)));
+        CUB(cudaEventCreateWithFlags(&done[b], cudaEventDisableTiming));
+        CUB(cudaEventCreateWithFlags(&copied[b], cudaEventDisableTiming));
+    }
+    for (int i = 0; i < nq && rc == 0; i++) {
+        const int b = i & 1;
+        int64_t s = 0, e = n;
+        const unsigned char* q = queries + q_offsets[i];
+        rc = check_search_args(db, q, q_lengths[i], gapOpen, gapExt, scoreMatrix, alphabetLength, mode, &s, &e);
+        if (rc) break;
+        if (i >= 2) CUB(cudaStreamWaitEvent(db->stream, copied[b], 0));
+        rc = enqueue_score_search(db, q, q_lengths[i], gapOpen, gapExt, scoreMatrix, alphabetLength, mode, 0, n,
+                                  d_rows[b], db->stream);
+        if (rc) break;
+        CUB(cudaEventRecord(done[b], db->stream));
+        CUB(cudaStreamWaitEvent(copy_stream, done[b], 0));
+        CUB(cudaMemcpyAsync(scores + (size_t)i * (size_t)n, d_rows[b], (size_t)n * sizeof(int32_t),
+                            cudaMemcpyDeviceToHost, copy_stream));
+        CUB(cudaEventRecord(copied[b], copy_stream));
+        // the per-search workspace (query, counters, lists) is reused by the next query
+        CUB(cudaStreamSynchronize(db->stream));
+    }
+    if (rc == 0) CUB(cudaStreamSynchronize(copy_stream));
+#undef CUB
+    cleanup();
+    return rc;
+}
+
+// Generic path with the reference's own signature (opal.pxd:40-54): stage the
+// database, search, unpack into the caller's OpalSearchResult structs.
+extern "C" int opalSearchDatabase(unsigned char query[], int queryLength, unsigned char* db[], int dbLength,
+                                  int dbSeqLengths[], int gapOpen, int gapExt, int* scoreMatrix,
+                                  int alphabetLength, OpalSearchResult* results[], const int searchType, int mode,
+                                  int overflowMethod) {
+    if (dbLength < 0) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "negative database length");
+    if (dbLength == 0) return 0;
+    if (!db || !dbSeqLengths || !results) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null argument");
+    int device = 0;
+    if (pyopal_cuda_device_count() <= 0) return fail(OPAL_ERR_NO_SIMD_SUPPORT, "no CUDA device available");
+    cudaGetDevice(&device);
+    pyopal_cuda_db* h = nullptr;
+    int rc = pyopal_cuda_db_create_from_pointers(device, (const unsigned char* const*)db, dbSeqLengths, dbLength,
+                                                 alphabetLength, &h);
+    if (rc) return rc;
+    const size_t n = (size_t)dbLength;
+    std::vector<int32_t> sc(n), eq(n, -1), et(n, -1), sq(n, -1), st(n, -1), ol(n, 0);
+    std::vector<int64_t> oo;
+    std::vector<unsigned char> ops;
+    if (searchType == OPAL_SEARCH_ALIGNMENT) {
+        oo.resize(n);
+        int64_t tot = 0;
+        for (size_t k = 0; k < n; k++) { oo[k] = tot; tot += (int64_t)queryLength + dbSeqLengths[k]; }
+        ops.resize((size_t)tot + 1);
+    }
+    rc = pyopal_cuda_search(h, query, queryLength, gapOpen, gapExt, scoreMatrix, alphabetLength, searchType, mode,
+                            overflowMethod, 0, dbLength, sc.data(), eq.data(), et.data(), sq.data(), st.data(),
+                            ops.empty() ? nullptr : ops.data(), oo.empty() ? nullptr : oo.data(), ol.data());
+    pyopal_cuda_db_destroy(h);
+    if (rc) return rc;
+    for (size_t k = 0; k < n; k++) {
+        OpalSearchResult* r = results[k];
+        if (!r) continue;
+        r->scoreSet = 1;
+        r->score = sc[k];
+        if (searchType >= OPAL_SEARCH_SCORE_END) { r->endLocationQuery = eq[k]; r->endLocationTarget = et[k]; }
+        if (searchType == OPAL_SEARCH_ALIGNMENT) {
+            r->startLocationQuery = sq[k];
+            r->startLocationTarget = st[k];
+            r->alignmentLength = ol[k];
+            r->alignment = nullptr;
+            if (ol[k] > 0) {
+                r->alignment = (unsigned char*)malloc((size_t)ol[k]);
+                if (!r->alignment) return fail(PYOPAL_CUDA_ERR_NOMEM, "host allocation failed");
+                memcpy(r->alignment, ops.data() + oo[k], (size_t)ol[k]);
+            }
+        }
+    }
+    return 0;
+}

@@ -1,0 +1,344 @@
+// pyopal_b200/csrc/kernels.cuh -- sm_100a database-search kernels.
+//
+// Replaces the SIMD inner loop of opalSearchDatabase (declared at
+// /root/reference/src/pyopal/opal.pxd:40-54; the source lives in the absent
+// vendor/opal submodule).  Not a port: the CPU library runs one target per
+// SIMD lane down whole query columns; here
+//
+//   * the QUERY is register-tiled: a group of G threads (G = 4..32 lanes of
+//     one warp) holds G*K consecutive query rows, K rows per thread, H-open
+//     and E of the previous column in registers;
+//   * the TARGET streams through the group one column per step, thread p
+//     working on column (step - p): an anti-diagonal wavefront whose only
+//     communication is two warp shuffles per step (H and F of the row above);
+//   * in the 16-bit rung every 32-bit lane carries TWO targets (s16x2) and the
+//     cell update is six DPX instructions (VIADDMNMX.S16x2, VIMNMX3.S16x2...);
+//     the database is stored pair-interleaved so one u16 load yields the
+//     residues of both targets;
+//   * substitution scores come from a query profile in shared memory
+//     (int8, score+gap_open folded), fetched K rows at a time with vector LDS
+//     and widened with one PRMT per cell pair;
+//   * queries longer than G*K rows take several passes; the last row of a
+//     pass (H, F per column) round-trips through an L2-resident buffer;
+//   * the 32-bit rung is the same code with one target per lane; 16-bit
+//     overflow is detected from the running maximum (scores stay exact, so the
+//     ladder is result-invisible, lib.pyx:1283-1289).
+//
+// Padding rows sit ABOVE query row 0 and are arithmetically transparent (see
+// build_profile), so the last query row is always the last register of the
+// last thread of the last pass: NW/HW/OV read their result from it without
+// any per-cell bookkeeping.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace pyopal {
+
+enum : int { MODE_NW = 0, MODE_HW = 1, MODE_OV = 2, MODE_SW = 3 };
+
+struct KParams {
+    // pair-interleaved store
+    const uint16_t* stream;   // column c of pair k at stream[pair_off[k] + c]: lo byte = target a, hi = target b
+    const int64_t* pair_off;  // [npairs]
+    const int32_t* pair_len;  // [2*npairs] len_a >= len_b (len_b = 0 if absent)
+    const int32_t* pair_idx;  // [2*npairs] database index of a, b (-1 if absent)
+    // work
+    const int32_t* worklist;  // W=16: pair ids; W=32: (pair << 1) | half
+    const int32_t* nwork;     // device-resident count (lets a kernel produce the next kernel's list)
+    int32_t* counter;         // task counter, zeroed before launch
+    // query
+    const uint8_t* query;
+    const int32_t* matrix;    // A x A, row = query letter, column = target letter (pyx.in:86)
+    const int8_t* gprofile;   // global-memory profile when it does not fit shared memory
+    const int32_t* wprofile;  // int32 global profile for matrices / gap costs outside the int8 range
+    int Lq, A, go, ge;
+    int G, logG, npass, pitch, padtop;
+    int mode;
+    int neg;                  // "-infinity" for this rung
+    int pad_score;            // folded score of padding rows / the padding letter
+    int ovf_thresh;           // 16-bit rung, SW: running max >= this => rescore at 32 bit
+    // results
+    int32_t* out;             // scores in database order, entry (index - out_start)
+    int64_t out_start, out_end;
+    int32_t* ovf_list;        // (pair << 1) | half of overflowed targets
+    int32_t* ovf_count;
+    // pass boundary (row above the tile): W=16 indexed like `stream`, W=32 at 2*column + half
+    uint32_t* bndH;
+    uint32_t* bndF;
+};
+
+// ---------------------------------------------------------------------------
+// value traits: one s16x2 word (two targets) or one s32 (one target) per lane
+template <int W> struct Val;
+
+template <> struct Val<16> {
+    typedef uint32_t T;
+    static __device__ __forceinline__ T splat(int v) { return (uint32_t)(uint16_t)(int16_t)v * 0x00010001u; }
+    static __device__ __forceinline__ T addmax(T a, T b, T c) { return __viaddmax_s16x2(a, b, c); }
+    static __device__ __forceinline__ T add(T a, T b) { return __vadd2(a, b); }
+    static __device__ __forceinline__ T sub(T a, T b) { return __vsub2(a, b); }
+    static __device__ __forceinline__ T max2(T a, T b) { return __vmaxs2(a, b); }
+    static __device__ __forceinline__ T max3(T a, T b, T c) { return __vimax3_s16x2(a, b, c); }
+    static __device__ __forceinline__ T max3relu(T a, T b, T c) { return __vimax3_s16x2_relu(a, b, c); }
+    static __device__ __forceinline__ int lo(T v) { return (int)(int16_t)(v & 0xffffu); }
+    static __device__ __forceinline__ int hi(T v) { return (int)(int16_t)(v >> 16); }
+};
+
+template <> struct Val<32> {
+    typedef int T;
+    static __device__ __forceinline__ T splat(int v) { return v; }
+    static __device__ __forceinline__ T addmax(T a, T b, T c) { return __viaddmax_s32(a, b, c); }
+    static __device__ __forceinline__ T add(T a, T b) { return a + b; }
+    static __device__ __forceinline__ T sub(T a, T b) { return a - b; }
+    static __device__ __forceinline__ T max2(T a, T b) { return max(a, b); }
+    static __device__ __forceinline__ T max3(T a, T b, T c) { return __vimax3_s32(a, b, c); }
+    static __device__ __forceinline__ T max3relu(T a, T b, T c) { return __vimax3_s32_relu(a, b, c); }
+    static __device__ __forceinline__ int lo(T v) { return v; }
+    static __device__ __forceinline__ int hi(T v) { return v; }
+};
+
+// Profile: prof[letter * pitch + tile_row], letter in [0, A] (A = padding
+// letter), tile_row in [0, npass*G*K).  Entry = S[q][letter] + gap_open so the
+// kernel can keep H-open instead of H (one subtract per cell feeds both E and
+// F).  Tile rows < padtop are padding ABOVE the query: with a free top border
+// (HW/OV/SW) score 0 keeps them at H = 0; with NW's penalised border a score
+// of -max(open, ext) makes each of them reproduce the border row exactly.
+__device__ __forceinline__ int profile_entry(const KParams& P, int letter, int trow) {
+    int qi = trow - P.padtop;
+    if (qi < 0 || letter >= P.A) return P.pad_score;
+    return P.matrix[(int)P.query[qi] * P.A + letter] + P.go;
+}
+
+// PRMT selectors (generic mode: nibble bit 3 replicates the selected byte's
+// sign).  __byte_perm masks that bit away, hence the inline PTX.
+template <unsigned SEL>
+__device__ __forceinline__ uint32_t prmt(uint32_t x, uint32_t y) {
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(x), "r"(y), "n"(SEL));
+    return d;
+}
+// (sext16(byte u of x), sext16(byte u of y))
+__device__ __forceinline__ uint32_t widen_pair(uint32_t x, uint32_t y, int u) {
+    switch (u) {
+        case 0: return prmt<0xC480>(x, y);
+        case 1: return prmt<0xD591>(x, y);
+        case 2: return prmt<0xE6A2>(x, y);
+        default: return prmt<0xF7B3>(x, y);
+    }
+}
+// sext32(byte u of x)
+__device__ __forceinline__ int widen_one(uint32_t x, int u) {
+    switch (u) {
+        case 0: return (int)prmt<0x8880>(x, 0u);
+        case 1: return (int)prmt<0x9991>(x, 0u);
+        case 2: return (int)prmt<0xAAA2>(x, 0u);
+        default: return (int)prmt<0xBBB3>(x, 0u);
+    }
+}
+
+template <int K, int W, bool LOCAL, bool PSMEM, bool WIDE = false>
+__global__ void __launch_bounds__(256) search_kernel(const __grid_constant__ KParams P) {
+    static_assert(K % 4 == 0, "K must be a multiple of 4");
+    static_assert(!WIDE || (W == 32 && !PSMEM), "wide profile: 32-bit rung, global memory only");
+    typedef Val<W> V;
+    typedef typename V::T val_t;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+
+    const int8_t* prof;
+    if (PSMEM) {
+        int8_t* sp = reinterpret_cast<int8_t*>(smem_raw);
+        const int total = (P.A + 1) * P.pitch;
+        for (int x = threadIdx.x; x < total; x += blockDim.x) {
+            int letter = x / P.pitch, trow = x - letter * P.pitch;
+            sp[x] = (int8_t)profile_entry(P, letter, trow);
+        }
+        __syncthreads();
+        prof = sp;
+    } else {
+        prof = P.gprofile;
+    }
+
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const int G = P.G;
+    const int p = lane & (G - 1);
+    const int grp = lane >> P.logG;
+    const int gpw = 32 >> P.logG;
+    const int T = G * K;
+    const int nwork = *P.nwork;
+    const int ntasks = (nwork + gpw - 1) / gpw;
+    const bool top_free = (P.mode != MODE_NW);
+    const bool left_free = (P.mode == MODE_OV || P.mode == MODE_SW);
+    const val_t NEGEXT = V::splat(-P.ge);
+    const val_t OPEN = V::splat(P.go);
+    const val_t NEG = V::splat(P.neg);
+    const int lastpass = P.npass - 1;
+
+    for (;;) {
+        int task = 0;
+        if (lane == 0) task = atomicAdd(P.counter, 1);
+        task = __shfl_sync(FULL, task, 0);
+        if (task >= ntasks) break;
+
+        const int work = task * gpw + grp;
+        const bool have = work < nwork;
+        const int entry = have ? P.worklist[work] : 0;
+        const int pair = (W == 16) ? entry : (entry >> 1);
+        const int half = entry & 1;
+        const int64_t off = have ? P.pair_off[pair] : 0;
+        const int lenA = have ? P.pair_len[2 * pair] : 0;
+        const int lenB = have ? P.pair_len[2 * pair + 1] : 0;
+        // columns this group walks; len0/len1 = lengths of the target(s) in the lo/hi half
+        const int len0 = (W == 16) ? lenA : (half ? lenB : lenA);
+        const int len1 = (W == 16) ? lenB : 0;
+        const int ncol = len0;
+        const int nsteps = __reduce_max_sync(FULL, ncol) + G - 1;
+
+        val_t best = V::splat(0);             // SW: running max of H
+        int res0 = INT_MIN, res1 = INT_MIN;   // NW/HW/OV
+
+        for (int pass = 0; pass < P.npass; ++pass) {
+            const int rowbase = pass * T + p * K;  // tile row of register 0
+            val_t Gl[K], E[K];
+#pragma unroll
+            for (int r = 0; r < K; ++r) {
+                int qi = rowbase + r - P.padtop;
+                int hl = (left_free || qi < 0) ? 0 : -(P.go + qi * P.ge);
+                Gl[r] = V::splat(hl - P.go);
+                E[r] = NEG;
+            }
+            val_t Gout = V::splat(0), Fout = NEG, upGprev;
+            {
+                int qi = rowbase - 1 - P.padtop;
+                int hl = (left_free || qi < 0) ? 0 : -(P.go + qi * P.ge);
+                upGprev = V::splat(hl - P.go);
+            }
+            for (int s = 0; s < nsteps; ++s) {
+                val_t upG = __shfl_up_sync(FULL, Gout, 1, G);
+                val_t upF = __shfl_up_sync(FULL, Fout, 1, G);
+                const int j = s - p;
+                const bool active = (j >= 0) && (j < ncol);
+                if (p == 0) {
+                    if (pass == 0) {
+                        int ht = top_free ? 0 : -(P.go + j * P.ge);
+                        upG = V::splat(ht - P.go);
+                        upF = NEG;
+                    } else if (active) {
+                        const int64_t bi = (W == 16) ? (off + j) : (2 * (off + j) + half);
+                        upG = (val_t)__ldcg(P.bndH + bi);
+                        upF = (val_t)__ldcg(P.bndF + bi);
+                    }
+                }
+                if (active) {
+                    const unsigned code = P.stream[off + j];
+                    const unsigned t0 = (W == 16) ? (code & 0xffu) : (half ? (code >> 8) : (code & 0xffu));
+                    const unsigned t1 = code >> 8;
+                    const int8_t* pa = prof + t0 * P.pitch + rowbase;
+                    const int8_t* pb = prof + t1 * P.pitch + rowbase;
+                    val_t F = upF, Gup = upG, Gd = upGprev;
+#pragma unroll
+                    for (int c = 0; c < K / 4; ++c) {
+                        uint32_t wa = 0, wb = 0;
+                        int4 sw = make_int4(0, 0, 0, 0);
+                        if (WIDE) {
+                            sw = __ldg(reinterpret_cast<const int4*>(P.wprofile + (size_t)t0 * P.pitch + rowbase) + c);
+                        } else if (PSMEM) {
+                            wa = *reinterpret_cast<const uint32_t*>(pa + 4 * c);
+                            if (W == 16) wb = *reinterpret_cast<const uint32_t*>(pb + 4 * c);
+                        } else {
+                            wa = __ldg(reinterpret_cast<const uint32_t*>(pa + 4 * c));
+                            if (W == 16) wb = __ldg(reinterpret_cast<const uint32_t*>(pb + 4 * c));
+                        }
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const int r = 4 * c + u;
+                            val_t S;
+                            if (WIDE) S = (val_t)(u == 0 ? sw.x : u == 1 ? sw.y : u == 2 ? sw.z : sw.w);
+                            else if (W == 16) S = (val_t)widen_pair(wa, wb, u);
+                            else S = (val_t)widen_one(wa, u);
+                            E[r] = V::addmax(E[r], NEGEXT, Gl[r]);   // max(E - ext, Hleft - open)
+                            F = V::addmax(F, NEGEXT, Gup);           // max(F - ext, Hup - open)
+                            val_t Td = V::add(Gd, S);                // Hdiag + S  (S carries the +open)
+                            val_t Hn = LOCAL ? V::max3relu(Td, E[r], F) : V::max3(Td, E[r], F);
+                            Gd = Gl[r];
+                            Gup = V::sub(Hn, OPEN);
+                            Gl[r] = Gup;
+                            if (LOCAL) best = V::max2(best, Hn);
+                        }
+                    }
+                    Gout = Gup;
+                    Fout = F;
+                    upGprev = upG;
+                    if (p == G - 1) {
+                        if (pass != lastpass) {
+                            const int64_t bi = (W == 16) ? (off + j) : (2 * (off + j) + half);
+                            __stcg(P.bndH + bi, (uint32_t)Gout);
+                            __stcg(P.bndF + bi, (uint32_t)Fout);
+                        } else if (!LOCAL) {
+                            // last query row: H = Gout + open
+                            const int h0 = V::lo(Gout) + P.go, h1 = V::hi(Gout) + P.go;
+                            if (P.mode == MODE_NW) {
+                                if (j == len0 - 1) res0 = h0;
+                                if (j == len1 - 1) res1 = h1;
+                            } else {
+                                if (j < len0) res0 = max(res0, h0);
+                                if (j < len1) res1 = max(res1, h1);
+                            }
+                        }
+                    }
+                    if (!LOCAL && P.mode == MODE_OV && (j == len0 - 1 || j == len1 - 1)) {
+                        // last target column: every real query row is a candidate
+#pragma unroll
+                        for (int r = 0; r < K; ++r) {
+                            if (rowbase + r >= P.padtop) {
+                                if (j == len0 - 1) res0 = max(res0, V::lo(Gl[r]) + P.go);
+                                if (W == 16 && j == len1 - 1) res1 = max(res1, V::hi(Gl[r]) + P.go);
+                            }
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+        }
+
+        // reduce over the group, lane p == 0 publishes
+        int r0, r1;
+        if (LOCAL) { r0 = V::lo(best); r1 = V::hi(best); }
+        else { r0 = res0; r1 = res1; }
+        for (int d = 1; d < G; d <<= 1) {
+            r0 = max(r0, __shfl_xor_sync(FULL, r0, d));
+            r1 = max(r1, __shfl_xor_sync(FULL, r1, d));
+        }
+        if (have && p == 0) {
+            if (W == 16) {
+                const int ia = P.pair_idx[2 * pair], ib = P.pair_idx[2 * pair + 1];
+                if (ia >= P.out_start && ia < P.out_end) {
+                    if (LOCAL && r0 >= P.ovf_thresh) P.ovf_list[atomicAdd(P.ovf_count, 1)] = pair << 1;
+                    else P.out[ia - P.out_start] = r0;
+                }
+                if (ib >= P.out_start && ib < P.out_end) {
+                    if (LOCAL && r1 >= P.ovf_thresh) P.ovf_list[atomicAdd(P.ovf_count, 1)] = (pair << 1) | 1;
+                    else P.out[ib - P.out_start] = r1;
+                }
+            } else {
+                const int ix = P.pair_idx[2 * pair + half];
+                if (ix >= P.out_start && ix < P.out_end) P.out[ix - P.out_start] = r0;
+            }
+        }
+    }
+}
+
+// Materialise the profile in global memory (queries too long for shared
+// memory, or scores outside int8).
+__global__ void build_profile_kernel(const KParams P, int8_t* narrow, int32_t* wide);
+
+typedef void (*search_kernel_t)(const KParams);
+
+// defined in kernels_w*_l*.cu; nullptr when the combination is not built
+search_kernel_t get_search_kernel_w16_l1(int K, bool psmem);
+search_kernel_t get_search_kernel_w16_l0(int K, bool psmem);
+search_kernel_t get_search_kernel_w32_l1(int K, bool psmem);
+search_kernel_t get_search_kernel_w32_l0(int K, bool psmem);
+search_kernel_t get_search_kernel_wide(bool local);  // K = 32, W = 32
+
+}  // namespace pyopal

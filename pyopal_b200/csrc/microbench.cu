@@ -1,0 +1,68 @@
+// pyopal_b200/csrc/microbench.cu -- integer-issue microbenchmark behind the
+// cell-update roofline: the six instructions of the 16-bit
+// cell (2x VIADDMNMX.S16x2, VIADDMNMX.S16x2.RELU, VIMNMX.S16x2.RELU,
+// VIADD.16x2, VIMNMX3.S16x2 at half rate, PRMT) on independent registers.
+#include "../../include/pyopal_cuda.h"
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace {
+constexpr int CHAINS = 8;
+constexpr int INNER = 64;
+// one "cell" per chain per inner iteration: 6 DPX/ALU instructions + 1 PRMT
+__global__ void __launch_bounds__(256) issue_kernel(uint32_t* out, int iters, uint32_t seed) {
+    uint32_t e[CHAINS], f[CHAINS], g[CHAINS], b = 0;
+    const uint32_t negext = 0xffffffffu, open = 0x000b000bu;
+    for (int c = 0; c < CHAINS; c++) { e[c] = seed + c; f[c] = seed * 3 + c; g[c] = seed * 7 + threadIdx.x + c; }
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int k = 0; k < INNER; k++) {
+#pragma unroll
+            for (int c = 0; c < CHAINS; c++) {
+                uint32_t s;
+                asm volatile("prmt.b32 %0, %1, %2, 0xC480;" : "=r"(s) : "r"(g[c]), "r"(e[c]));
+                e[c] = __viaddmax_s16x2(e[c], negext, g[c]);
+                f[c] = __viaddmax_s16x2(f[c], negext, g[(c + 1) % CHAINS]);
+                uint32_t h = __viaddmax_s16x2_relu(g[c], s, e[c]);
+                h = __vimax_s16x2_relu(h, f[c]);
+                g[c] = __vsub2(h, open);
+                if (k & 1) b = __vimax3_s16x2(b, h, g[c]);
+            }
+        }
+    }
+    uint32_t acc = b;
+    for (int c = 0; c < CHAINS; c++) acc ^= e[c] ^ f[c] ^ g[c];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
+}
+}  // namespace
+
+extern "C" int pyopal_cuda_int_issue_rate(int device, double* thread_instr_per_s, double* sm_clock_mhz) {
+    if (cudaSetDevice(device) != cudaSuccess) return OPAL_ERR_NO_SIMD_SUPPORT;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return PYOPAL_CUDA_ERR_CUDA;
+    const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 200;
+    uint32_t* d = nullptr;
+    if (cudaMalloc(&d, (size_t)blocks * threads * sizeof(uint32_t)) != cudaSuccess) return PYOPAL_CUDA_ERR_NOMEM;
+    cudaEvent_t a, b;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    issue_kernel<<<blocks, threads>>>(d, 10, 1u);  // warm-up
+    cudaDeviceSynchronize();
+    float best_ms = 1e30f;
+    for (int rep = 0; rep < 5; rep++) {
+        cudaEventRecord(a);
+        issue_kernel<<<blocks, threads>>>(d, iters, 1u + rep);
+        cudaEventRecord(b);
+        cudaEventSynchronize(b);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, a, b);
+        if (ms < best_ms) best_ms = ms;
+    }
+    cudaError_t e = cudaGetLastError();
+    cudaEventDestroy(a); cudaEventDestroy(b); cudaFree(d);
+    if (e != cudaSuccess) return PYOPAL_CUDA_ERR_CUDA;
+    // 6.5 instructions per cell: E, F, H(2), G, best (every other cell), PRMT
+    const double instr = (double)blocks * threads * (double)iters * INNER * CHAINS * 6.5;
+    if (thread_instr_per_s) *thread_instr_per_s = instr / (best_ms * 1e-3);
+    if (sm_clock_mhz) *sm_clock_mhz = prop.clockRate / 1000.0;
+    return 0;
+}

@@ -1,0 +1,401 @@
+"""The CUDA (sm_100a) platform module: ``searchCUDA``.
+
+This is the fifth sibling of the reference's per-ISA plugin modules
+``pyopal.platform.{sse2,sse4,avx2,neon}``, all generated from
+/root/reference/src/pyopal/platform/pyx.in.  ``searchCUDA`` has the signature
+of ``search${SIMD}`` (pyx.in:16-27), builds the result list the same way
+(pyx.in:62-72), maps return codes to the same exceptions (pyx.in:102-107) and
+calls the C-ABI in ``libpyopal_cuda.so`` (include/pyopal_cuda.h) where the
+template calls ``opalSearchDatabase`` (pyx.in:77-91).
+
+There is no CPU fallback: if the shared library is missing, or no CUDA device
+is visible, the call raises ``RuntimeError`` -- the class the reference raises
+for "no supported SIMD backend available" (lib.pyx:1226-1227).
+"""
+
+import array
+import ctypes
+import os
+import threading
+
+UINT32_MAX = 0xFFFFFFFF
+
+# include/pyopal_cuda.h
+OPAL_ERR_OVERFLOW = 1
+OPAL_ERR_NO_SIMD_SUPPORT = 2
+OPAL_ERR_INVALID_MODE = 3
+PYOPAL_CUDA_ERR_CUDA = 16
+PYOPAL_CUDA_ERR_NOMEM = 17
+PYOPAL_CUDA_ERR_ARGUMENT = 18
+PYOPAL_CUDA_ERR_INTERNAL = 19
+
+OPAL_MODE_NW, OPAL_MODE_HW, OPAL_MODE_OV, OPAL_MODE_SW = 0, 1, 2, 3
+OPAL_OVERFLOW_SIMPLE, OPAL_OVERFLOW_BUCKETS = 0, 1
+OPAL_SEARCH_SCORE, OPAL_SEARCH_SCORE_END, OPAL_SEARCH_ALIGNMENT = 0, 1, 2
+OPAL_ALIGN_MATCH, OPAL_ALIGN_DEL, OPAL_ALIGN_INS, OPAL_ALIGN_MISMATCH = 0, 1, 2, 3
+
+_LIB_NAME = "libpyopal_cuda.so"
+_lib = None
+_lib_lock = threading.Lock()
+
+_c_i32p = ctypes.POINTER(ctypes.c_int32)
+_c_i64p = ctypes.POINTER(ctypes.c_int64)
+_c_u8p = ctypes.POINTER(ctypes.c_ubyte)
+
+
+class OpalSearchResult(ctypes.Structure):
+    """/root/reference/src/pyopal/opal.pxd:26-34."""
+
+    _fields_ = [
+        ("scoreSet", ctypes.c_int),
+        ("score", ctypes.c_int),
+        ("endLocationTarget", ctypes.c_int),
+        ("endLocationQuery", ctypes.c_int),
+        ("startLocationTarget", ctypes.c_int),
+        ("startLocationQuery", ctypes.c_int),
+        ("alignment", ctypes.POINTER(ctypes.c_ubyte)),
+        ("alignmentLength", ctypes.c_int),
+    ]
+
+
+def library_path():
+    return os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), _LIB_NAME)
+
+
+def load_library():
+    """Load ``libpyopal_cuda.so`` and declare every prototype of the header."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lib_lock:
+        if _lib is not None:
+            return _lib
+        path = library_path()
+        if not os.path.exists(path):
+            raise RuntimeError(
+                f"CUDA backend not built: {path} is missing (run `python -c 'import __graft_entry__ as g; g.build()'`); "
+                "there is no CPU fallback"
+            )
+        lib = ctypes.CDLL(path)
+        vp, ci, i64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64
+        lib.pyopal_cuda_device_count.restype = ci
+        lib.pyopal_cuda_device_count.argtypes = []
+        lib.pyopal_cuda_device_info.restype = ci
+        lib.pyopal_cuda_device_info.argtypes = [ci, ctypes.c_char_p, ci, ctypes.POINTER(ci), _c_i64p]
+        lib.pyopal_cuda_last_error.restype = ctypes.c_char_p
+        lib.pyopal_cuda_last_error.argtypes = []
+        lib.pyopal_cuda_db_create.restype = ci
+        lib.pyopal_cuda_db_create.argtypes = [ci, vp, vp, vp, i64, ci, ctypes.POINTER(vp)]
+        lib.pyopal_cuda_db_create_from_pointers.restype = ci
+        lib.pyopal_cuda_db_create_from_pointers.argtypes = [ci, vp, vp, i64, ci, ctypes.POINTER(vp)]
+        lib.pyopal_cuda_db_destroy.restype = None
+        lib.pyopal_cuda_db_destroy.argtypes = [vp]
+        for name in ("pyopal_cuda_db_size", "pyopal_cuda_db_total_length", "pyopal_cuda_db_device_bytes"):
+            getattr(lib, name).restype = i64
+            getattr(lib, name).argtypes = [vp]
+        lib.pyopal_cuda_search.restype = ci
+        lib.pyopal_cuda_search.argtypes = [vp, vp, ci, ci, ci, vp, ci, ci, ci, ci, i64, i64] + [vp] * 8
+        lib.pyopal_cuda_search_scores_device.restype = ci
+        lib.pyopal_cuda_search_scores_device.argtypes = [vp, vp, ci, ci, ci, vp, ci, ci, i64, i64, vp, vp]
+        lib.pyopal_cuda_search_batch.restype = ci
+        lib.pyopal_cuda_search_batch.argtypes = [vp, vp, vp, vp, ci, ci, ci, vp, ci, ci, vp]
+        lib.pyopal_cuda_last_stats.restype = ci
+        lib.pyopal_cuda_last_stats.argtypes = [vp, _c_i64p, ci]
+        lib.pyopal_cuda_int_issue_rate.restype = ci
+        lib.pyopal_cuda_int_issue_rate.argtypes = [ci, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]
+        lib.opalSearchDatabase.restype = ci
+        lib.opalSearchDatabase.argtypes = [vp, ci, vp, ci, vp, ci, ci, vp, ci, vp, ci, ci, ci]
+        lib.opalInitSearchResult.restype = None
+        lib.opalInitSearchResult.argtypes = [ctypes.POINTER(OpalSearchResult)]
+        lib.opalSearchResultIsEmpty.restype = ci
+        lib.opalSearchResultIsEmpty.argtypes = [OpalSearchResult]
+        lib.opalSearchResultSetScore.restype = None
+        lib.opalSearchResultSetScore.argtypes = [ctypes.POINTER(OpalSearchResult), ci]
+        _lib = lib
+    return _lib
+
+
+def last_error():
+    msg = load_library().pyopal_cuda_last_error()
+    return msg.decode("utf-8", "replace") if msg else ""
+
+
+def check(retcode):
+    """Return-code -> exception mapping of pyx.in:102-107 (plus this backend's codes)."""
+    if retcode == 0:
+        return
+    detail = last_error()
+    if retcode == OPAL_ERR_NO_SIMD_SUPPORT:
+        raise RuntimeError("no supported CUDA device available" + (f" ({detail})" if detail else ""))
+    if retcode == OPAL_ERR_OVERFLOW:
+        raise OverflowError("overflow detected while computing alignment scores")
+    if retcode == PYOPAL_CUDA_ERR_NOMEM:
+        raise MemoryError(detail or "allocation failed in the CUDA backend")
+    raise RuntimeError(f"failed to align to Opal database (code={retcode})" + (f": {detail}" if detail else ""))
+
+
+def device_count():
+    return load_library().pyopal_cuda_device_count()
+
+
+def device_info(device=0):
+    lib = load_library()
+    name = ctypes.create_string_buffer(256)
+    sms = ctypes.c_int(0)
+    mem = ctypes.c_int64(0)
+    check(lib.pyopal_cuda_device_info(device, name, 256, ctypes.byref(sms), ctypes.byref(mem)))
+    return {"name": name.value.decode(), "sm_count": sms.value, "total_memory": mem.value}
+
+
+def default_device():
+    """Device of this process: ``PYOPAL_CUDA_DEVICE`` or ``LOCAL_RANK`` (one process per GPU), else 0."""
+    for var in ("PYOPAL_CUDA_DEVICE", "LOCAL_RANK"):
+        if os.environ.get(var, "").isdigit():
+            n = device_count()
+            return int(os.environ[var]) % n if n > 0 else 0
+    return 0
+
+
+def _addr(buf):
+    """Address of a bytes / bytearray / array.array / ctypes buffer without copying."""
+    if buf is None:
+        return None
+    if isinstance(buf, bytes):
+        return ctypes.cast(ctypes.c_char_p(buf), ctypes.c_void_p).value
+    if isinstance(buf, array.array):
+        return buf.buffer_info()[0]
+    if isinstance(buf, ctypes.Array):
+        return ctypes.addressof(buf)
+    if hasattr(buf, "ctypes"):  # numpy array (must be C-contiguous)
+        return buf.ctypes.data
+    return ctypes.addressof(ctypes.c_char.from_buffer(buf))
+
+
+class DeviceStore:
+    """Device-resident, length-sorted, pair-interleaved copy of a database.
+
+    Replaces, for the search, the per-sequence heap store of
+    /root/reference/src/pyopal/lib.pxd:95-98 (see include/pyopal_cuda.h).
+    """
+
+    def __init__(self, residues, offsets, lengths, alphabet_length, device=None):
+        lib = load_library()
+        self._lib = lib
+        self._handle = ctypes.c_void_p(None)
+        self.device = default_device() if device is None else device
+        n = len(lengths)
+        check(
+            lib.pyopal_cuda_db_create(
+                self.device, _addr(residues), _addr(offsets), _addr(lengths), n, alphabet_length,
+                ctypes.byref(self._handle),
+            )
+        )
+        self.size = n
+        self.alphabet_length = alphabet_length
+
+    @classmethod
+    def from_sequences(cls, sequences, alphabet_length, device=None):
+        """Build from a list of encoded ``bytes`` (one per target)."""
+        lengths = array.array("i", map(len, sequences))
+        offsets = array.array("q", [0]) * len(sequences)
+        total = 0
+        for i, n in enumerate(lengths):
+            offsets[i] = total
+            total += n
+        return cls(b"".join(sequences), offsets, lengths, alphabet_length, device)
+
+    def close(self):
+        if getattr(self, "_handle", None) is not None and self._handle:
+            self._lib.pyopal_cuda_db_destroy(self._handle)
+            self._handle = ctypes.c_void_p(None)
+
+    __del__ = close
+
+    @property
+    def handle(self):
+        return self._handle
+
+    def device_bytes(self):
+        return self._lib.pyopal_cuda_db_device_bytes(self._handle)
+
+    def stats(self):
+        buf = (ctypes.c_int64 * 12)()
+        check(self._lib.pyopal_cuda_last_stats(self._handle, buf, 12))
+        keys = ("launches", "targets16", "targets32", "escalated", "device_us", "G", "K", "passes",
+                "k32_us", "k16_us", "rescore_us", "profile_in_smem")
+        return dict(zip(keys, buf))
+
+    def search(self, query, gap_open, gap_extend, int_matrix, search_type, algorithm, overflow=OPAL_OVERFLOW_BUCKETS,
+               start=0, end=None, lengths=None):
+        """Run one query; returns arrays (scores, endQ, endT, startQ, startT, ops, ops_offsets, ops_len)."""
+        end = self.size if end is None or end > self.size else end
+        n = max(end - start, 0)
+        scores = array.array("i", bytes(4 * n))
+        eq = et = sq = st = ops = oo = ol = None
+        if search_type >= OPAL_SEARCH_SCORE_END:
+            eq = array.array("i", bytes(4 * n))
+            et = array.array("i", bytes(4 * n))
+        if search_type == OPAL_SEARCH_ALIGNMENT:
+            sq = array.array("i", bytes(4 * n))
+            st = array.array("i", bytes(4 * n))
+            ol = array.array("i", bytes(4 * n))
+            oo = array.array("q", bytes(8 * n))
+            total = 0
+            qn = len(query)
+            for k in range(n):
+                oo[k] = total
+                total += qn + lengths[start + k]
+            ops = bytearray(total + 1)
+        matrix = int_matrix if isinstance(int_matrix, array.array) else array.array("i", int_matrix)
+        alen = int(round(len(matrix) ** 0.5))
+        rc = self._lib.pyopal_cuda_search(
+            self._handle, _addr(query), len(query), gap_open, gap_extend, _addr(matrix), alen, search_type,
+            algorithm, overflow, start, end, _addr(scores), _addr(eq), _addr(et), _addr(sq), _addr(st),
+            _addr(ops), _addr(oo), _addr(ol),
+        )
+        check(rc)
+        return scores, eq, et, sq, st, ops, oo, ol
+
+    def search_scores_device(self, query, gap_open, gap_extend, int_matrix, algorithm, d_scores, stream=0,
+                             start=0, end=None):
+        """Enqueue a score search whose output stays on the device (``d_scores``: device pointer)."""
+        end = self.size if end is None or end > self.size else end
+        matrix = int_matrix if isinstance(int_matrix, array.array) else array.array("i", int_matrix)
+        alen = int(round(len(matrix) ** 0.5))
+        check(
+            self._lib.pyopal_cuda_search_scores_device(
+                self._handle, _addr(query), len(query), gap_open, gap_extend, _addr(matrix), alen, algorithm,
+                start, end, d_scores, stream,
+            )
+        )
+
+    def kernel_times(self):
+        """Resolve the per-kernel CUDA events of the last search (call after synchronising its stream)."""
+        return self.stats()
+
+    def search_batch(self, queries, gap_open, gap_extend, int_matrix, algorithm):
+        """Score-mode search of several encoded queries; returns one ``array('i')`` of nq*size scores."""
+        nq = len(queries)
+        ql = array.array("i", map(len, queries))
+        qo = array.array("q", bytes(8 * nq))
+        total = 0
+        for i, n in enumerate(ql):
+            qo[i] = total
+            total += n
+        scores = array.array("i", bytes(4 * nq * self.size))
+        matrix = int_matrix if isinstance(int_matrix, array.array) else array.array("i", int_matrix)
+        alen = int(round(len(matrix) ** 0.5))
+        blob = b"".join(queries)
+        check(
+            self._lib.pyopal_cuda_search_batch(
+                self._handle, _addr(blob), _addr(qo), _addr(ql), nq, gap_open, gap_extend, _addr(matrix), alen,
+                algorithm, _addr(scores),
+            )
+        )
+        return scores
+
+
+def _search_generic(encoded, sequences, lengths, mode, overflow, algorithm, gap_open, gap_extend, matrix, alen):
+    """Any ``BaseDatabase`` subclass: the C function with the reference's own signature (opal.pxd:40-54)."""
+    lib = load_library()
+    n = len(sequences)
+    results_raw = (OpalSearchResult * n)()
+    for r in results_raw:
+        lib.opalInitSearchResult(ctypes.byref(r))
+    ptrs = (ctypes.c_void_p * n)(*[ctypes.addressof(results_raw[i]) for i in range(n)])
+    seqs = (ctypes.c_void_p * n)(*[_addr(s) if len(s) else None for s in sequences])
+    lens = array.array("i", lengths)
+    rc = lib.opalSearchDatabase(
+        _addr(encoded), len(encoded), seqs, n, _addr(lens), gap_open, gap_extend, _addr(matrix), alen, ptrs,
+        mode, algorithm, overflow,
+    )
+    check(rc)
+    return results_raw
+
+
+def searchCUDA(encoded, database, mode, overflow, algorithm, gap_open, gap_extend, int_matrix, start=0, end=UINT32_MAX):
+    """``search${SIMD}`` of pyx.in:16-108 for the CUDA backend."""
+    from ..lib import ScoreResult, EndResult, FullResult, Database  # late: lib imports this module
+
+    if not isinstance(encoded, bytes):
+        raise TypeError("expected bytes for the encoded query")
+    matrix = int_matrix if isinstance(int_matrix, array.array) else array.array("i", int_matrix)
+    alen = int(len(matrix) ** 0.5)  # pyx.in:41
+    if mode == OPAL_SEARCH_SCORE:
+        result_type = ScoreResult
+    elif mode == OPAL_SEARCH_SCORE_END:
+        result_type = EndResult
+    elif mode == OPAL_SEARCH_ALIGNMENT:
+        result_type = FullResult
+    else:
+        raise ValueError("invalid search mode")
+
+    dbsize = database.get_size()
+    if end > dbsize:
+        end = dbsize
+    if start > end:  # the reference wraps around here; raise instead
+        raise IndexError("database slice start is past the end")
+    size = 0 if end == 0 else end - start  # pyx.in:62
+    if size == 0:
+        return []
+    qlen = len(encoded)
+    lengths = database.get_lengths()
+
+    if isinstance(database, Database):
+        store = database._device_store()
+        scores, eq, et, sq, st, ops, oo, ol = store.search(
+            encoded, gap_open, gap_extend, matrix, mode, algorithm, overflow, start, end, lengths
+        )
+    else:
+        sequences = database.get_sequences()
+        raw = _search_generic(
+            encoded, sequences[start:end], lengths[start:end], mode, overflow, algorithm, gap_open, gap_extend,
+            matrix, alen,
+        )
+        scores = [r.score for r in raw]
+        eq = [r.endLocationQuery for r in raw]
+        et = [r.endLocationTarget for r in raw]
+        sq = [r.startLocationQuery for r in raw]
+        st = [r.startLocationTarget for r in raw]
+        ol = [r.alignmentLength for r in raw]
+        oo = None
+        ops = [bytes(bytearray(r.alignment[: r.alignmentLength])) if r.alignmentLength else b"" for r in raw]
+        libc = ctypes.CDLL(None)
+        libc.free.argtypes = [ctypes.c_void_p]
+        for r in raw:
+            if r.alignment:
+                libc.free(ctypes.cast(r.alignment, ctypes.c_void_p))
+
+    new = result_type.__new__
+    results = [None] * size
+    if mode == OPAL_SEARCH_SCORE:
+        for i in range(size):
+            r = new(result_type)
+            r._target_index = start + i
+            r._score = scores[i]
+            results[i] = r
+    elif mode == OPAL_SEARCH_SCORE_END:
+        for i in range(size):
+            r = new(result_type)
+            r._target_index = start + i
+            r._score = scores[i]
+            r._query_end = eq[i]
+            r._target_end = et[i]
+            results[i] = r
+    else:
+        for i in range(size):
+            r = new(result_type)
+            r._target_index = start + i
+            r._score = scores[i]
+            r._query_end = eq[i]
+            r._target_end = et[i]
+            r._query_start = sq[i]
+            r._target_start = st[i]
+            r._query_length = qlen  # pyx.in:95-99
+            r._target_length = lengths[start + i]
+            if oo is None:
+                r._alignment = ops[i]
+            else:
+                r._alignment = bytes(ops[oo[i] : oo[i] + ol[i]])
+            results[i] = r
+    return results

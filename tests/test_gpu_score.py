@@ -1,0 +1,204 @@
+"""GPU parity: score mode through the C-ABI vs the oracle (bit-exact)."""
+
+import array
+
+import numpy as np
+import pytest
+
+import pyopal_b200 as pyopal
+import synthetic
+
+pytestmark = pytest.mark.gpu
+
+ALGOS = ("sw", "nw", "hw", "ov")
+
+
+def make_db(seqs, alphabet=None):
+    db = pyopal.Database.__new__(pyopal.Database)
+    db.alphabet = alphabet or pyopal.Alphabet()
+    db._sequences = list(seqs)
+    db._lengths = [len(s) for s in seqs]
+    return db
+
+
+def rand_seqs(seed, n, mu, sigma, lo, hi):
+    return synthetic.as_sequences(synthetic.database(seed, n, mu, sigma, lo, hi))
+
+
+def rand_query(seed, n):
+    return synthetic.random_residues(np.random.Generator(np.random.PCG64(seed)), n).tobytes()
+
+
+def check(oracle, aligner, query, seqs, algo, db=None, **kw):
+    db = db or make_db(seqs, aligner.alphabet)
+    got = list(aligner.align_scores(query_str(aligner, query), db, algorithm=algo, **kw))
+    s, e = kw.get("start", 0), min(kw.get("end", len(seqs)), len(seqs))
+    want = oracle.search(query, seqs[s:e], aligner._int_matrix, len(aligner.alphabet), aligner.gap_open,
+                         aligner.gap_extend, algo, "score", threads=8)["score"]
+    assert len(got) == len(want)
+    bad = [i for i, (a, b) in enumerate(zip(got, want)) if a != b]
+    assert not bad, f"{algo}: {len(bad)} mismatches, first {[(i, got[i], want[i], len(seqs[s + i])) for i in bad[:5]]}"
+    return db
+
+
+def query_str(aligner, encoded):
+    return aligner.alphabet.decode(encoded)
+
+
+def test_golden_vectors_through_api(cuda):
+    # /root/reference/src/pyopal/tests/test_aligner.py:42-60,93-111 and _align.py:106-111
+    aligner = pyopal.Aligner()
+    db = pyopal.Database(["AACCGCTG"])
+    assert aligner.align("ACCTCG", db, algorithm="nw")[0].score == 44
+    assert aligner.align("ACCTCG", db, algorithm="sw")[0].score == 47
+    assert isinstance(aligner.align("ACCTCG", db)[0], pyopal.ScoreResult)
+    targets = ["AACCGCTG", "ATGCGCT", "TTATTACG"]
+    res = list(pyopal.align("ACCTG", targets, gap_open=2, ordered=True))
+    assert [r.score for r in res] == [41, 31, 23]
+    assert [r.target_index for r in res] == [0, 1, 2]
+
+
+@pytest.mark.parametrize("algo", ALGOS)
+@pytest.mark.parametrize("lq", [1, 7, 33, 100, 300, 517])
+def test_random_db(cuda, oracle, algo, lq):
+    seqs = rand_seqs(100 + lq, 1500, 5.0, 0.7, 1, 4000)
+    aligner = pyopal.Aligner("BLOSUM62", 11, 1)
+    check(oracle, aligner, rand_query(lq, lq), seqs, algo)
+
+
+@pytest.mark.parametrize("algo", ALGOS)
+def test_default_scoring_low_gap_costs(cuda, oracle, algo):
+    # reference defaults BLOSUM50 / 3 / 1 (lib.pyx:1153-1155): higher scores, stresses the ladder
+    seqs = rand_seqs(21, 800, 5.3, 0.6, 1, 3000)
+    check(oracle, pyopal.Aligner(), rand_query(22, 250), seqs, algo)
+
+
+@pytest.mark.parametrize("algo", ALGOS)
+def test_multi_pass_long_query(cuda, oracle, algo):
+    # 1500 and 2900 rows need 2 and 3 passes of the widest tile (32 threads x 40 rows)
+    seqs = rand_seqs(31, 300, 5.5, 0.8, 1, 6000)
+    aligner = pyopal.Aligner("BLOSUM62", 11, 1)
+    for lq in (1500, 2900):
+        check(oracle, aligner, rand_query(lq, lq), seqs, algo)
+
+
+@pytest.mark.parametrize("algo", ALGOS)
+def test_empty_and_tiny_targets(cuda, oracle, algo):
+    seqs = [b"", b"\x00", b"\x01\x02", b"", rand_query(1, 50), b"\x05" * 3, b""] + rand_seqs(41, 40, 2.0, 0.8, 1, 30)
+    aligner = pyopal.Aligner("BLOSUM62", 11, 1)
+    for lq in (1, 5, 64):
+        check(oracle, aligner, rand_query(40 + lq, lq), seqs, algo)
+
+
+def test_sw_overflow_escalation(cuda, oracle):
+    # query = long mutated copies of targets => SW scores far above 32767: 16 -> 32 bit rescore
+    rng = np.random.Generator(np.random.PCG64(51))
+    base = [synthetic.random_residues(rng, n) for n in (9000, 7000, 8000)]
+    seqs = [b.tobytes() for b in base] + [synthetic.mutate(rng, base[0]).tobytes()] + rand_seqs(52, 200, 5.5, 0.6, 10, 2000)
+    aligner = pyopal.Aligner("BLOSUM62", 11, 1)
+    query = base[0][:8500].tobytes()
+    db = check(oracle, aligner, query, seqs, "sw")
+    st = db._device_store().stats()
+    assert st["escalated"] >= 2, st
+    got = list(aligner.align_scores(query_str(aligner, query), db))
+    assert max(got) > 32767
+
+
+@pytest.mark.parametrize("algo", ("nw", "hw", "ov"))
+def test_static_32bit_rung(cuda, oracle, algo):
+    # NW of a short query against 30k+ targets goes below -32768; long identical pairs go above +32767
+    rng = np.random.Generator(np.random.PCG64(61))
+    big = synthetic.random_residues(rng, 33000)
+    seqs = [big.tobytes(), synthetic.random_residues(rng, 31000).tobytes(), big[:6000].tobytes()] + rand_seqs(62, 100, 5.5, 0.6, 10, 2000)
+    aligner = pyopal.Aligner("BLOSUM62", 11, 1)
+    db = check(oracle, aligner, rand_query(63, 120), seqs, algo)
+    assert db._device_store().stats()["targets32"] >= 2
+    check(oracle, aligner, big[:5000].tobytes(), seqs, algo)
+
+
+def test_slices(cuda, oracle):
+    seqs = rand_seqs(71, 501, 5.0, 0.6, 1, 1500)
+    aligner = pyopal.Aligner("BLOSUM62", 11, 1)
+    q = rand_query(72, 90)
+    db = make_db(seqs, aligner.alphabet)
+    for s, e in ((0, 10), (3, 4), (250, 501), (100, 10_000), (7, 7)):
+        for algo in ("sw", "nw"):
+            check(oracle, aligner, q, seqs, algo, db=db, start=s, end=e)
+    res = aligner.align(query_str(aligner, q), db, start=5, end=9)
+    assert [r.target_index for r in res] == [5, 6, 7, 8]
+    with pytest.raises(IndexError):
+        aligner.align(query_str(aligner, q), db, start=9, end=5)
+
+
+def test_wide_scores_and_gaps(cuda, oracle):
+    # scores / gap costs outside the int8 profile: everything runs on the 32-bit wide-profile kernel
+    rows = [[(37 * i + 11 * j) % 400 - 150 if i != j else 300 for j in range(24)] for i in range(24)]
+    for i in range(24):
+        for j in range(i):
+            rows[i][j] = rows[j][i]
+    m = pyopal.ScoringMatrix(rows)
+    aligner = pyopal.Aligner(m, 200, 30)
+    seqs = rand_seqs(81, 200, 4.5, 0.6, 1, 800)
+    for algo in ALGOS:
+        check(oracle, aligner, rand_query(82, 77), seqs, algo)
+        check(oracle, aligner, rand_query(83, 1300), seqs, algo)
+
+
+def test_small_alphabet(cuda, oracle):
+    alphabet = pyopal.Alphabet("ACGT")
+    m = pyopal.ScoringMatrix([[5 if i == j else -4 for j in range(4)] for i in range(4)], "ACGT")
+    aligner = pyopal.Aligner(m, 10, 1)
+    rng = np.random.Generator(np.random.PCG64(91))
+    seqs = [rng.integers(0, 4, size=int(n), dtype=np.uint8).tobytes() for n in rng.integers(1, 900, size=300)]
+    q = rng.integers(0, 4, size=200, dtype=np.uint8).tobytes()
+    for algo in ALGOS:
+        check(oracle, aligner, q, seqs, algo, db=make_db(seqs, alphabet))
+
+
+def test_generic_entry_point_any_basedatabase(cuda, oracle):
+    """A foreign BaseDatabase subclass goes through opalSearchDatabase's own signature (opal.pxd:40-54)."""
+
+    class ListDatabase(pyopal.BaseDatabase):
+        def __init__(self, seqs, alphabet=None):
+            super().__init__(alphabet=alphabet)
+            self._seqs = list(seqs)
+
+        def get_sequences(self):
+            return self._seqs
+
+        def get_lengths(self):
+            return [len(s) for s in self._seqs]
+
+        def get_size(self):
+            return len(self._seqs)
+
+    seqs = rand_seqs(95, 64, 4.5, 0.6, 1, 600)
+    aligner = pyopal.Aligner("BLOSUM62", 11, 1)
+    q = rand_query(96, 80)
+    db = ListDatabase(seqs, aligner.alphabet)
+    for algo in ALGOS:
+        res = aligner.align(query_str(aligner, q), db, algorithm=algo)
+        want = oracle.search(q, seqs, aligner._int_matrix, 24, 11, 1, algo, "score")["score"]
+        assert [r.score for r in res] == want
+        assert [r.target_index for r in res] == list(range(len(seqs)))
+
+
+def test_batch_matches_single(cuda, oracle):
+    seqs = rand_seqs(97, 700, 5.0, 0.6, 1, 1500)
+    aligner = pyopal.Aligner("BLOSUM62", 11, 1)
+    db = make_db(seqs, aligner.alphabet)
+    queries = [rand_query(200 + i, n) for i, n in enumerate((50, 300, 1400, 9))]
+    rows = aligner.align_batch([query_str(aligner, q) for q in queries], db)
+    for q, row in zip(queries, rows):
+        assert list(row) == oracle.search(q, seqs, aligner._int_matrix, 24, 11, 1, "sw", "score", threads=8)["score"]
+
+
+def test_mutation_invalidates_device_store(cuda):
+    aligner = pyopal.Aligner()
+    db = pyopal.Database(["AACCGCTG"])
+    assert aligner.align("ACCTCG", db)[0].score == 47
+    db.append("ACCTCG")
+    res = aligner.align("ACCTCG", db)
+    assert len(res) == 2 and res[1].score == 5 + 13 + 13 + 5 + 13 + 8
+    db[0] = "TTTT"
+    assert aligner.align("ACCTCG", db)[0].score == 5
