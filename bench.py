@@ -135,44 +135,48 @@ def run_reference(args):
 
 
 class ClockSampler(threading.Thread):
-    def __init__(self, index):
+    """SM clock + throttle reasons of one GPU during the timed region, through NVML in-process
+    (a looping `nvidia-smi` process measurably perturbs the kernels it is watching)."""
+
+    def __init__(self, pci_bus_id, period=0.2):
         super().__init__(daemon=True)
-        self.index = index
+        self.pci = pci_bus_id
+        self.period = period
         self.samples = []
         self.reasons = set()
+        self.max_mhz = None
         self.stop_flag = threading.Event()
-        self.proc = None
 
     def run(self):
-        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
         try:
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i", str(self.index), "-lms", "100"],
-                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-        except OSError:
-            return
-        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
-        for line in self.proc.stdout:
-            if self.stop_flag.is_set():
-                break
-            parts = [p.strip() for p in line.split(",")]
-            try:
-                self.samples.append((float(parts[0]), float(parts[1])))
-            except (ValueError, IndexError):
-                continue
-            for nm, val in zip(names, parts[2:]):
-                if val.lower().startswith("active"):
-                    self.reasons.add(nm)
+            import pynvml as nv
+
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByPciBusId(self.pci.encode() if isinstance(self.pci, str) else self.pci)
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            masks = {
+                "hw_slowdown": nv.nvmlClocksThrottleReasonHwSlowdown,
+                "hw_thermal_slowdown": nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown,
+                "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap,
+            }
+            while not self.stop_flag.is_set():
+                self.samples.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                for name, m in masks.items():
+                    if r & m:
+                        self.reasons.add(name)
+                self.stop_flag.wait(self.period)
+        except Exception as err:  # NVML missing: report no clocks rather than die
+            self.error = repr(err)
 
     def finish(self):
         self.stop_flag.set()
-        if self.proc:
-            self.proc.terminate()
+        self.join(timeout=2)
         if not self.samples:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
-        sm = sorted(s[0] for s in self.samples)
-        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": self.samples[0][1], "reasons": sorted(self.reasons),
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "error": getattr(self, "error", None)}
+        sm = sorted(self.samples)
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
                 "samples": len(sm)}
 
 
@@ -268,9 +272,9 @@ def run_b200(args):
     for _ in range(args.warmup):
         step()
     barrier()
-    sampler = ClockSampler(local)
+    props = torch.cuda.get_device_properties(local)
+    sampler = ClockSampler("%08x:%02x:%02x.0" % (props.pci_domain_id, props.pci_bus_id, props.pci_device_id))
     sampler.start()
-    time.sleep(0.3)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()

@@ -139,8 +139,8 @@ int pyopal_cuda_search_batch(pyopal_cuda_db* db, const unsigned char* queries, c
  * at 32 bit (static), [3]=targets escalated 16->32 after overflow,
  * [4]=device time of the last search in microseconds (CUDA events),
  * [5]=threads per target group G, [6]=query rows per thread K, [7]=passes,
- * [8]/[9]/[10]=device microseconds of the 32-bit static kernel / the 16-bit
- * kernel / the 32-bit rescore kernel of the last search (0 until its stream
+ * [8]/[9]/[10]=device microseconds of the side stream (32-bit static + 16-bit
+ * tail kernels) / the 16-bit bulk kernel / the 32-bit rescore kernel of the last search (0 until its stream
  * has completed), [11]=1 if the query profile was held in shared memory. */
 int pyopal_cuda_last_stats(const pyopal_cuda_db* db, int64_t* stats, int n);
 

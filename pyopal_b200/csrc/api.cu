@@ -94,7 +94,9 @@ struct pyopal_cuda_db {
     DevBuf<uint8_t> query;
     DevBuf<int8_t> gprofile;
     DevBuf<int32_t> wprofile;
-    DevBuf<uint32_t> bndH, bndF;
+    DevBuf<uint32_t> bndH, bndF, bnd32H, bnd32F;
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int32_t* d_matrix = nullptr;  // 32*32
     int32_t* d_counts = nullptr;  // [0..2] list sizes, [4..6] task counters
     int64_t stats[12] = {0};
@@ -157,7 +159,10 @@ void pyopal_cuda_db_destroy(pyopal_cuda_db* db) {
     cudaFree(db->d_counts);
     db->wl16.release(); db->wl32.release(); db->ovf.release(); db->out.release(); db->fixes.release();
     db->query.release(); db->gprofile.release(); db->wprofile.release();
-    db->bndH.release(); db->bndF.release();
+    db->bndH.release(); db->bndF.release(); db->bnd32H.release(); db->bnd32F.release();
+    if (db->ev_fork) cudaEventDestroy(db->ev_fork);
+    if (db->ev_join) cudaEventDestroy(db->ev_join);
+    if (db->side) cudaStreamDestroy(db->side);
     for (int i = 0; i < 6; i++) if (db->kev[i]) cudaEventDestroy(db->kev[i]);
     if (db->ev0) cudaEventDestroy(db->ev0);
     if (db->ev1) cudaEventDestroy(db->ev1);
@@ -311,6 +316,14 @@ static int db_build(int device, GetSeq get_seq, const int32_t* lengths, int64_t 
     CU(cudaMalloc(&db->d_matrix, 32 * 32 * sizeof(int32_t)));
     CU(cudaMalloc(&db->d_counts, 16 * sizeof(int32_t)));
     CU(cudaStreamCreateWithFlags(&db->stream, cudaStreamNonBlocking));
+    {
+        // the side stream carries the longest targets: highest priority so its CTAs are placed first
+        int lo_prio = 0, hi_prio = 0;
+        CU(cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio));
+        CU(cudaStreamCreateWithPriority(&db->side, cudaStreamNonBlocking, hi_prio));
+    }
+    CU(cudaEventCreateWithFlags(&db->ev_fork, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&db->ev_join, cudaEventDisableTiming));
     CU(cudaEventCreate(&db->ev0));
     CU(cudaEventCreate(&db->ev1));
     for (int i = 0; i < 6; i++) CU(cudaEventCreate(&db->kev[i]));
@@ -344,6 +357,17 @@ struct Plan {
     size_t smem = 0;
 };
 
+Plan finish_plan(Plan p, int Lq, int A, size_t smem_limit) {
+    const int T = p.G * p.K;
+    p.npass = (Lq + T - 1) / T;
+    p.pitch = (p.npass * T + 15) / 16 * 16;
+    p.padtop = p.npass * T - Lq;
+    p.smem = (size_t)(A + 1) * (size_t)p.pitch;
+    p.psmem = p.smem <= smem_limit;
+    if (!p.psmem) p.smem = 0;
+    return p;
+}
+
 // Pick the tile (G threads x K rows) that minimises issue slots for this query
 // length and the store's mean target length.  Per column step a thread issues
 // about C0 instructions of bookkeeping plus C1 per row; a target of L columns
@@ -357,29 +381,31 @@ Plan make_plan(int Lq, int A, double mean_cols, size_t smem_limit) {
         for (int K = 4; K <= 40; K += 4) {
             const int T = G * K;
             const int npass = (Lq + T - 1) / T;
-            const double cost = (double)npass * (mean_cols + G - 1) * (C0 + C1 * K) * (double)G;
+            // several passes also pay the boundary round trip through L2 every step
+            const double cost = (double)npass * (mean_cols + G - 1) * (C0 + (npass > 1 ? 12.0 : 0.0) + C1 * K) * (double)G;
             if (cost < best_cost - 1e-9) {
                 best_cost = cost;
                 best.G = G; best.logG = logG; best.K = K; best.npass = npass;
             }
         }
     }
-    auto finish = [&](Plan& p) {
-        const int T = p.G * p.K;
-        p.pitch = (p.npass * T + 15) / 16 * 16;
-        p.padtop = p.npass * T - Lq;
-        p.smem = (size_t)(A + 1) * (size_t)p.pitch;
-    };
-    finish(best);
-    if (best.smem > smem_limit) {
-        // profile from global memory (L1/L2 resident); only K = 32 is built for it
-        best.G = 32; best.logG = 5; best.K = 32;
-        best.npass = (Lq + 1023) / 1024;
-        finish(best);
-        best.psmem = false;
-        best.smem = 0;
-    }
+    best = finish_plan(best, Lq, A, smem_limit);
     return best;
+}
+
+Plan make_forced_plan(int Lq) {
+    Plan p; p.G = 32; p.logG = 5; p.K = 32;
+    p = finish_plan(p, Lq, 0, 0);
+    p.psmem = false; p.smem = 0;
+    return p;
+}
+// Latency tile for the longest targets: a whole warp per pair and as few rows
+// per thread as one pass allows (the per-step critical path is ~12 cycles per
+// row); with several passes, deep tiles amortise the per-step latency better.
+Plan make_tail_plan(int Lq, int A, size_t smem_limit) {
+    Plan p; p.G = 32; p.logG = 5;
+    p.K = std::min(40, std::max(4, (Lq + 127) / 128 * 4));
+    return finish_plan(p, Lq, A, smem_limit);
 }
 
 struct Rung {
@@ -439,9 +465,8 @@ search_kernel_t pick_kernel(int K, int W, bool local, bool psmem) {
     return local ? get_search_kernel_w32_l1(K, psmem) : get_search_kernel_w32_l0(K, psmem);
 }
 
-int launch_search(pyopal_cuda_db* db, search_kernel_t fn, const KParams& P, size_t smem, int64_t max_tasks,
-                  cudaStream_t st) {
-    const int threads = 256;
+int launch_search(pyopal_cuda_db* db, search_kernel_t fn, const KParams& P, size_t smem, int threads,
+                  int64_t max_tasks, cudaStream_t st) {
     CU(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, threads, smem));
@@ -455,7 +480,20 @@ int launch_search(pyopal_cuda_db* db, search_kernel_t fn, const KParams& P, size
     return 0;
 }
 
+void apply_plan(KParams& P, const Plan& pl) {
+    P.G = pl.G; P.logG = pl.logG; P.npass = pl.npass; P.pitch = pl.pitch; P.padtop = pl.padtop;
+}
+
 // Enqueue a SCORE search of [start, end) on `st`; scores land in d_out (device).
+//
+// Up to four launches:
+//   bulk  : 16-bit rung, throughput tile (make_plan), 256-thread CTAs, on `st`
+//   tail  : 16-bit rung for the longest pairs, one warp per pair with the
+//           latency tile (32 threads x few rows), on the side stream
+//   wide32: 32-bit rung for pairs the 16-bit rung cannot hold exactly
+//           (NW/HW/OV static bound), latency tile, side stream
+//   rescue: 32-bit rescore of SW targets whose 16-bit running max overflowed;
+//           its work list is produced on the device by bulk/tail.
 int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq, int go, int ge,
                          const int* M, int A, int mode, int64_t start, int64_t end, int32_t* d_out,
                          cudaStream_t st) {
@@ -468,7 +506,6 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
     // host-side fix-ups: zero-length targets, or everything when the query is empty
     std::vector<int32_t> fixes;
     if (Lq == 0) {
-        // one value per target length; cheap enough to do on the host
         for (int64_t i = start; i < end; i++) {
             fixes.push_back((int32_t)(i - start));
             fixes.push_back(degenerate_score(mode, 0, db->h_lengths[(size_t)i], go, ge));
@@ -487,74 +524,110 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
         CU(cudaMemcpyAsync(db->fixes.p, fixes.data(), fixes.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
         scatter_fixes_kernel<<<(nfix + 255) / 256, 256, 0, st>>>(db->fixes.p, nfix, d_out);
         CU(cudaGetLastError());
-        CU(cudaStreamSynchronize(st));  // `fixes` is a stack vector
         return 0;
     };
     if (Lq == 0 || db->npairs == 0) return apply_fixes();
 
-    // plan
-    Plan plan = make_plan(Lq, A, db->mean_cols, (size_t)200 * 1024);
-    const int Lp = plan.npass * plan.G * plan.K;
+    // ---- plans -------------------------------------------------------------
+    const size_t SMEM_LIMIT = (size_t)200 * 1024;
+    Plan bulk = make_plan(Lq, A, db->mean_cols, SMEM_LIMIT);
+    Plan tail = make_tail_plan(Lq, A, SMEM_LIMIT);
+    int smax = INT_MIN, smin = INT_MAX;
+    for (int i = 0; i < A * A; i++) { smax = std::max(smax, M[i]); smin = std::min(smin, M[i]); }
+    const int Lp = std::max(bulk.npass * bulk.G * bulk.K, tail.npass * tail.G * tail.K);
     Rung rung = make_rung(M, A, go, ge, mode, Lp);
-    // 32-bit overflow cannot happen below this bound (scores are exact otherwise)
+    const bool wide = !rung.fits8;
+    if (wide || !bulk.psmem || !tail.psmem) {
+        // profile in global memory: one tile shape (32 x 32) for every launch
+        bulk = make_forced_plan(Lq);
+        tail = bulk;
+    }
     {
-        int64_t mag = std::max<int64_t>({(int64_t)go, (int64_t)ge, 1});
-        for (int i = 0; i < A * A; i++) mag = std::max<int64_t>(mag, std::llabs((long long)M[i]));
+        // 32-bit overflow cannot happen below this bound (scores are exact otherwise)
+        int64_t mag = std::max<int64_t>({(int64_t)go, (int64_t)ge, 1, std::llabs((long long)smax), std::llabs((long long)smin)});
         const int64_t longest = db->h_pair_len[0];
         if (mag * ((int64_t)Lp + longest + 8) >= (1LL << 29))
             return fail(OPAL_ERR_OVERFLOW, "scores may exceed the 32-bit range");
     }
+    const bool same_plan = (bulk.G == tail.G && bulk.K == tail.K && bulk.npass == tail.npass) ||
+                           getenv("PYOPAL_CUDA_NO_TAIL") != nullptr;
+    if (getenv("PYOPAL_CUDA_NO_TAIL")) tail = bulk;
 
-    // split the (length-sorted) pairs between the rungs
-    const bool whole = (start == 0 && end >= db->n);
-    int64_t n32pairs = 0;  // leading pairs (longest) that must run at 32 bit
-    if (!rung.ok16) n32pairs = db->npairs;
+    // ---- split the (length-sorted) pairs ------------------------------------
+    // [0, n32p): 32-bit static; [n32p, n32p + ntailp): 16-bit tail; rest: 16-bit bulk
+    int64_t n32p = 0;
+    if (!rung.ok16) n32p = db->npairs;
     else if (!local) {
-        // first pair whose column count fits the 16-bit rung (lengths are descending)
         int64_t lo = 0, hi = db->npairs;
         while (lo < hi) {
             int64_t mid = (lo + hi) / 2;
             if (db->h_pair_len[(size_t)(2 * mid)] > rung.max_cols16) lo = mid + 1; else hi = mid;
         }
-        n32pairs = lo;
+        n32p = lo;
     }
-    std::vector<int32_t> wl16, wl32;
-    const int32_t* d_wl16 = nullptr;
-    int64_t n16 = 0;
+    int64_t tail_end = n32p;
+    if (!same_plan) {
+        // a pair goes to the tail kernel when walking it alone in the bulk tile would
+        // take more than a quarter of the whole search at full machine throughput
+        const double C0 = 28.0, C1 = 6.5;
+        const double total_instr = (double)db->ncols * bulk.npass * bulk.G * (C0 + C1 * bulk.K);
+        const double ideal_cycles = total_instr / ((double)db->sm_count * 64.0);
+        const double step_latency = 12.0 * bulk.K + 80.0;
+        const double thr = std::max(256.0, ideal_cycles / 4.0 / (bulk.npass * step_latency));
+        int64_t lo = n32p, hi = db->npairs;
+        while (lo < hi) {
+            int64_t mid = (lo + hi) / 2;
+            if ((double)db->h_pair_len[(size_t)(2 * mid)] > thr) lo = mid + 1; else hi = mid;
+        }
+        tail_end = lo;
+    }
+    const bool whole = (start == 0 && end >= db->n);
     auto in_range = [&](int32_t idx) { return idx >= start && idx < end; };
-    for (int64_t k = 0; k < n32pairs; k++) {
+    auto pair_in_range = [&](int64_t k) {
+        return in_range(db->h_pair_idx[(size_t)(2 * k)]) ||
+               (db->h_pair_idx[(size_t)(2 * k + 1)] >= 0 && in_range(db->h_pair_idx[(size_t)(2 * k + 1)]));
+    };
+    std::vector<int32_t> wl32, wl16;
+    for (int64_t k = 0; k < n32p; k++) {
         if (in_range(db->h_pair_idx[(size_t)(2 * k)])) wl32.push_back((int32_t)(k << 1));
         if (db->h_pair_idx[(size_t)(2 * k + 1)] >= 0 && in_range(db->h_pair_idx[(size_t)(2 * k + 1)]))
             wl32.push_back((int32_t)((k << 1) | 1));
     }
+    const int32_t* d_wl_tail = nullptr;
+    const int32_t* d_wl_bulk = nullptr;
+    int64_t ntail = 0, nbulk = 0;
     if (whole) {
-        d_wl16 = db->d_identity + n32pairs;
-        n16 = db->npairs - n32pairs;
+        d_wl_tail = db->d_identity + n32p; ntail = tail_end - n32p;
+        d_wl_bulk = db->d_identity + tail_end; nbulk = db->npairs - tail_end;
     } else {
-        for (int64_t k = n32pairs; k < db->npairs; k++)
-            if (in_range(db->h_pair_idx[(size_t)(2 * k)]) ||
-                (db->h_pair_idx[(size_t)(2 * k + 1)] >= 0 && in_range(db->h_pair_idx[(size_t)(2 * k + 1)])))
-                wl16.push_back((int32_t)k);
-        n16 = (int64_t)wl16.size();
+        for (int64_t k = n32p; k < tail_end; k++) if (pair_in_range(k)) wl16.push_back((int32_t)k);
+        ntail = (int64_t)wl16.size();
+        for (int64_t k = tail_end; k < db->npairs; k++) if (pair_in_range(k)) wl16.push_back((int32_t)k);
+        nbulk = (int64_t)wl16.size() - ntail;
         if (db->wl16.reserve(wl16.size() + 1)) return PYOPAL_CUDA_ERR_NOMEM;
-        if (n16) CU(cudaMemcpyAsync(db->wl16.p, wl16.data(), wl16.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
-        d_wl16 = db->wl16.p;
+        if (!wl16.empty())
+            CU(cudaMemcpyAsync(db->wl16.p, wl16.data(), wl16.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+        d_wl_tail = db->wl16.p; d_wl_bulk = db->wl16.p + ntail;
     }
     const int64_t n32 = (int64_t)wl32.size();
     if (db->wl32.reserve(wl32.size() + 1)) return PYOPAL_CUDA_ERR_NOMEM;
     if (n32) CU(cudaMemcpyAsync(db->wl32.p, wl32.data(), wl32.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    const int64_t n16 = ntail + nbulk;
+    if (same_plan) { d_wl_bulk = d_wl_tail; nbulk = n16; ntail = 0; }
     if (local && n16 && db->ovf.reserve((size_t)(2 * n16))) return PYOPAL_CUDA_ERR_NOMEM;
 
-    // query, matrix, counters
+    // ---- query, matrix, counters, buffers ------------------------------------
     if (db->query.reserve((size_t)Lq)) return PYOPAL_CUDA_ERR_NOMEM;
     CU(cudaMemcpyAsync(db->query.p, query, (size_t)Lq, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(db->d_matrix, M, (size_t)A * A * sizeof(int32_t), cudaMemcpyHostToDevice, st));
     int32_t counts[16] = {0};
-    counts[0] = (int32_t)n16; counts[1] = (int32_t)n32; counts[2] = 0;
+    counts[0] = (int32_t)nbulk; counts[1] = (int32_t)n32; counts[2] = 0; counts[3] = (int32_t)ntail;
     CU(cudaMemcpyAsync(db->d_counts, counts, sizeof(counts), cudaMemcpyHostToDevice, st));
-    if (plan.npass > 1) {
-        const size_t need = (size_t)db->ncols * 2 + 16;
-        if (db->bndH.reserve(need) || db->bndF.reserve(need)) return PYOPAL_CUDA_ERR_NOMEM;
+    if (bulk.npass > 1 || tail.npass > 1) {
+        if (db->bndH.reserve((size_t)db->ncols + 16) || db->bndF.reserve((size_t)db->ncols + 16)) return PYOPAL_CUDA_ERR_NOMEM;
+        if (n32 > 0 || local)
+            if (db->bnd32H.reserve((size_t)db->ncols * 2 + 16) || db->bnd32F.reserve((size_t)db->ncols * 2 + 16))
+                return PYOPAL_CUDA_ERR_NOMEM;
     }
 
     KParams P;
@@ -562,78 +635,103 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
     P.stream = db->d_stream; P.pair_off = db->d_pair_off; P.pair_len = db->d_pair_len; P.pair_idx = db->d_pair_idx;
     P.query = db->query.p; P.matrix = db->d_matrix;
     P.Lq = Lq; P.A = A; P.go = go; P.ge = ge;
-    P.G = plan.G; P.logG = plan.logG; P.npass = plan.npass; P.pitch = plan.pitch; P.padtop = plan.padtop;
     P.mode = mode; P.pad_score = rung.pad_score; P.ovf_thresh = rung.ovf_thresh;
     P.out = d_out; P.out_start = start; P.out_end = end;
     P.ovf_list = db->ovf.p; P.ovf_count = db->d_counts + 2;
     P.bndH = db->bndH.p; P.bndF = db->bndF.p;
 
-    const bool wide = !rung.fits8;
     search_kernel_t k32 = nullptr;
     if (wide) {
-        // int32 profile in global memory; tile fixed at 32 x 32
-        Plan w; w.G = 32; w.logG = 5; w.K = 32; w.npass = (Lq + 1023) / 1024;
-        w.pitch = (w.npass * 1024 + 15) / 16 * 16; w.padtop = w.npass * 1024 - Lq; w.psmem = false; w.smem = 0;
-        plan = w;
-        P.G = 32; P.logG = 5; P.npass = w.npass; P.pitch = w.pitch; P.padtop = w.padtop;
-        if (w.npass > 1) {
-            const size_t need = (size_t)db->ncols * 2 + 16;
-            if (db->bndH.reserve(need) || db->bndF.reserve(need)) return PYOPAL_CUDA_ERR_NOMEM;
-            P.bndH = db->bndH.p; P.bndF = db->bndF.p;
-        }
-        if (db->wprofile.reserve((size_t)(A + 1) * w.pitch)) return PYOPAL_CUDA_ERR_NOMEM;
+        apply_plan(P, tail);
+        if (db->wprofile.reserve((size_t)(A + 1) * tail.pitch)) return PYOPAL_CUDA_ERR_NOMEM;
         P.wprofile = db->wprofile.p;
         build_profile_kernel<<<64, 256, 0, st>>>(P, nullptr, db->wprofile.p);
         CU(cudaGetLastError());
         k32 = get_search_kernel_wide(local);
     } else {
-        if (!plan.psmem) {
-            if (db->gprofile.reserve((size_t)(A + 1) * plan.pitch)) return PYOPAL_CUDA_ERR_NOMEM;
+        if (!tail.psmem) {
+            apply_plan(P, tail);
+            if (db->gprofile.reserve((size_t)(A + 1) * tail.pitch)) return PYOPAL_CUDA_ERR_NOMEM;
             P.gprofile = db->gprofile.p;
             build_profile_kernel<<<64, 256, 0, st>>>(P, db->gprofile.p, nullptr);
             CU(cudaGetLastError());
         }
-        k32 = pick_kernel(plan.K, 32, local, plan.psmem);
+        k32 = pick_kernel(tail.K, 32, local, tail.psmem);
     }
     if (!k32) return fail(PYOPAL_CUDA_ERR_INTERNAL, "no 32-bit kernel for this tile");
-    const int gpw = 32 >> plan.logG;
 
-    // 32-bit rung first: it holds the longest targets (tail latency)
+    // ---- side stream: longest targets first, concurrently with the bulk -------
+    const bool side_work = (n32 > 0) || (ntail > 0 && !same_plan);
+    cudaStream_t side = db->side;
+    if (side_work) {
+        CU(cudaEventRecord(db->ev_fork, st));
+        CU(cudaStreamWaitEvent(side, db->ev_fork, 0));
+        CU(cudaEventRecord(db->kev[0], side));
+    }
     if (n32 > 0) {
         KParams Q = P;
+        apply_plan(Q, tail);
         Q.worklist = db->wl32.p; Q.nwork = db->d_counts + 1; Q.counter = db->d_counts + 5;
         Q.neg = -(1 << 29);
-        CU(cudaEventRecord(db->kev[0], st));
-        int rc = launch_search(db, k32, Q, plan.smem, (n32 + gpw - 1) / gpw, st);
+        Q.bndH = db->bnd32H.p; Q.bndF = db->bnd32F.p;
+        int rc = launch_search(db, k32, Q, tail.smem, 32, n32, side);
         if (rc) return rc;
-        CU(cudaEventRecord(db->kev[1], st));
-        db->kev_valid[0] = true;
     }
-    if (n16 > 0) {
-        search_kernel_t k16 = pick_kernel(plan.K, 16, local, plan.psmem);
-        if (!k16) return fail(PYOPAL_CUDA_ERR_INTERNAL, "no 16-bit kernel for this tile");
+    if (ntail > 0 && !same_plan) {
+        search_kernel_t kt = pick_kernel(tail.K, 16, local, tail.psmem);
+        if (!kt) return fail(PYOPAL_CUDA_ERR_INTERNAL, "no 16-bit kernel for the tail tile");
         KParams Q = P;
-        Q.worklist = d_wl16; Q.nwork = db->d_counts + 0; Q.counter = db->d_counts + 4;
+        apply_plan(Q, tail);
+        Q.worklist = d_wl_tail; Q.nwork = db->d_counts + 3; Q.counter = db->d_counts + 7;
         Q.neg = rung.neg16;
-        CU(cudaEventRecord(db->kev[2], st));
-        int rc = launch_search(db, k16, Q, plan.smem, (n16 + gpw - 1) / gpw, st);
+        int rc = launch_search(db, kt, Q, tail.smem, 32, ntail, side);
         if (rc) return rc;
-        CU(cudaEventRecord(db->kev[3], st));
-        db->kev_valid[1] = true;
-        if (local) {
-            // rescore what overflowed; the list and its size live on the device
-            KParams R = P;
-            R.worklist = db->ovf.p; R.nwork = db->d_counts + 2; R.counter = db->d_counts + 6;
-            R.neg = -(1 << 29);
-            CU(cudaEventRecord(db->kev[4], st));
-            rc = launch_search(db, k32, R, plan.smem, std::min<int64_t>(2 * n16, (int64_t)db->sm_count * 64), st);
+    }
+    if (side_work) {
+        CU(cudaEventRecord(db->kev[1], side));
+        db->kev_valid[0] = true;
+        CU(cudaEventRecord(db->ev_join, side));
+    }
+
+    // ---- bulk -------------------------------------------------------------------
+    {
+        const int32_t* wl = d_wl_bulk;
+        const int64_t nw = nbulk;
+        if (nw > 0) {
+            search_kernel_t kb = pick_kernel(bulk.K, 16, local, bulk.psmem);
+            if (!kb) return fail(PYOPAL_CUDA_ERR_INTERNAL, "no 16-bit kernel for this tile");
+            KParams Q = P;
+            apply_plan(Q, bulk);
+            Q.worklist = wl; Q.nwork = db->d_counts + 0; Q.counter = db->d_counts + 4;
+            Q.neg = rung.neg16;
+            const int gpw = 32 >> bulk.logG;
+            // one CTA per SM when the profile is large: use the whole register file with 16 warps
+            // (with side-stream CTAs resident, 7-warp CTAs leave them registers: 2 x 224 x 128 < 64K)
+            const int threads = (bulk.smem > (size_t)110 * 1024) ? (side_work ? 480 : 512) : (side_work ? 224 : 256);
+            CU(cudaEventRecord(db->kev[2], st));
+            int rc = launch_search(db, kb, Q, bulk.smem, threads, (nw + gpw - 1) / gpw, st);
             if (rc) return rc;
-            CU(cudaEventRecord(db->kev[5], st));
-            db->kev_valid[2] = true;
+            CU(cudaEventRecord(db->kev[3], st));
+            db->kev_valid[1] = true;
         }
     }
+    if (side_work) CU(cudaStreamWaitEvent(st, db->ev_join, 0));
+
+    // ---- rescue: 32-bit rescore of what overflowed (list and size live on the device)
+    if (local && n16 > 0) {
+        KParams R = P;
+        apply_plan(R, tail);
+        R.worklist = db->ovf.p; R.nwork = db->d_counts + 2; R.counter = db->d_counts + 6;
+        R.neg = -(1 << 29);
+        R.bndH = db->bnd32H.p; R.bndF = db->bnd32F.p;
+        CU(cudaEventRecord(db->kev[4], st));
+        int rc = launch_search(db, k32, R, tail.smem, 32, std::min<int64_t>(2 * n16, (int64_t)db->sm_count * 4), st);
+        if (rc) return rc;
+        CU(cudaEventRecord(db->kev[5], st));
+        db->kev_valid[2] = true;
+    }
     db->stats[1] = n16 * 2; db->stats[2] = n32;
-    db->stats[5] = plan.G; db->stats[6] = plan.K; db->stats[7] = plan.npass; db->stats[11] = plan.psmem ? 1 : 0;
+    db->stats[5] = bulk.G; db->stats[6] = bulk.K; db->stats[7] = bulk.npass; db->stats[11] = bulk.psmem ? 1 : 0;
     return apply_fixes();
 }
 

@@ -137,12 +137,15 @@ __device__ __forceinline__ int widen_one(uint32_t x, int u) {
 }
 
 template <int K, int W, bool LOCAL, bool PSMEM, bool WIDE = false>
-__global__ void __launch_bounds__(256) search_kernel(const __grid_constant__ KParams P) {
+__global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KParams P) {
     static_assert(K % 4 == 0, "K must be a multiple of 4");
     static_assert(!WIDE || (W == 32 && !PSMEM), "wide profile: 32-bit rung, global memory only");
     typedef Val<W> V;
     typedef typename V::T val_t;
     extern __shared__ __align__(16) unsigned char smem_raw[];
+
+    const int nwork = *P.nwork;
+    if (nwork <= 0) return;  // e.g. the rescue launch when nothing overflowed
 
     const int8_t* prof;
     if (PSMEM) {
@@ -165,7 +168,6 @@ __global__ void __launch_bounds__(256) search_kernel(const __grid_constant__ KPa
     const int grp = lane >> P.logG;
     const int gpw = 32 >> P.logG;
     const int T = G * K;
-    const int nwork = *P.nwork;
     const int ntasks = (nwork + gpw - 1) / gpw;
     const bool top_free = (P.mode != MODE_NW);
     const bool left_free = (P.mode == MODE_OV || P.mode == MODE_SW);
@@ -213,24 +215,46 @@ __global__ void __launch_bounds__(256) search_kernel(const __grid_constant__ KPa
                 int hl = (left_free || qi < 0) ? 0 : -(P.go + qi * P.ge);
                 upGprev = V::splat(hl - P.go);
             }
+            // software pipeline: the residue pair and the pass boundary of step s+1 are
+            // fetched while step s computes
+            unsigned code_nx = 0;
+            val_t bG_nx = V::splat(0), bF_nx = NEG;
+            if (p == 0 && ncol > 0) {
+                code_nx = P.stream[off];
+                if (pass != 0) {
+                    const int64_t bi = (W == 16) ? off : (2 * off + half);
+                    bG_nx = (val_t)__ldcg(P.bndH + bi);
+                    bF_nx = (val_t)__ldcg(P.bndF + bi);
+                }
+            }
             for (int s = 0; s < nsteps; ++s) {
                 val_t upG = __shfl_up_sync(FULL, Gout, 1, G);
                 val_t upF = __shfl_up_sync(FULL, Fout, 1, G);
                 const int j = s - p;
                 const bool active = (j >= 0) && (j < ncol);
+                const unsigned code = code_nx;
                 if (p == 0) {
                     if (pass == 0) {
                         int ht = top_free ? 0 : -(P.go + j * P.ge);
                         upG = V::splat(ht - P.go);
                         upF = NEG;
-                    } else if (active) {
-                        const int64_t bi = (W == 16) ? (off + j) : (2 * (off + j) + half);
-                        upG = (val_t)__ldcg(P.bndH + bi);
-                        upF = (val_t)__ldcg(P.bndF + bi);
+                    } else {
+                        upG = bG_nx;
+                        upF = bF_nx;
+                    }
+                }
+                {
+                    const int jn = j + 1;
+                    if (jn >= 0 && jn < ncol) {
+                        code_nx = P.stream[off + jn];
+                        if (p == 0 && pass != 0) {
+                            const int64_t bi = (W == 16) ? (off + jn) : (2 * (off + jn) + half);
+                            bG_nx = (val_t)__ldcg(P.bndH + bi);
+                            bF_nx = (val_t)__ldcg(P.bndF + bi);
+                        }
                     }
                 }
                 if (active) {
-                    const unsigned code = P.stream[off + j];
                     const unsigned t0 = (W == 16) ? (code & 0xffu) : (half ? (code >> 8) : (code & 0xffu));
                     const unsigned t1 = code >> 8;
                     const int8_t* pa = prof + t0 * P.pitch + rowbase;

@@ -205,9 +205,10 @@ class DeviceStore:
         return cls(b"".join(sequences), offsets, lengths, alphabet_length, device)
 
     def close(self):
-        if getattr(self, "_handle", None) is not None and self._handle:
-            self._lib.pyopal_cuda_db_destroy(self._handle)
-            self._handle = ctypes.c_void_p(None)
+        handle = getattr(self, "_handle", None)
+        if handle:
+            self._handle = None
+            self._lib.pyopal_cuda_db_destroy(handle)
 
     __del__ = close
 
