@@ -232,7 +232,10 @@ def run_b200(args):
 
     n_mine = len(mine)
     n_pad = (n_all + world - 1) // world + 1
-    stream = torch.cuda.current_stream()
+    # a non-blocking stream of our own: on torch's legacy default stream the library's
+    # high-priority side stream (longest targets) does not overlap the bulk kernel
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
     d_scores = [torch.zeros(n_pad, dtype=torch.int32, device="cuda") for _ in qbytes]
     gathered = [torch.empty(world * n_pad, dtype=torch.int32, device="cuda") for _ in qbytes] if world > 1 else None
     # global index of every gathered slot -> un-permute on rank 0
