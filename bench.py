@@ -255,8 +255,9 @@ def run_b200(args):
     def step(collect=False):
         for qi, q in enumerate(qbytes):
             store.search_scores_device(q, GAP_OPEN, GAP_EXTEND, M, algo, d_scores[qi].data_ptr(), stream.cuda_stream)
+            # one query = one API call: wait for it like Aligner.align does before the next one is issued
+            stream.synchronize()
             if collect:
-                stream.synchronize()
                 st = store.stats()
                 launches[0] += st["launches"]
                 k16_us[0] += st["k16_us"]
