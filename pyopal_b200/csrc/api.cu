@@ -5,8 +5,7 @@
 // per-target results.  No PyTorch, no CPU fallback: without a CUDA device every
 // entry point fails with OPAL_ERR_NO_SIMD_SUPPORT (pyx.in:102-103 maps it to
 // RuntimeError, the same class the reference raises when no SIMD backend fits).
-#include "../../include/pyopal_cuda.h"
-#include "kernels.cuh"
+#include "store.h"
 
 #include <algorithm>
 #include <climits>
@@ -21,88 +20,13 @@
 using namespace pyopal;
 
 namespace {
-
 thread_local std::string g_err;
+}  // namespace
 
-int fail(int code, const std::string& msg) {
+int pyopal::fail(int code, const std::string& msg) {
     g_err = msg;
     return code;
 }
-
-#define CU(call)                                                                                   \
-    do {                                                                                           \
-        cudaError_t e_ = (call);                                                                   \
-        if (e_ != cudaSuccess) {                                                                   \
-            int code_ = (e_ == cudaErrorMemoryAllocation) ? PYOPAL_CUDA_ERR_NOMEM                  \
-                        : (e_ == cudaErrorNoDevice || e_ == cudaErrorInsufficientDriver)           \
-                            ? OPAL_ERR_NO_SIMD_SUPPORT                                             \
-                            : PYOPAL_CUDA_ERR_CUDA;                                                \
-            return fail(code_, std::string(#call) + ": " + cudaGetErrorString(e_));                \
-        }                                                                                          \
-    } while (0)
-
-template <typename T>
-struct DevBuf {
-    T* p = nullptr;
-    size_t cap = 0;
-    int reserve(size_t n) {
-        if (n <= cap) return 0;
-        if (p) cudaFree(p);
-        p = nullptr;
-        cap = 0;
-        size_t want = n + n / 4 + 64;
-        CU(cudaMalloc(&p, want * sizeof(T)));
-        cap = want;
-        return 0;
-    }
-    void release() {
-        if (p) cudaFree(p);
-        p = nullptr;
-        cap = 0;
-    }
-};
-
-constexpr int PAD_ALIGN_COLS = 8;  // pair streams start on 16-byte boundaries
-
-}  // namespace
-
-struct pyopal_cuda_db {
-    int device = 0;
-    int sm_count = 148;
-    int A = 0;
-    int64_t n = 0;          // sequences
-    int64_t total_len = 0;  // residues
-    int64_t npairs = 0;     // pairs of non-empty targets, sorted by len_a descending
-    int64_t ncols = 0;      // u16 entries in the stream
-    double mean_cols = 0;   // mean len_a
-    // host mirrors of the pair tables (worklists, rung eligibility, fix-ups)
-    std::vector<int64_t> h_pair_off;
-    std::vector<int32_t> h_pair_len, h_pair_idx;
-    std::vector<int32_t> h_lengths;   // database order
-    std::vector<int32_t> h_zero_idx;  // zero-length targets (closed form on the host)
-    // device store
-    uint16_t* d_stream = nullptr;
-    int64_t* d_pair_off = nullptr;
-    int32_t* d_pair_len = nullptr;
-    int32_t* d_pair_idx = nullptr;
-    int32_t* d_identity = nullptr;  // 0..npairs-1
-    // per-search workspace, serialised by `mu`
-    std::mutex mu;
-    cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    DevBuf<int32_t> wl16, wl32, ovf, out, fixes;
-    DevBuf<uint8_t> query;
-    DevBuf<int8_t> gprofile;
-    DevBuf<int32_t> wprofile;
-    DevBuf<uint32_t> bndH, bndF, bnd32H, bnd32F;
-    cudaStream_t side = nullptr;
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
-    int32_t* d_matrix = nullptr;  // 32*32
-    int32_t* d_counts = nullptr;  // [0..2] list sizes, [4..6] task counters
-    int64_t stats[12] = {0};
-    cudaEvent_t kev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // around k32 / k16 / rescore
-    bool kev_valid[3] = {false, false, false};
-};
 
 // ---------------------------------------------------------------------------
 extern "C" {
@@ -160,6 +84,7 @@ void pyopal_cuda_db_destroy(pyopal_cuda_db* db) {
     db->wl16.release(); db->wl32.release(); db->ovf.release(); db->out.release(); db->fixes.release();
     db->query.release(); db->gprofile.release(); db->wprofile.release();
     db->bndH.release(); db->bndF.release(); db->bnd32H.release(); db->bnd32F.release();
+    db->pd_i32.release(); db->pd_tb.release(); db->pd_ops.release(); db->pd_bnd.release(); db->pd_jobs.release();
     if (db->ev_fork) cudaEventDestroy(db->ev_fork);
     if (db->ev_join) cudaEventDestroy(db->ev_join);
     if (db->side) cudaStreamDestroy(db->side);
@@ -754,12 +679,6 @@ int check_search_args(pyopal_cuda_db* db, const unsigned char* query, int Lq, in
 
 // ---------------------------------------------------------------------------
 // Public search entry points
-
-// end / full modes (endloc.cu)
-int pyopal_end_full_search(pyopal_cuda_db* db, const unsigned char* query, int Lq, int go, int ge, const int* M,
-                           int A, int searchType, int mode, int64_t start, int64_t end, int32_t* scores,
-                           int32_t* endQ, int32_t* endT, int32_t* startQ, int32_t* startT, unsigned char* ops,
-                           const int64_t* ops_offsets, int32_t* ops_len);
 
 extern "C" int pyopal_cuda_search_scores_device(pyopal_cuda_db* db, const unsigned char* query, int queryLength,
                                                 int gapOpen, int gapExt, const int* scoreMatrix,

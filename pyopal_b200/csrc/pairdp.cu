@@ -1,0 +1,613 @@
+// pyopal_b200/csrc/pairdp.cu -- end-location and alignment (full) modes.
+//
+// Replaces what opalSearchDatabase does for searchType = OPAL_SEARCH_SCORE_END
+// and OPAL_SEARCH_ALIGNMENT (/root/reference/src/pyopal/opal.pxd:40-54,
+// lib.pyx:73-77, doc lib.pyx:1278-1282; result fields read back at
+// lib.pyx:783-1119).  Three device passes, all 32-bit, one warp per target:
+//
+//   forward : score + end cell (first maximum in the mode's examination
+//             order: SW column-major over all cells, HW last row, OV last row
+//             then last column, NW the corner);
+//   reverse : the same kernel on the reversed prefixes query[0..endQ],
+//             target[0..endT], anchored at the end cell (both borders
+//             penalised, no floor) -> start cell;
+//   fill    : global DP over the [start..end] rectangle writing one direction
+//             byte per cell, then one thread per target walks it backwards
+//             and emits the operations (M=0 D=1 I=2 X=3, lib.pyx:991-996).
+//
+// A warp holds 32*K consecutive query rows (K per lane) in registers and the
+// target streams through it as an anti-diagonal wavefront (two shuffles per
+// step); longer queries take several passes whose last row round-trips
+// through global memory.  Tie-breaks are those of oracle/opal_oracle.c.
+#include "store.h"
+
+#include <algorithm>
+#include <climits>
+#include <cstring>
+
+using namespace pyopal;
+
+namespace {
+
+enum : int { END_CORNER = 0, END_LASTROW = 1, END_LASTROW_LASTCOL = 2, END_ALL = 3 };
+constexpr int NEGV = -(1 << 29);
+
+struct PairJob {
+    int64_t tbase;   // first column of the target in the u16 stream
+    int64_t tb_off;  // fill: byte offset of this job's direction matrix
+    int32_t half;    // 0: low byte of each u16, 1: high byte
+    int32_t q0, qdir, m;  // DP row i    <-> query[q0 + qdir * i]
+    int32_t t0, tdir, n;  // DP column c <-> target[t0 + tdir * c]
+    int32_t expect;  // reverse / fill: the forward score
+    int32_t slot;    // where the results go
+    int32_t ops_end; // walk: one past the last byte of this job's ops slot
+};
+
+struct PairParams {
+    const uint16_t* stream;
+    const uint8_t* query;
+    const int32_t* matrix;
+    int A, go, ge;
+    const PairJob* jobs;
+    int njobs;
+    int32_t* counter;
+    int top_free, left_free, floor0, endrule, anchored;
+    int32_t* out_score;
+    int32_t* out_q;
+    int32_t* out_t;
+    int32_t* bndH;
+    int32_t* bndF;
+    uint8_t* tb;
+    int32_t* err;
+};
+
+__device__ __forceinline__ int border_val(int is_free, int k, int go, int ge) {
+    if (k < 0) return 0;
+    return is_free ? 0 : -(go + k * ge);
+}
+
+// (value desc, column asc, row asc)
+__device__ __forceinline__ bool better(int v, int c, int i, int bv, int bc, int bi) {
+    return v > bv || (v == bv && (c < bc || (c == bc && i < bi)));
+}
+
+// KIND 0: locate (forward / reverse); KIND 1: fill the direction matrix.
+template <int K, int KIND>
+__global__ void __launch_bounds__(128) pair_kernel(const __grid_constant__ PairParams P) {
+    static_assert(K % 4 == 0, "K must be a multiple of 4");
+    __shared__ int sS[32 * 32];
+    for (int x = threadIdx.x; x < P.A * P.A; x += blockDim.x) sS[x] = P.matrix[x];
+    __syncthreads();
+
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const int go = P.go, ge = P.ge;
+    constexpr int T = 32 * K;
+
+    for (;;) {
+        int task = 0;
+        if (lane == 0) task = atomicAdd(P.counter, 1);
+        task = __shfl_sync(FULL, task, 0);
+        if (task >= P.njobs) break;
+        const PairJob jb = P.jobs[task];
+        const int m = jb.m, n = jb.n;
+        if (m <= 0 || n <= 0) continue;
+        const uint8_t* tbytes = reinterpret_cast<const uint8_t*>(P.stream + jb.tbase) + jb.half;
+        const int64_t bbase = 2 * jb.tbase + jb.half;
+        const int npass = (m + T - 1) / T;
+        const int rr = (m - 1) - (npass - 1) * T;  // tile row of the last query row in the last pass
+        const int owner = rr / K, rl = rr % K;
+
+        // trackers
+        int gv = P.floor0 ? 0 : INT_MIN, gc = -1, gi = -1;              // END_ALL
+        int lv = INT_MIN, lc = -1;                                         // last row
+        int cv = INT_MIN, ci = -1;                                         // last column
+        if (P.anchored) lv = border_val(0, m - 1, go, ge);
+        int ncols = n;  // may shrink once the reverse pass has met `expect`
+        int corner = 0;
+
+        for (int pass = 0; pass < npass; ++pass) {
+            const int i0 = pass * T + lane * K;
+            const int nv = min(max(m - i0, 0), K);
+            int qa[K], Hl[K], El[K];
+#pragma unroll
+            for (int r = 0; r < K; ++r) {
+                const int i = i0 + r;
+                qa[r] = (r < nv) ? (int)P.query[jb.q0 + jb.qdir * i] * P.A : 0;
+                Hl[r] = border_val(P.left_free, i, go, ge);
+                El[r] = NEGV;
+            }
+            int Hd0 = border_val(P.left_free, i0 - 1, go, ge);
+            int Hout = 0, Fout = NEGV;
+            int pv = INT_MIN, pc = -1, pi = -1;
+            const bool last = (pass == npass - 1);
+            const bool own = last && (lane == owner);
+            int nsteps = ncols + 31;
+            uint32_t tbw[K / 4];
+
+            for (int s = 0; s < nsteps; ++s) {
+                int upH = __shfl_up_sync(FULL, Hout, 1);
+                int upF = __shfl_up_sync(FULL, Fout, 1);
+                const int c = s - lane;
+                const bool active = (c >= 0) && (c < ncols) && (nv > 0);
+                bool hit = false;
+                if (active) {
+                    if (lane == 0) {
+                        if (pass == 0) {
+                            upH = border_val(P.top_free, c, go, ge);
+                            upF = NEGV;
+                        } else {
+                            upH = __ldcg(P.bndH + bbase + 2 * (int64_t)c);
+                            upF = __ldcg(P.bndF + bbase + 2 * (int64_t)c);
+                        }
+                    }
+                    const int tl = tbytes[2 * (int64_t)(jb.t0 + jb.tdir * c)];
+                    int hd = Hd0, hu = upH, f = upF, hlast = 0;
+#pragma unroll
+                    for (int r = 0; r < K; ++r) {
+                        const int sc = sS[qa[r] + tl];
+                        const int ho = Hl[r] - go;
+                        const int e = max(El[r] - ge, ho);
+                        const int fo = hu - go;
+                        f = max(f - ge, fo);
+                        const int d = hd + sc;
+                        int h = max(d, max(e, f));
+                        if (KIND == 0) {
+                            if (P.floor0) h = max(h, 0);
+                            if (P.endrule == END_ALL) {
+                                if (r < nv && h > pv) { pv = h; pc = c; pi = i0 + r; }
+                            } else {
+                                if (r == rl) hlast = h;
+                                if (P.endrule == END_LASTROW_LASTCOL && c == n - 1 && r < nv && h > cv) {
+                                    cv = h; ci = i0 + r;
+                                }
+                            }
+                        } else {
+                            const uint32_t src = (h == d) ? 0u : (h == e) ? 1u : 2u;
+                            const uint32_t b = src | ((e == ho) ? 4u : 0u) | ((f == fo) ? 8u : 0u);
+                            if ((r & 3) == 0) tbw[r >> 2] = b;
+                            else tbw[r >> 2] |= b << (8 * (r & 3));
+                            if (r == rl) hlast = h;
+                        }
+                        hd = Hl[r];
+                        Hl[r] = h;
+                        El[r] = e;
+                        hu = h;
+                    }
+                    Hout = hu;
+                    Fout = f;
+                    Hd0 = upH;
+                    if (lane == 31 && !last) {
+                        __stcg(P.bndH + bbase + 2 * (int64_t)c, Hout);
+                        __stcg(P.bndF + bbase + 2 * (int64_t)c, Fout);
+                    }
+                    if (KIND == 0) {
+                        if (P.endrule == END_ALL) {
+                            hit = P.anchored && (pv == jb.expect);
+                        } else if (own) {
+                            if (P.endrule == END_CORNER) {
+                                if (c == n - 1) { lv = hlast; lc = c; }
+                            } else if (hlast > lv) {
+                                lv = hlast; lc = c;
+                            }
+                        }
+                    } else {
+                        uint32_t* col = reinterpret_cast<uint32_t*>(P.tb + jb.tb_off + (int64_t)c * ((m + 3) & ~3) + i0);
+#pragma unroll
+                        for (int w = 0; w < K / 4; ++w)
+                            if (4 * w < nv) col[w] = tbw[w];
+                        if (own && c == n - 1) corner = hlast;
+                    }
+                }
+                if (KIND == 0 && P.endrule == END_ALL && P.anchored) {
+                    // reverse pass: stop once every lane is past the first column that reached `expect`
+                    if (__any_sync(FULL, hit)) {
+                        int cm = hit ? pc : INT_MAX;
+                        for (int d = 16; d > 0; d >>= 1) cm = min(cm, __shfl_xor_sync(FULL, cm, d));
+                        if (cm + 1 < ncols) ncols = cm + 1;
+                        nsteps = min(nsteps, ncols + 31);
+                    }
+                }
+            }
+            if (KIND == 0 && P.endrule == END_ALL && better(pv, pc, pi, gv, gc, gi)) { gv = pv; gc = pc; gi = pi; }
+            __syncwarp();
+        }
+
+        if (KIND == 0) {
+            int score, rq, rt;
+            if (P.endrule == END_ALL) {
+                for (int d = 16; d > 0; d >>= 1) {
+                    const int ov = __shfl_xor_sync(FULL, gv, d), oc = __shfl_xor_sync(FULL, gc, d),
+                              oi = __shfl_xor_sync(FULL, gi, d);
+                    if (better(ov, oc, oi, gv, gc, gi)) { gv = ov; gc = oc; gi = oi; }
+                }
+                score = gv; rq = gi; rt = gc;
+            } else {
+                lv = __shfl_sync(FULL, lv, owner);
+                lc = __shfl_sync(FULL, lc, owner);
+                score = lv; rq = m - 1; rt = lc;
+                if (P.endrule == END_LASTROW_LASTCOL) {
+                    if (P.anchored) {
+                        const int tbv = border_val(0, n - 1, go, ge);
+                        if (tbv > score) { score = tbv; rq = -1; rt = n - 1; }
+                    }
+                    for (int d = 16; d > 0; d >>= 1) {
+                        const int ov = __shfl_xor_sync(FULL, cv, d), oi = __shfl_xor_sync(FULL, ci, d);
+                        if (ov > cv || (ov == cv && oi < ci)) { cv = ov; ci = oi; }
+                    }
+                    if (cv > score) { score = cv; rq = ci; rt = n - 1; }
+                }
+            }
+            if (lane == 0) {
+                P.out_score[jb.slot] = score;
+                P.out_q[jb.slot] = rq;
+                P.out_t[jb.slot] = rt;
+            }
+        } else {
+            corner = __shfl_sync(FULL, corner, owner);
+            if (lane == 0 && corner != jb.expect) atomicExch(P.err, 1 + jb.slot);
+        }
+    }
+}
+
+// One thread per job: walk the direction matrix backwards from the corner
+// (oracle/opal_oracle.c traceback()): at an H cell the diagonal wins over the
+// horizontal gap (E, OPAL_ALIGN_INS) which wins over the vertical gap (F,
+// OPAL_ALIGN_DEL); inside a gap, closing it wins over extending it.  The
+// operations are written backwards from the end of the job's slot.
+__global__ void walk_kernel(const PairParams P, uint8_t* ops, int32_t* ops_len) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= P.njobs) return;
+    const PairJob jb = P.jobs[x];
+    const int m = jb.m, n = jb.n;
+    const int64_t mpad = (m + 3) & ~3;
+    const uint8_t* tbytes = reinterpret_cast<const uint8_t*>(P.stream + jb.tbase) + jb.half;
+    const uint8_t* tb = P.tb + jb.tb_off;
+    uint8_t* w = ops + jb.ops_end;
+    int i = m - 1, j = n - 1, state = 0, len = 0;
+    while (i >= 0 && j >= 0) {
+        const unsigned b = tb[(int64_t)j * mpad + i];
+        if (state == 0) {
+            const unsigned src = b & 3u;
+            if (src == 0) {
+                const bool same = P.query[jb.q0 + i] == tbytes[2 * (int64_t)(jb.t0 + j)];
+                *--w = same ? OPAL_ALIGN_MATCH : OPAL_ALIGN_MISMATCH;
+                ++len; --i; --j;
+            } else {
+                state = (int)src;
+            }
+        } else if (state == 1) {
+            *--w = OPAL_ALIGN_INS;
+            ++len;
+            state = (b & 4u) ? 0 : 1;
+            --j;
+        } else {
+            *--w = OPAL_ALIGN_DEL;
+            ++len;
+            state = (b & 8u) ? 0 : 2;
+            --i;
+        }
+    }
+    for (; j >= 0; --j) { *--w = OPAL_ALIGN_INS; ++len; }
+    for (; i >= 0; --i) { *--w = OPAL_ALIGN_DEL; ++len; }
+    ops_len[jb.slot] = len;
+}
+
+// forward jobs straight from the store's tables: job x = sorted position x
+// (longest targets first), skipped (m = 0) when outside [start, end)
+__global__ void make_forward_jobs(PairJob* jobs, int njobs, const int64_t* pair_off, const int32_t* pair_len,
+                                  const int32_t* pair_idx, int Lq, int64_t start, int64_t end) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= njobs) return;
+    PairJob jb;
+    const int idx = pair_idx[x];
+    jb.tbase = pair_off[x >> 1];
+    jb.tb_off = 0;
+    jb.half = x & 1;
+    jb.q0 = 0; jb.qdir = 1; jb.m = Lq;
+    jb.t0 = 0; jb.tdir = 1; jb.n = pair_len[x];
+    jb.expect = 0;
+    jb.slot = 0;
+    jb.ops_end = 0;
+    if (idx < start || idx >= end) jb.m = 0;
+    else jb.slot = (int)(idx - start);
+    jobs[x] = jb;
+}
+
+// reverse jobs from the forward results (database order, relative to start)
+__global__ void make_reverse_jobs(PairJob* jobs, int njobs, const int32_t* score, const int32_t* eq, const int32_t* et) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= njobs) return;
+    PairJob jb = jobs[x];
+    if (jb.m > 0) {
+        const int q = eq[jb.slot], t = et[jb.slot];
+        if (q < 0 || t < 0) {
+            jb.m = 0;
+        } else {
+            jb.q0 = q; jb.qdir = -1; jb.m = q + 1;
+            jb.t0 = t; jb.tdir = -1; jb.n = t + 1;
+            jb.expect = score[jb.slot];
+        }
+    }
+    jobs[x] = jb;
+}
+
+__global__ void fill_i32(int32_t* p, int64_t n, int32_t v) {
+    for (int64_t x = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; x < n; x += (int64_t)gridDim.x * blockDim.x) p[x] = v;
+}
+
+typedef void (*pair_kernel_t)(const PairParams);
+
+template <int KIND>
+pair_kernel_t pick_pair_kernel(int rows, int* K) {
+    if (rows <= 128) { *K = 4; return pair_kernel<4, KIND>; }
+    if (rows <= 256) { *K = 8; return pair_kernel<8, KIND>; }
+    if (rows <= 512) { *K = 16; return pair_kernel<16, KIND>; }
+    *K = 32;
+    return pair_kernel<32, KIND>;
+}
+
+int launch_pair(pyopal_cuda_db* db, pair_kernel_t fn, const PairParams& P, cudaStream_t st) {
+    if (P.njobs <= 0) return 0;
+    CU(cudaMemsetAsync(P.counter, 0, sizeof(int32_t), st));
+    int per_sm = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 128, 0));
+    if (per_sm < 1) return fail(PYOPAL_CUDA_ERR_INTERNAL, "pair kernel does not fit on an SM");
+    int64_t grid = std::min<int64_t>((int64_t)db->sm_count * per_sm, ((int64_t)P.njobs + 3) / 4);
+    fn<<<(unsigned)std::max<int64_t>(grid, 1), 128, 0, st>>>(P);
+    CU(cudaGetLastError());
+    db->stats[0]++;
+    return 0;
+}
+
+struct ModeCfg {
+    int top_free, left_free, floor0, endrule;
+};
+ModeCfg cfg_for_mode(int mode) {
+    switch (mode) {
+        case MODE_NW: return {0, 0, 0, END_CORNER};
+        case MODE_HW: return {1, 0, 0, END_LASTROW};
+        case MODE_OV: return {1, 1, 0, END_LASTROW_LASTCOL};
+        default: return {1, 1, 1, END_ALL};
+    }
+}
+
+// closed forms for an empty query / empty target (oracle/opal_oracle.c dp_end, m == 0 || n == 0)
+void degenerate_end(int mode, int m, int n, int go, int ge, int* score, int* eq, int* et) {
+    *eq = -1; *et = -1; *score = 0;
+    if (mode == MODE_NW) {
+        if (!(m == 0 && n == 0)) *score = -(go + (std::max(m, n) - 1) * ge);
+        *eq = m - 1; *et = n - 1;
+    } else if (mode == MODE_HW) {
+        *score = (m == 0) ? 0 : -(go + (m - 1) * ge);
+        *eq = m - 1; *et = -1;
+    }
+}
+
+}  // namespace
+
+int pyopal_end_full_search(pyopal_cuda_db* db, const unsigned char* query, int Lq, int go, int ge, const int* M,
+                           int A, int searchType, int mode, int64_t start, int64_t end, int32_t* scores,
+                           int32_t* endQ, int32_t* endT, int32_t* startQ, int32_t* startT, unsigned char* ops,
+                           const int64_t* ops_offsets, int32_t* ops_len) {
+    const int64_t nout = end - start;
+    if (nout <= 0) return 0;
+    const bool full = (searchType == OPAL_SEARCH_ALIGNMENT);
+    if (!endQ || !endT) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null end-location output");
+    if (full && (!startQ || !startT || !ops || !ops_offsets || !ops_len))
+        return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null alignment output");
+    for (int i = 0; i < 12; i++) db->stats[i] = 0;
+    cudaStream_t st = db->stream;
+    CU(cudaEventRecord(db->ev0, st));
+
+    // 32-bit overflow cannot happen below this bound (values stay exact otherwise)
+    {
+        int smax = INT_MIN, smin = INT_MAX;
+        for (int i = 0; i < A * A; i++) { smax = std::max(smax, M[i]); smin = std::min(smin, M[i]); }
+        const int64_t mag = std::max<int64_t>({(int64_t)go, (int64_t)ge, 1, std::llabs((long long)smax), std::llabs((long long)smin)});
+        const int64_t longest = db->npairs ? db->h_pair_len[0] : 0;
+        if (mag * ((int64_t)Lq + longest + 40) >= (1LL << 29))
+            return fail(OPAL_ERR_OVERFLOW, "scores may exceed the 32-bit range");
+    }
+
+    std::vector<int32_t> h_sc((size_t)nout), h_eq((size_t)nout, -1), h_et((size_t)nout, -1);
+    std::vector<int32_t> h_sq((size_t)nout, -1), h_st((size_t)nout, -1), h_rs((size_t)nout, 0);
+    const int njobs = (int)(2 * db->npairs);
+    const bool device_work = (Lq > 0 && njobs > 0);
+    int32_t* d_res = nullptr;  // [score | eq | et | rscore | rq | rt] x nout, then counter, err
+    PairJob* d_jobs = nullptr;
+    PairParams P;
+    memset(&P, 0, sizeof(P));
+
+    if (device_work) {
+        if (db->pd_i32.reserve((size_t)nout * 6 + 16)) return PYOPAL_CUDA_ERR_NOMEM;
+        if (db->pd_jobs.reserve((size_t)njobs * sizeof(PairJob))) return PYOPAL_CUDA_ERR_NOMEM;
+        if (db->query.reserve((size_t)Lq)) return PYOPAL_CUDA_ERR_NOMEM;
+        d_res = db->pd_i32.p;
+        d_jobs = reinterpret_cast<PairJob*>(db->pd_jobs.p);
+        int K = 4;
+        pair_kernel_t kloc = pick_pair_kernel<0>(Lq, &K);
+        if (Lq > 32 * K) {
+            if (db->bnd32H.reserve((size_t)db->ncols * 2 + 16) || db->bnd32F.reserve((size_t)db->ncols * 2 + 16))
+                return PYOPAL_CUDA_ERR_NOMEM;
+        }
+        CU(cudaMemcpyAsync(db->query.p, query, (size_t)Lq, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(db->d_matrix, M, (size_t)A * A * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+        int32_t* d_ctl = d_res + (size_t)nout * 6;
+        CU(cudaMemsetAsync(d_ctl, 0, 16 * sizeof(int32_t), st));
+        fill_i32<<<256, 256, 0, st>>>(d_res, nout * 6, -1);
+        const int tpb = 256;
+        make_forward_jobs<<<(njobs + tpb - 1) / tpb, tpb, 0, st>>>(d_jobs, njobs, db->d_pair_off, db->d_pair_len,
+                                                                  db->d_pair_idx, Lq, start, end);
+        CU(cudaGetLastError());
+        P.stream = db->d_stream; P.query = db->query.p; P.matrix = db->d_matrix;
+        P.A = A; P.go = go; P.ge = ge;
+        P.jobs = d_jobs; P.njobs = njobs; P.counter = d_ctl; P.err = d_ctl + 1;
+        P.bndH = reinterpret_cast<int32_t*>(db->bnd32H.p); P.bndF = reinterpret_cast<int32_t*>(db->bnd32F.p);
+        const ModeCfg c = cfg_for_mode(mode);
+        P.top_free = c.top_free; P.left_free = c.left_free; P.floor0 = c.floor0; P.endrule = c.endrule; P.anchored = 0;
+        P.out_score = d_res; P.out_q = d_res + nout; P.out_t = d_res + 2 * nout;
+        int rc = launch_pair(db, kloc, P, st);
+        if (rc) return rc;
+        if (full && mode != MODE_NW) {
+            make_reverse_jobs<<<(njobs + tpb - 1) / tpb, tpb, 0, st>>>(d_jobs, njobs, d_res, d_res + nout, d_res + 2 * nout);
+            CU(cudaGetLastError());
+            PairParams R = P;
+            R.top_free = 0; R.left_free = 0; R.floor0 = 0; R.anchored = 1;
+            R.out_score = d_res + 3 * nout; R.out_q = d_res + 4 * nout; R.out_t = d_res + 5 * nout;
+            rc = launch_pair(db, kloc, R, st);
+            if (rc) return rc;
+        }
+        CU(cudaMemcpyAsync(h_sc.data(), d_res, (size_t)nout * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(h_eq.data(), d_res + nout, (size_t)nout * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(h_et.data(), d_res + 2 * nout, (size_t)nout * 4, cudaMemcpyDeviceToHost, st));
+        if (full && mode != MODE_NW) {
+            CU(cudaMemcpyAsync(h_rs.data(), d_res + 3 * nout, (size_t)nout * 4, cudaMemcpyDeviceToHost, st));
+            CU(cudaMemcpyAsync(h_sq.data(), d_res + 4 * nout, (size_t)nout * 4, cudaMemcpyDeviceToHost, st));
+            CU(cudaMemcpyAsync(h_st.data(), d_res + 5 * nout, (size_t)nout * 4, cudaMemcpyDeviceToHost, st));
+        }
+        CU(cudaStreamSynchronize(st));
+    }
+    // degenerate targets (empty query or empty target): closed forms
+    for (int64_t k = 0; k < nout; k++) {
+        const int n = db->h_lengths[(size_t)(start + k)];
+        if (Lq == 0 || n == 0) {
+            int s, q, t;
+            degenerate_end(mode, Lq, n, go, ge, &s, &q, &t);
+            h_sc[(size_t)k] = s; h_eq[(size_t)k] = q; h_et[(size_t)k] = t;
+        }
+    }
+    for (int64_t k = 0; k < nout; k++) {
+        scores[k] = h_sc[(size_t)k];
+        endQ[k] = h_eq[(size_t)k];
+        endT[k] = h_et[(size_t)k];
+    }
+    if (!full) {
+        CU(cudaEventRecord(db->ev1, st));
+        CU(cudaEventSynchronize(db->ev1));
+        float ms = 0;
+        CU(cudaEventElapsedTime(&ms, db->ev0, db->ev1));
+        db->stats[4] = (int64_t)(ms * 1000.0f);
+        return 0;
+    }
+
+    // ---- start cells -----------------------------------------------------------
+    struct Todo { int64_t k; int sq, stt, m, n; };
+    std::vector<Todo> todo;
+    for (int64_t k = 0; k < nout; k++) {
+        const int eq = h_eq[(size_t)k], et = h_et[(size_t)k];
+        ops_len[k] = 0;
+        startQ[k] = -1; startT[k] = -1;
+        if (eq < 0 || et < 0) continue;  // SW score 0 / degenerate: no alignment
+        int sq = 0, stt = 0;
+        if (mode != MODE_NW) {
+            if (h_rs[(size_t)k] != h_sc[(size_t)k])
+                return fail(PYOPAL_CUDA_ERR_INTERNAL, "reverse pass does not reproduce the forward score");
+            sq = eq - h_sq[(size_t)k];
+            stt = et - h_st[(size_t)k];
+        }
+        startQ[k] = sq; startT[k] = stt;
+        if (sq > eq || stt > et) {
+            // the alignment is a single gap (oracle/opal_oracle.c search_one)
+            int len = (sq > eq) ? (et - stt + 1) : (eq - sq + 1);
+            if (sq > eq && stt > et) len = 0;
+            memset(ops + ops_offsets[k], (sq > eq) ? OPAL_ALIGN_INS : OPAL_ALIGN_DEL, (size_t)std::max(len, 0));
+            ops_len[k] = std::max(len, 0);
+            continue;
+        }
+        todo.push_back({k, sq, stt, eq - sq + 1, et - stt + 1});
+    }
+
+    // ---- direction matrices + walk, in batches bounded by device memory ----------
+    size_t free_b = 0, total_b = 0;
+    CU(cudaMemGetInfo(&free_b, &total_b));
+    const int64_t budget = std::max<int64_t>((int64_t)1 << 28, std::min<int64_t>((int64_t)(free_b / 2), (int64_t)8 << 30));
+    std::vector<int32_t> where;  // database index -> sorted position, built lazily
+    where.assign((size_t)db->n, -1);
+    for (size_t x = 0; x < db->h_pair_idx.size(); x++)
+        if (db->h_pair_idx[x] >= 0) where[(size_t)db->h_pair_idx[x]] = (int32_t)x;
+    // big rectangles first so that the dynamic scheduler starts them early
+    std::stable_sort(todo.begin(), todo.end(), [](const Todo& a, const Todo& b) {
+        return (int64_t)a.m * a.n > (int64_t)b.m * b.n;
+    });
+    size_t pos = 0;
+    std::vector<PairJob> hjobs;
+    std::vector<int32_t> hlen;
+    std::vector<unsigned char> hops;
+    while (pos < todo.size()) {
+        hjobs.clear();
+        int64_t tb_bytes = 0, ops_bytes = 0;
+        int maxm = 0;
+        size_t p2 = pos;
+        while (p2 < todo.size()) {
+            const Todo& t = todo[p2];
+            const int64_t need = (int64_t)((t.m + 3) & ~3) * t.n;
+            if (!hjobs.empty() && (tb_bytes + need > budget || hjobs.size() >= (size_t)1 << 22)) break;
+            if (need > (int64_t)free_b - ((int64_t)1 << 28))
+                return fail(PYOPAL_CUDA_ERR_NOMEM, "alignment matrix of one target does not fit in device memory");
+            const int32_t x = where[(size_t)(start + t.k)];
+            PairJob jb;
+            jb.tbase = db->h_pair_off[(size_t)(x >> 1)];
+            jb.tb_off = tb_bytes;
+            jb.half = x & 1;
+            jb.q0 = t.sq; jb.qdir = 1; jb.m = t.m;
+            jb.t0 = t.stt; jb.tdir = 1; jb.n = t.n;
+            jb.expect = h_sc[(size_t)t.k];
+            jb.slot = (int32_t)hjobs.size();
+            ops_bytes += t.m + t.n;
+            if (ops_bytes > INT32_MAX - 16) { if (hjobs.empty()) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "alignment too long"); break; }
+            jb.ops_end = (int32_t)ops_bytes;
+            hjobs.push_back(jb);
+            tb_bytes += need;
+            maxm = std::max(maxm, t.m);
+            p2++;
+        }
+        const int nb = (int)hjobs.size();
+        if (db->pd_jobs.reserve((size_t)nb * sizeof(PairJob)) || db->pd_tb.reserve((size_t)tb_bytes + 16) ||
+            db->pd_ops.reserve((size_t)ops_bytes + 16) || db->pd_i32.reserve((size_t)nb + 16))
+            return PYOPAL_CUDA_ERR_NOMEM;
+        d_jobs = reinterpret_cast<PairJob*>(db->pd_jobs.p);
+        int32_t* d_len = db->pd_i32.p;
+        int32_t* d_ctl = d_len + nb;
+        int K = 4;
+        pair_kernel_t kfill = pick_pair_kernel<1>(maxm, &K);
+        if (maxm > 32 * K)
+            if (db->bnd32H.reserve((size_t)db->ncols * 2 + 16) || db->bnd32F.reserve((size_t)db->ncols * 2 + 16))
+                return PYOPAL_CUDA_ERR_NOMEM;
+        CU(cudaMemcpyAsync(d_jobs, hjobs.data(), (size_t)nb * sizeof(PairJob), cudaMemcpyHostToDevice, st));
+        CU(cudaMemsetAsync(d_ctl, 0, 16 * sizeof(int32_t), st));
+        PairParams F = P;
+        F.stream = db->d_stream; F.query = db->query.p; F.matrix = db->d_matrix;
+        F.A = A; F.go = go; F.ge = ge;
+        F.jobs = d_jobs; F.njobs = nb; F.counter = d_ctl; F.err = d_ctl + 1;
+        F.bndH = reinterpret_cast<int32_t*>(db->bnd32H.p); F.bndF = reinterpret_cast<int32_t*>(db->bnd32F.p);
+        F.top_free = 0; F.left_free = 0; F.floor0 = 0; F.endrule = END_CORNER; F.anchored = 0;
+        F.tb = db->pd_tb.p;
+        int rc = launch_pair(db, kfill, F, st);
+        if (rc) return rc;
+        walk_kernel<<<(nb + 63) / 64, 64, 0, st>>>(F, db->pd_ops.p, d_len);
+        CU(cudaGetLastError());
+        db->stats[0]++;
+        hlen.resize((size_t)nb + 2);
+        hops.resize((size_t)ops_bytes + 1);
+        CU(cudaMemcpyAsync(hlen.data(), d_len, (size_t)nb * 4, cudaMemcpyDeviceToHost, st));
+        int32_t herr[2] = {0, 0};
+        CU(cudaMemcpyAsync(herr, d_ctl, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(hops.data(), db->pd_ops.p, (size_t)ops_bytes, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        if (herr[1] != 0) return fail(PYOPAL_CUDA_ERR_INTERNAL, "traceback does not reproduce the forward score");
+        for (int b = 0; b < nb; b++) {
+            const Todo& t = todo[pos + (size_t)b];
+            const int len = hlen[(size_t)b];
+            memcpy(ops + ops_offsets[t.k], hops.data() + hjobs[(size_t)b].ops_end - len, (size_t)len);
+            ops_len[t.k] = len;
+        }
+        pos = p2;
+    }
+    CU(cudaEventRecord(db->ev1, st));
+    CU(cudaEventSynchronize(db->ev1));
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, db->ev0, db->ev1));
+    db->stats[4] = (int64_t)(ms * 1000.0f);
+    return 0;
+}
