@@ -180,18 +180,6 @@ class ClockSampler(threading.Thread):
                 "samples": len(sm)}
 
 
-def shard_indices(lengths, world, rank):
-    """Cell-balanced sharding: length-sorted targets dealt round-robin, alternating direction
-    (snake) so every rank gets the same length mix and the giants spread out."""
-    import numpy as np
-
-    order = np.argsort(-lengths.astype(np.int64), kind="stable")
-    pos = np.arange(len(order))
-    rnd, k = pos // world, pos % world
-    owner = np.where(rnd % 2 == 0, k, world - 1 - k)
-    return np.sort(order[owner == rank])
-
-
 def run_b200(args):
     import numpy as np
     import torch
@@ -213,17 +201,14 @@ def run_b200(args):
     residues, offsets, lengths = db
     total_res = int(lengths.sum())
     n_all = len(lengths)
-    mine = shard_indices(lengths, world, rank) if world > 1 else np.arange(n_all)
+    from pyopal_b200 import sharding
+
+    mine = sharding.shard_indices(lengths, world, rank) if world > 1 else np.arange(n_all)
     # pack this rank's shard
     if world == 1:
         sr, so, sl = residues, offsets, lengths
     else:
-        sl = lengths[mine]
-        so = np.zeros(len(mine), dtype=np.int64)
-        np.cumsum(sl[:-1], out=so[1:])
-        # gather the shard's residues: source position of every destination byte
-        src = np.repeat(offsets[mine] - so, sl) + np.arange(int(sl.sum()), dtype=np.int64)
-        sr = residues[src]
+        sr, so, sl = sharding.pack_shard(residues, offsets, lengths, mine)
     store = cuda.DeviceStore(sr, so, np.ascontiguousarray(sl), 24, device=local)
     aligner = pyopal.Aligner(MATRIX, GAP_OPEN, GAP_EXTEND)
     M = aligner._int_matrix
@@ -231,22 +216,14 @@ def run_b200(args):
     qbytes = [q.tobytes() for q in queries]
 
     n_mine = len(mine)
-    n_pad = (n_all + world - 1) // world + 1
     # a non-blocking stream of our own: on torch's legacy default stream the library's
     # high-priority side stream (longest targets) does not overlap the bulk kernel
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)
-    d_scores = [torch.zeros(n_pad, dtype=torch.int32, device="cuda") for _ in qbytes]
-    gathered = [torch.empty(world * n_pad, dtype=torch.int32, device="cuda") for _ in qbytes] if world > 1 else None
-    # global index of every gathered slot -> un-permute on rank 0
-    if world > 1:
-        idx = torch.full((n_pad,), -1, dtype=torch.int64, device="cuda")
-        idx[:n_mine] = torch.from_numpy(mine).cuda()
-        all_idx = torch.empty(world * n_pad, dtype=torch.int64, device="cuda")
-        dist.all_gather_into_tensor(all_idx, idx)
-        valid = (all_idx >= 0).nonzero().squeeze(1)
-        dest = all_idx[valid]
-        final = [torch.zeros(n_all, dtype=torch.int32, device="cuda") for _ in qbytes]
+    gather = sharding.ScoreGather(mine, n_all, world, "cuda")
+    d_scores = [gather.new_local() for _ in qbytes]
+    gathered = [torch.empty(world * gather.n_pad, dtype=torch.int32, device="cuda") for _ in qbytes] if world > 1 else None
+    final = [torch.zeros(n_all, dtype=torch.int32, device="cuda") for _ in qbytes] if world > 1 else None
 
     launches = [0]
     k16_us = [0.0]
@@ -264,9 +241,7 @@ def run_b200(args):
                 k16_n[0] += 1
                 step.last = st
             if world > 1:
-                dist.all_gather_into_tensor(gathered[qi], d_scores[qi])
-                if rank == 0:
-                    final[qi][dest] = gathered[qi][valid]
+                gather.gather(d_scores[qi], gathered[qi], final[qi])
 
     def barrier():
         if world > 1:

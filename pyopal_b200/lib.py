@@ -222,6 +222,8 @@ class Alphabet:
                 sequence = sequence.encode("ascii")
             except UnicodeEncodeError as err:
                 raise ValueError(f"character outside ASCII range: {sequence[err.start]!r}") from None
+        elif isinstance(sequence, int):
+            raise TypeError(f"expected str or a bytes-like object, found {type(sequence).__name__}")
         return self._translate(sequence)
 
     def decode(self, encoded):
