@@ -183,3 +183,49 @@ def test_top_hits_workflow_config4(cuda, oracle):
     hit_seqs = [seqs[i] for i in top]
     check_mode(oracle, aligner, q, hit_seqs, "sw", "end", db=hits)
     check_mode(oracle, aligner, q, hit_seqs, "sw", "full", db=hits)
+
+
+GOLDEN = __import__("os").path.join(__import__("os").path.dirname(__file__), "golden")
+
+
+@pytest.mark.parametrize("name", sorted(f for f in __import__("os").listdir(GOLDEN) if f.startswith("oracle_")))
+def test_committed_fixtures_on_gpu(cuda, name):
+    """The committed fixtures (tests/golden/, no oracle call) through the C-ABI."""
+    import json
+
+    with open(__import__("os").path.join(GOLDEN, name)) as f:
+        fx = json.load(f)
+    aligner = pyopal.Aligner(fx["matrix"], fx["gap_open"], fx["gap_extend"])
+    q = bytes(fx["query"])
+    db = make_db([bytes(t) for t in fx["targets"]], aligner.alphabet)
+    for case in fx["cases"]:
+        res = aligner.align(query_str(aligner, q), db, algorithm=case["algorithm"], mode="full")
+        assert [r.score for r in res] == case["score"]
+        assert [r._query_end for r in res] == case["query_end"] and [r._target_end for r in res] == case["target_end"]
+        assert [r._query_start for r in res] == case["query_start"]
+        assert [r._target_start for r in res] == case["target_start"]
+        assert [r.alignment for r in res] == case["alignment"]
+        score_only = aligner.align(query_str(aligner, q), db, algorithm=case["algorithm"])
+        assert [r.score for r in score_only] == case["score"]
+
+
+def test_reference_vectors_on_gpu(cuda):
+    """tests/golden/reference_vectors.json: the reference's own pinned values through the public API."""
+    import json
+
+    with open(__import__("os").path.join(GOLDEN, "reference_vectors.json")) as f:
+        ref = json.load(f)
+    for v in ref["vectors"]:
+        aligner = pyopal.Aligner(v["matrix"], v["gap_open"], v["gap_extend"])
+        res = aligner.align(v["query"], pyopal.Database(v["targets"]), algorithm=v["algorithm"], mode="full")
+        n = 1 if v.get("first_only") else len(v["targets"])
+        got = {
+            "score": [r.score for r in res], "query_end": [r._query_end for r in res],
+            "target_end": [r._target_end for r in res], "query_start": [r._query_start for r in res],
+            "target_start": [r._target_start for r in res], "alignment": [r.alignment for r in res],
+            "cigar": [r.cigar() for r in res], "coverage_query": [r.coverage("query") for r in res],
+            "coverage_target": [r.coverage("target") for r in res],
+        }
+        for key, want in v.items():
+            if key in got:
+                assert got[key][:n] == want, (v["source"], key)

@@ -111,9 +111,12 @@ def test_full_mode_alignment_consistency(oracle):
             assert score == r["score"][0], (algo, q, t)
 
 
-@pytest.mark.parametrize("name", sorted(f for f in os.listdir(GOLDEN) if f.endswith(".json")) if os.path.isdir(GOLDEN) else [])
+FIXTURES = sorted(f for f in os.listdir(GOLDEN) if f.startswith("oracle_") and f.endswith(".json"))
+
+
+@pytest.mark.parametrize("name", FIXTURES)
 def test_committed_fixtures(oracle, name):
-    """Fixtures under tests/golden/ (made by tests/golden/make_fixtures.py) still reproduce."""
+    """Regression fixtures under tests/golden/ (made by tests/golden/make_fixtures.py) still reproduce."""
     with open(os.path.join(GOLDEN, name)) as f:
         fx = json.load(f)
     q = bytes(fx["query"])
@@ -125,3 +128,20 @@ def test_committed_fixtures(oracle, name):
         assert r["query_end"] == case["query_end"] and r["target_end"] == case["target_end"]
         assert r["query_start"] == case["query_start"] and r["target_start"] == case["target_start"]
         assert [a.translate(OPS).decode() for a in r["alignment"]] == case["alignment"]
+
+
+def test_reference_vectors_file(oracle):
+    """tests/golden/reference_vectors.json: every value the reference's own tests pin."""
+    with open(os.path.join(GOLDEN, "reference_vectors.json")) as f:
+        ref = json.load(f)
+    assert ref["alphabet"] == pyopal.Alphabet().letters
+    assert len(ref["vectors"]) == 4
+    for v in ref["vectors"]:
+        r = oracle.search(_enc(v["query"]), [_enc(t) for t in v["targets"]], _matrix(v["matrix"]), 24,
+                          v["gap_open"], v["gap_extend"], v["algorithm"], "full")
+        n = 1 if v.get("first_only") else len(v["targets"])
+        for key in ("score", "query_end", "target_end", "query_start", "target_start"):
+            if key in v:
+                assert r[key][:n] == v[key], (v["source"], key)
+        if "alignment" in v:
+            assert [a.translate(OPS).decode() for a in r["alignment"]][:n] == v["alignment"]
