@@ -1,0 +1,128 @@
+"""GPU parity at BASELINE.json's full sizes (config 2: 570k Swiss-Prot-shaped proteins, 2.05e8 residues).
+
+The oracle cannot score 1e11+ cells in seconds, so the full-size runs are
+checked through size-independent properties: the oracle on a random subsample
+plus every planted giant, ordering between the algorithms, planted homologs,
+and agreement between the whole-database search and its slices / shards /
+batched form.
+"""
+
+import array
+
+import numpy as np
+import pytest
+
+import pyopal_b200 as pyopal
+import synthetic
+from pyopal_b200 import sharding
+
+pytestmark = pytest.mark.gpu
+
+GO, GE = 11, 1
+ALGO = {"nw": 0, "hw": 1, "ov": 2, "sw": 3}
+
+
+@pytest.fixture(scope="module")
+def full(cuda):
+    db = synthetic.config2()
+    residues, offsets, lengths = db
+    store = cuda.DeviceStore(residues, offsets, np.ascontiguousarray(lengths), 24, device=0)
+    aligner = pyopal.Aligner("BLOSUM62", GO, GE)
+    queries = synthetic.config2_queries(db)
+    return {"db": db, "store": store, "M": aligner._int_matrix, "queries": [q.tobytes() for q in queries]}
+
+
+def gpu_scores(full, q, algo, **kw):
+    return np.frombuffer(full["store"].search(q, GO, GE, full["M"], 0, ALGO[algo], **kw)[0], dtype=np.int32)
+
+
+def oracle_subset(oracle, full, q, algo, idx):
+    residues, offsets, lengths = full["db"]
+    sr, so, sl = sharding.pack_shard(residues, offsets, lengths, np.asarray(idx))
+    out = oracle.search_flat(q, sr.tobytes() + b"\0", array.array("q", so.tolist()), array.array("i", sl.tolist()),
+                             full["M"], 24, GO, GE, algo, "score", 8)
+    return np.asarray(out["score"], dtype=np.int32)
+
+
+@pytest.mark.parametrize("algo", ["sw", "nw", "hw", "ov"])
+def test_subsample_and_giants_match_oracle(full, oracle, algo):
+    # a random subsample + all planted giants, query 300 aa (a mutated database entry)
+    _, _, lengths = full["db"]
+    rng = np.random.Generator(np.random.PCG64(99))
+    giants = np.nonzero(lengths >= 10_000)[0]
+    idx = np.unique(np.concatenate([rng.choice(len(lengths), 3000, replace=False), giants]))
+    q = full["queries"][1]
+    got = gpu_scores(full, q, algo)
+    assert len(got) == len(lengths)
+    want = oracle_subset(oracle, full, q, algo, idx)
+    bad = np.nonzero(got[idx] != want)[0]
+    assert len(bad) == 0, f"{algo}: {len(bad)} mismatches, first {[(int(idx[b]), int(got[idx[b]]), int(want[b])) for b in bad[:5]]}"
+
+
+def test_long_query_giants_overflow_ladder(full, oracle):
+    # the 5000-aa query against the giants: positive 16-bit overflow (SW) and negative (NW) escalate to 32 bit
+    _, _, lengths = full["db"]
+    giants = np.nonzero(lengths >= 10_000)[0]
+    q = full["queries"][4]
+    for algo in ("sw", "nw"):
+        got = gpu_scores(full, q, algo)
+        want = oracle_subset(oracle, full, q, algo, giants)
+        assert np.array_equal(got[giants], want), algo
+        if algo == "nw":
+            assert got[giants].min() < -32768
+
+
+def test_algorithm_ordering_full_size(full):
+    # free end gaps can only help: SW >= OV >= HW >= NW for every target; SW >= 0
+    q = full["queries"][0]
+    sw, ov, hw, nw = (gpu_scores(full, q, a) for a in ("sw", "ov", "hw", "nw"))
+    assert (sw >= 0).all()
+    assert (sw >= ov).all() and (ov >= hw).all() and (hw >= nw).all()
+
+
+def test_planted_homolog_is_top_hit(full):
+    # an exact copy of a database entry scores at least its identity diagonal and is the best hit
+    residues, offsets, lengths = full["db"]
+    k = int(np.nonzero((lengths > 400) & (lengths < 600))[0][7])
+    q = residues[offsets[k]: offsets[k] + lengths[k]].tobytes()
+    M = np.asarray(full["M"]).reshape(24, 24)
+    diag = int(sum(M[c, c] for c in q))
+    sw = gpu_scores(full, q, "sw")
+    assert sw[k] >= diag
+    assert sw[k] == sw.max()
+    assert gpu_scores(full, q, "nw")[k] == diag
+
+
+def test_slices_reproduce_whole(full):
+    q = full["queries"][1]
+    whole = gpu_scores(full, q, "sw")
+    n = len(whole)
+    for s, e in [(0, 1000), (123_456, 234_567), (n - 777, n), (n // 2, n // 2 + 1)]:
+        part = gpu_scores(full, q, "sw", start=s, end=e)
+        assert np.array_equal(part, whole[s:e]), (s, e)
+
+
+def test_four_way_shards_reproduce_whole(full, cuda):
+    # the N-GPU partition (sharding.shard_indices) run shard by shard on one device
+    residues, offsets, lengths = full["db"]
+    q = full["queries"][2]
+    whole = gpu_scores(full, q, "sw")
+    out = np.full(len(lengths), np.iinfo(np.int32).min, dtype=np.int32)
+    totals = []
+    for rank in range(4):
+        mine = sharding.shard_indices(lengths, 4, rank)
+        sr, so, sl = sharding.pack_shard(residues, offsets, lengths, mine)
+        store = cuda.DeviceStore(sr, so, sl, 24, device=0)
+        out[mine] = np.frombuffer(store.search(q, GO, GE, full["M"], 0, 3)[0], dtype=np.int32)
+        totals.append(int(sl.sum()))
+        store.close()
+    assert np.array_equal(out, whole)
+    assert max(totals) - min(totals) <= int(lengths.max())
+
+
+def test_batch_equals_single_full_size(full):
+    qs = full["queries"][:3]
+    flat = np.frombuffer(full["store"].search_batch(qs, GO, GE, full["M"], 3), dtype=np.int32)
+    n = full["store"].size
+    for i, q in enumerate(qs):
+        assert np.array_equal(flat[i * n: (i + 1) * n], gpu_scores(full, q, "sw")), i
