@@ -27,6 +27,7 @@ sys.path.insert(0, ROOT)
 QUERY_LENGTHS = (100, 300, 1000, 2000, 5000)
 GAP_OPEN, GAP_EXTEND, MATRIX = 11, 1, "BLOSUM62"
 METRIC = "GCUPS (whole box, device-timed) at 1/2/4/8 B200 vs PyOpal CPU"
+ALU_INSTR_PER_CELL_PAIR = 5.5  # PRMT, E, M, G, F + half a VIMNMX3 for the running best (kernels.cuh)
 
 
 def parse():
@@ -287,12 +288,20 @@ def run_b200(args):
     h2d = d2h = 0
     if rank == 0 or world > 1:
         barrier()
+        e2e_q = [0.0] * len(qbytes)
+        e2e_dev = [0.0] * len(qbytes)
         t0 = time.perf_counter()
         for _ in range(args.steps):
-            for q in qbytes:
+            for qi, q in enumerate(qbytes):
+                tq = time.perf_counter()
                 store.search(q, GAP_OPEN, GAP_EXTEND, M, 0, algo)
+                e2e_q[qi] += time.perf_counter() - tq
+                e2e_dev[qi] += store.stats()["device_us"] * 1e-6
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
+        for qi in range(len(qbytes)):
+            per_q[qi]["e2e_wall_ms"] = round(1e3 * e2e_q[qi] / args.steps, 3)
+            per_q[qi]["e2e_device_ms"] = round(1e3 * e2e_dev[qi] / args.steps, 3)
         tt = torch.tensor([dt], dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -301,7 +310,7 @@ def run_b200(args):
         d2h = len(qbytes) * n_mine * 4
 
     if rank == 0:
-        # integer-issue roofline: measured 6.5-instruction cell mix
+        # integer-ALU roofline: measured ALU-pipe rate of the kernel's own cell mix
         rate = None
         try:
             import ctypes
@@ -321,24 +330,27 @@ def run_b200(args):
         cells_k = sum(p["Lq"] for p in per_q) * int(sl.sum())
         gcups_k = cells_k / tot_us / 1e3
         bytes_k = sum(p["passes"] * int(store.device_bytes()) for p in per_q)
-        roof_gcups = rate * 2 / 6.5 / 1e9 if rate else None
+        roof_gcups = rate * 2 / ALU_INSTR_PER_CELL_PAIR / 1e9 if rate else None
         line = {
             "metric": METRIC, "value": value, "unit": "GCUPS", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "s16x2 (s32 rescore)", "data": "synthetic",
+            "vs_baseline": None, "dtype": "u16x2 (s32 rescore)", "data": "synthetic",
             "config": config_dict(args, db, {"parallelism": f"db sharded by cells over {world} GPU(s), NCCL all-gather of scores"}),
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "GCUPS", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "api": "pyopal_cuda_search (host query in, host scores out), wall clock"},
-            "roofline": {"bound": "hbm", "achieved": bytes_k / tot_us / 1e3, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": bytes_k / tot_us / 1e3 / hbm_peak, "traffic": None,
-                         "note": "residue stream of the 16-bit kernel; HBM is NOT the binding roof of this path, "
-                                 "see roofline_alu (SURVEY.md 8(d))",
-                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback"},
-            "roofline_alu": {"bound": "int_alu_issue", "achieved": gcups_k, "peak": roof_gcups, "unit": "GCUPS",
-                             "frac": (gcups_k / roof_gcups) if roof_gcups else None,
-                             "thread_instr_per_s": rate,
-                             "note": "peak = measured issue rate of the 6.5-instruction s16x2 cell mix x 2 cells / 6.5"},
+            # the binding roof of max-plus DP is the integer ALU pipe (64 lanes/clk/SM), neither HBM nor tensor
+            # cores: achieved = algorithmic cell updates of the 16-bit kernel / its CUDA-event
+            # time; peak = ALU-pipe instruction rate measured in this run (VIADDMNMX.U16x2 stream) x 2 cells / 5.5
+            "roofline": {"bound": "int_alu", "achieved": gcups_k, "peak": roof_gcups, "unit": "GCUPS",
+                         "frac": (gcups_k / roof_gcups) if roof_gcups else None, "traffic": None,
+                         "alu_thread_instr_per_s": rate, "alu_instr_per_cell_pair": ALU_INSTR_PER_CELL_PAIR,
+                         "peak_source": "pyopal_cuda_int_issue_rate (measured on this GPU in this run)"},
+            "roofline_hbm": {"bound": "hbm", "achieved": bytes_k / tot_us / 1e3, "peak": hbm_peak, "unit": "GB/s",
+                             "frac": bytes_k / tot_us / 1e3 / hbm_peak, "traffic": None,
+                             "note": "residue stream (2 B per pair column per pass) of the 16-bit kernel; "
+                                     "1/Lq byte per cell, so HBM is not the binding roof",
+                             "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback"},
             "kernels": per_q,
         }
         # launches inside the timed region: counted from the library's own counter

@@ -338,6 +338,8 @@ struct Rung {
     bool ok16 = false;        // the 16-bit rung may be used at all
     int64_t max_cols16 = 0;   // NW/HW/OV: longest pair (columns) the 16-bit rung is exact for
     int neg16 = 0, ovf_thresh = 0, pad_score = 0;
+    int bias16 = 0;           // 16-bit rung: stored value = true value + bias16 (kernels.cuh)
+    bool tdadd = false;       // every folded profile entry >= 0: Hdiag + S may be a 32-bit add
 };
 
 Rung make_rung(const int* M, int A, int go, int ge, int mode, int Lp) {
@@ -350,10 +352,16 @@ Rung make_rung(const int* M, int A, int go, int ge, int mode, int Lp) {
     r.pad_score = pad_raw + go;
     const int lo = std::min(smin, pad_raw) + go, hi = std::max(smax, pad_raw) + go;
     r.fits8 = (lo >= -128 && hi <= 127);
-    r.neg16 = -32768 + ge;
-    r.ovf_thresh = 32767 - 128 - 1;
-    const int64_t slack = 256;
-    r.ok16 = r.fits8 && (3LL * go + 2LL * ge + slack < 16000);
+    r.tdadd = (lo >= 0);
+    // Bias of the u16 halves.  Local alignment never goes below -(open + ext), so a small bias
+    // leaves almost the whole 16-bit range to the score; the other modes are symmetric.
+    r.bias16 = (mode == MODE_SW) ? 2 * go + ge + 256 : 32768;
+    // stored as max(open, ext): neither (E - ext) nor (F - open) wraps below 0 (kernels.cuh, sweep 2)
+    r.neg16 = std::max(go, ge) - r.bias16;
+    r.ovf_thresh = 65535 - 128 - 1 - r.bias16;     // SW: a running max >= this is rescored at 32 bit
+    const int64_t slack = 512;  // covers S + open <= 127 twice (M - open and F - open are formed below H - open)
+    // the 16-bit kernel's short F chain needs ext <= open
+    r.ok16 = r.fits8 && (3LL * go + 2LL * ge + slack < 16000) && ge <= go;
     if (r.ok16 && mode != MODE_SW) {
         // lower bound of any live value: -(3*open + (Lp + cols + 2)*ext + 128) must stay above neg16
         int64_t cap = INT32_MAX;
@@ -385,8 +393,8 @@ __global__ void scatter_fixes_kernel(const int32_t* fixes, int nfix, int32_t* ou
     if (i < nfix) out[fixes[2 * i]] = fixes[2 * i + 1];
 }
 
-search_kernel_t pick_kernel(int K, int W, bool local, bool psmem) {
-    if (W == 16) return local ? get_search_kernel_w16_l1(K, psmem) : get_search_kernel_w16_l0(K, psmem);
+search_kernel_t pick_kernel(int K, int W, bool local, bool psmem, bool tdadd = true) {
+    if (W == 16) return local ? get_search_kernel_w16_l1(K, psmem, tdadd) : get_search_kernel_w16_l0(K, psmem, tdadd);
     return local ? get_search_kernel_w32_l1(K, psmem) : get_search_kernel_w32_l0(K, psmem);
 }
 
@@ -561,6 +569,7 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
     P.query = db->query.p; P.matrix = db->d_matrix;
     P.Lq = Lq; P.A = A; P.go = go; P.ge = ge;
     P.mode = mode; P.pad_score = rung.pad_score; P.ovf_thresh = rung.ovf_thresh;
+    P.one = 1u; P.bias = 0;
     P.out = d_out; P.out_start = start; P.out_end = end;
     P.ovf_list = db->ovf.p; P.ovf_count = db->d_counts + 2;
     P.bndH = db->bndH.p; P.bndF = db->bndF.p;
@@ -603,12 +612,12 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
         if (rc) return rc;
     }
     if (ntail > 0 && !same_plan) {
-        search_kernel_t kt = pick_kernel(tail.K, 16, local, tail.psmem);
+        search_kernel_t kt = pick_kernel(tail.K, 16, local, tail.psmem, rung.tdadd);
         if (!kt) return fail(PYOPAL_CUDA_ERR_INTERNAL, "no 16-bit kernel for the tail tile");
         KParams Q = P;
         apply_plan(Q, tail);
         Q.worklist = d_wl_tail; Q.nwork = db->d_counts + 3; Q.counter = db->d_counts + 7;
-        Q.neg = rung.neg16;
+        Q.neg = rung.neg16; Q.bias = rung.bias16;
         int rc = launch_search(db, kt, Q, tail.smem, 32, ntail, side);
         if (rc) return rc;
     }
@@ -623,12 +632,12 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
         const int32_t* wl = d_wl_bulk;
         const int64_t nw = nbulk;
         if (nw > 0) {
-            search_kernel_t kb = pick_kernel(bulk.K, 16, local, bulk.psmem);
+            search_kernel_t kb = pick_kernel(bulk.K, 16, local, bulk.psmem, rung.tdadd);
             if (!kb) return fail(PYOPAL_CUDA_ERR_INTERNAL, "no 16-bit kernel for this tile");
             KParams Q = P;
             apply_plan(Q, bulk);
             Q.worklist = wl; Q.nwork = db->d_counts + 0; Q.counter = db->d_counts + 4;
-            Q.neg = rung.neg16;
+            Q.neg = rung.neg16; Q.bias = rung.bias16;
             const int gpw = 32 >> bulk.logG;
             // one CTA per SM when the profile is large: use the whole register file with 16 warps
             // (with side-stream CTAs resident, 7-warp CTAs leave them registers: 2 x 224 x 128 < 64K)

@@ -11,10 +11,17 @@
 //   * the TARGET streams through the group one column per step, thread p
 //     working on column (step - p): an anti-diagonal wavefront whose only
 //     communication is two warp shuffles per step (H and F of the row above);
-//   * in the 16-bit rung every 32-bit lane carries TWO targets (s16x2) and the
-//     cell update is six DPX instructions (VIADDMNMX.S16x2, VIMNMX3.S16x2...);
-//     the database is stored pair-interleaved so one u16 load yields the
-//     residues of both targets;
+//   * in the 16-bit rung every 32-bit lane carries TWO targets (u16x2, values
+//     stored with a bias B so that they are non-negative): maxima are DPX
+//     instructions on the ALU pipe (VIADDMNMX.U16x2, VIMNMX3.U16x2,
+//     VIMNMX.U16x2) and -- because no half can go negative or overflow --
+//     the two additions of a cell (Hdiag + S, H - open) are plain 32-bit
+//     IMADs on the otherwise idle FMA pipe; the database is stored
+//     pair-interleaved so one u16 load yields the residues of both targets;
+//   * a column step is two sweeps over the thread's K rows: bottom-up
+//     (E and max(Hdiag + S, E), independent rows, results overwrite the
+//     previous column in place) then top-down (the F chain), so no register
+//     rotation is needed between steps;
 //   * substitution scores come from a query profile in shared memory
 //     (int8, score+gap_open folded), fetched K rows at a time with vector LDS
 //     and widened with one PRMT per cell pair;
@@ -54,7 +61,9 @@ struct KParams {
     int Lq, A, go, ge;
     int G, logG, npass, pitch, padtop;
     int mode;
-    int neg;                  // "-infinity" for this rung
+    int neg;                  // "-infinity" for this rung (true value; stored as neg + bias)
+    int bias;                 // W=16: values are stored as value + bias in each u16 half; W=32: 0
+    unsigned one;             // 1, as a run-time value: forces IMAD (FMA pipe) for the 32-bit adds
     int pad_score;            // folded score of padding rows / the padding letter
     int ovf_thresh;           // 16-bit rung, SW: running max >= this => rescore at 32 bit
     // results
@@ -71,28 +80,40 @@ struct KParams {
 // value traits: one s16x2 word (two targets) or one s32 (one target) per lane
 template <int W> struct Val;
 
+// d = a + b on the FMA pipe (a * one + b); exact for biased u16x2 words as long
+// as neither half leaves [0, 65535] and the low half of the addend is >= 0, or
+// the addend is a borrow-adjusted constant (see delta())
+__device__ __forceinline__ uint32_t imad_add(uint32_t a, uint32_t b, unsigned one) {
+    uint32_t d;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(one), "r"(b));
+    return d;
+}
+
 template <> struct Val<16> {
     typedef uint32_t T;
-    static __device__ __forceinline__ T splat(int v) { return (uint32_t)(uint16_t)(int16_t)v * 0x00010001u; }
-    static __device__ __forceinline__ T addmax(T a, T b, T c) { return __viaddmax_s16x2(a, b, c); }
-    static __device__ __forceinline__ T add(T a, T b) { return __vadd2(a, b); }
-    static __device__ __forceinline__ T sub(T a, T b) { return __vsub2(a, b); }
-    static __device__ __forceinline__ T max2(T a, T b) { return __vmaxs2(a, b); }
-    static __device__ __forceinline__ T max3(T a, T b, T c) { return __vimax3_s16x2(a, b, c); }
-    static __device__ __forceinline__ T max3relu(T a, T b, T c) { return __vimax3_s16x2_relu(a, b, c); }
-    static __device__ __forceinline__ int lo(T v) { return (int)(int16_t)(v & 0xffffu); }
-    static __device__ __forceinline__ int hi(T v) { return (int)(int16_t)(v >> 16); }
+    // value v (already biased, in [0, 65535]) in both halves
+    static __device__ __forceinline__ T splat(int v) { return (uint32_t)(uint16_t)v * 0x00010001u; }
+    // a signed delta for the packed adder of VIADDMNMX (each half wraps mod 2^16)
+    static __device__ __forceinline__ T pdelta(int v) { return (uint32_t)(uint16_t)(int16_t)v * 0x00010001u; }
+    // the same delta for a 32-bit add: v + v * 65536 in two's complement (borrow-adjusted)
+    static __device__ __forceinline__ T delta(int v) { return (uint32_t)(v * 0x00010001); }
+    static __device__ __forceinline__ T addmax(T a, T b, T c) { return __viaddmax_u16x2(a, b, c); }
+    static __device__ __forceinline__ T add(T a, T b, unsigned one) { return imad_add(a, b, one); }
+    static __device__ __forceinline__ T max2(T a, T b) { return __vmaxu2(a, b); }
+    static __device__ __forceinline__ T max3(T a, T b, T c) { return __vimax3_u16x2(a, b, c); }
+    static __device__ __forceinline__ int lo(T v) { return (int)(v & 0xffffu); }
+    static __device__ __forceinline__ int hi(T v) { return (int)(v >> 16); }
 };
 
 template <> struct Val<32> {
     typedef int T;
     static __device__ __forceinline__ T splat(int v) { return v; }
+    static __device__ __forceinline__ T pdelta(int v) { return v; }
+    static __device__ __forceinline__ T delta(int v) { return v; }
     static __device__ __forceinline__ T addmax(T a, T b, T c) { return __viaddmax_s32(a, b, c); }
-    static __device__ __forceinline__ T add(T a, T b) { return a + b; }
-    static __device__ __forceinline__ T sub(T a, T b) { return a - b; }
+    static __device__ __forceinline__ T add(T a, T b, unsigned one) { return (int)imad_add((uint32_t)a, (uint32_t)b, one); }
     static __device__ __forceinline__ T max2(T a, T b) { return max(a, b); }
     static __device__ __forceinline__ T max3(T a, T b, T c) { return __vimax3_s32(a, b, c); }
-    static __device__ __forceinline__ T max3relu(T a, T b, T c) { return __vimax3_s32_relu(a, b, c); }
     static __device__ __forceinline__ int lo(T v) { return v; }
     static __device__ __forceinline__ int hi(T v) { return v; }
 };
@@ -136,12 +157,17 @@ __device__ __forceinline__ int widen_one(uint32_t x, int u) {
     }
 }
 
-template <int K, int W, bool LOCAL, bool PSMEM, bool WIDE = false>
+// TDADD: every profile entry (S + open, padding included) is >= 0, so the
+// 16-bit rung may form Hdiag + S with a 32-bit IMAD; otherwise that add stays
+// in the packed adder of VIADDMNMX.  (Ignored by the 32-bit rung.)
+template <int K, int W, bool LOCAL, bool PSMEM, bool WIDE = false, bool TDADD = true>
 __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KParams P) {
     static_assert(K % 4 == 0, "K must be a multiple of 4");
     static_assert(!WIDE || (W == 32 && !PSMEM), "wide profile: 32-bit rung, global memory only");
     typedef Val<W> V;
     typedef typename V::T val_t;
+    constexpr bool ADDPATH = TDADD || (W == 32);
+    constexpr bool SHORTF = (W == 16);        // the host sends ext > open to the 32-bit rung
     extern __shared__ __align__(16) unsigned char smem_raw[];
 
     const int nwork = *P.nwork;
@@ -171,9 +197,13 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
     const int ntasks = (nwork + gpw - 1) / gpw;
     const bool top_free = (P.mode != MODE_NW);
     const bool left_free = (P.mode == MODE_OV || P.mode == MODE_SW);
-    const val_t NEGEXT = V::splat(-P.ge);
-    const val_t OPEN = V::splat(P.go);
-    const val_t NEG = V::splat(P.neg);
+    const int B = P.bias;
+    const unsigned one = P.one;
+    const val_t NEGEXT = V::pdelta(-P.ge);    // packed adder of VIADDMNMX
+    const val_t NEGOPEN = V::delta(-P.go);    // 32-bit adder (IMAD)
+    const val_t PNEGOPEN = V::pdelta(-P.go);  // packed adder
+    const val_t NEG = V::splat(P.neg + B);
+    const val_t FLOOR = V::splat(B);          // local alignment: H >= 0
     const int lastpass = P.npass - 1;
 
     for (;;) {
@@ -196,8 +226,8 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
         const int ncol = len0;
         const int nsteps = __reduce_max_sync(FULL, ncol) + G - 1;
 
-        val_t best = V::splat(0);             // SW: running max of H
-        int res0 = INT_MIN, res1 = INT_MIN;   // NW/HW/OV
+        val_t best = FLOOR;                   // SW: running max of H
+        int res0 = INT_MIN, res1 = INT_MIN;   // NW/HW/OV (true values)
 
         for (int pass = 0; pass < P.npass; ++pass) {
             const int rowbase = pass * T + p * K;  // tile row of register 0
@@ -206,19 +236,19 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
             for (int r = 0; r < K; ++r) {
                 int qi = rowbase + r - P.padtop;
                 int hl = (left_free || qi < 0) ? 0 : -(P.go + qi * P.ge);
-                Gl[r] = V::splat(hl - P.go);
+                Gl[r] = V::splat(hl - P.go + B);
                 E[r] = NEG;
             }
-            val_t Gout = V::splat(0), Fout = NEG, upGprev;
+            val_t Gout = FLOOR, Fout = NEG, upGprev;
             {
                 int qi = rowbase - 1 - P.padtop;
                 int hl = (left_free || qi < 0) ? 0 : -(P.go + qi * P.ge);
-                upGprev = V::splat(hl - P.go);
+                upGprev = V::splat(hl - P.go + B);
             }
             // software pipeline: the residue pair and the pass boundary of step s+1 are
             // fetched while step s computes
             unsigned code_nx = 0;
-            val_t bG_nx = V::splat(0), bF_nx = NEG;
+            val_t bG_nx = FLOOR, bF_nx = NEG;
             if (p == 0 && ncol > 0) {
                 code_nx = P.stream[off];
                 if (pass != 0) {
@@ -236,7 +266,7 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
                 if (p == 0) {
                     if (pass == 0) {
                         int ht = top_free ? 0 : -(P.go + j * P.ge);
-                        upG = V::splat(ht - P.go);
+                        upG = V::splat(ht - P.go + B);
                         upF = NEG;
                     } else {
                         upG = bG_nx;
@@ -259,9 +289,10 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
                     const unsigned t1 = code >> 8;
                     const int8_t* pa = prof + t0 * P.pitch + rowbase;
                     const int8_t* pb = prof + t1 * P.pitch + rowbase;
-                    val_t F = upF, Gup = upG, Gd = upGprev;
+                    // ---- sweep 1, bottom-up: E and M = max(Hdiag + S, E [, 0]); rows are
+                    // independent and M overwrites the previous column's G in place
 #pragma unroll
-                    for (int c = 0; c < K / 4; ++c) {
+                    for (int c = K / 4 - 1; c >= 0; --c) {
                         uint32_t wa = 0, wb = 0;
                         int4 sw = make_int4(0, 0, 0, 0);
                         if (WIDE) {
@@ -274,20 +305,52 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
                             if (W == 16) wb = __ldg(reinterpret_cast<const uint32_t*>(pb + 4 * c));
                         }
 #pragma unroll
-                        for (int u = 0; u < 4; ++u) {
+                        for (int u = 3; u >= 0; --u) {
                             const int r = 4 * c + u;
                             val_t S;
                             if (WIDE) S = (val_t)(u == 0 ? sw.x : u == 1 ? sw.y : u == 2 ? sw.z : sw.w);
                             else if (W == 16) S = (val_t)widen_pair(wa, wb, u);
                             else S = (val_t)widen_one(wa, u);
+                            const val_t Gd = (r == 0) ? upGprev : Gl[r - 1];
                             E[r] = V::addmax(E[r], NEGEXT, Gl[r]);   // max(E - ext, Hleft - open)
-                            F = V::addmax(F, NEGEXT, Gup);           // max(F - ext, Hup - open)
-                            val_t Td = V::add(Gd, S);                // Hdiag + S  (S carries the +open)
-                            val_t Hn = LOCAL ? V::max3relu(Td, E[r], F) : V::max3(Td, E[r], F);
-                            Gd = Gl[r];
-                            Gup = V::sub(Hn, OPEN);
+                            val_t M;
+                            if (ADDPATH) {
+                                const val_t Td = V::add(Gd, S, one);     // Hdiag + S  (S carries the +open)
+                                M = LOCAL ? V::max3(Td, E[r], FLOOR) : V::max2(Td, E[r]);
+                            } else {
+                                M = V::addmax(Gd, S, E[r]);
+                                if (LOCAL && SHORTF) M = V::max2(M, FLOOR);
+                            }
+                            if (SHORTF) {
+                                // F never sets a new maximum, so the running best only looks at M
+                                if (LOCAL) best = V::max2(best, M);
+                                Gl[r] = V::add(M, NEGOPEN, one);         // M - open
+                            } else {
+                                Gl[r] = M;
+                            }
+                        }
+                    }
+                    // ---- sweep 2, top-down: the F chain, H, G = H - open
+                    val_t F = upF, Gup = upG;
+                    if (SHORTF) {
+                        // ext <= open: F(r+1) = max(F(r) - ext, M(r) - open) does not need H(r), so the
+                        // serial chain is one instruction per row; G(r) = max(M(r) - open, F(r) - open)
+                        F = V::addmax(F, NEGEXT, Gup);               // F(0) = max(Fup - ext, Hup - open)
+#pragma unroll
+                        for (int r = 0; r < K; ++r) {
+                            const val_t MO = Gl[r];
+                            Gup = V::addmax(F, PNEGOPEN, MO);        // G(r) = max(F(r), M(r)) - open
                             Gl[r] = Gup;
+                            if (r < K - 1) F = V::addmax(F, NEGEXT, MO);   // F(r+1)
+                        }
+                    } else {
+#pragma unroll
+                        for (int r = 0; r < K; ++r) {
+                            F = V::addmax(F, NEGEXT, Gup);               // max(F - ext, Hup - open)
+                            const val_t Hn = (LOCAL && !ADDPATH) ? V::max3(Gl[r], F, FLOOR) : V::max2(Gl[r], F);
                             if (LOCAL) best = V::max2(best, Hn);
+                            Gup = V::add(Hn, NEGOPEN, one);
+                            Gl[r] = Gup;
                         }
                     }
                     Gout = Gup;
@@ -299,8 +362,8 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
                             __stcg(P.bndH + bi, (uint32_t)Gout);
                             __stcg(P.bndF + bi, (uint32_t)Fout);
                         } else if (!LOCAL) {
-                            // last query row: H = Gout + open
-                            const int h0 = V::lo(Gout) + P.go, h1 = V::hi(Gout) + P.go;
+                            // last query row: H = G + open
+                            const int h0 = V::lo(Gout) + P.go - B, h1 = V::hi(Gout) + P.go - B;
                             if (P.mode == MODE_NW) {
                                 if (j == len0 - 1) res0 = h0;
                                 if (j == len1 - 1) res1 = h1;
@@ -315,8 +378,8 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
 #pragma unroll
                         for (int r = 0; r < K; ++r) {
                             if (rowbase + r >= P.padtop) {
-                                if (j == len0 - 1) res0 = max(res0, V::lo(Gl[r]) + P.go);
-                                if (W == 16 && j == len1 - 1) res1 = max(res1, V::hi(Gl[r]) + P.go);
+                                if (j == len0 - 1) res0 = max(res0, V::lo(Gl[r]) + P.go - B);
+                                if (W == 16 && j == len1 - 1) res1 = max(res1, V::hi(Gl[r]) + P.go - B);
                             }
                         }
                     }
@@ -327,7 +390,7 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
 
         // reduce over the group, lane p == 0 publishes
         int r0, r1;
-        if (LOCAL) { r0 = V::lo(best); r1 = V::hi(best); }
+        if (LOCAL) { r0 = V::lo(best) - B; r1 = V::hi(best) - B; }
         else { r0 = res0; r1 = res1; }
         for (int d = 1; d < G; d <<= 1) {
             r0 = max(r0, __shfl_xor_sync(FULL, r0, d));
@@ -336,12 +399,18 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
         if (have && p == 0) {
             if (W == 16) {
                 const int ia = P.pair_idx[2 * pair], ib = P.pair_idx[2 * pair + 1];
-                if (ia >= P.out_start && ia < P.out_end) {
-                    if (LOCAL && r0 >= P.ovf_thresh) P.ovf_list[atomicAdd(P.ovf_count, 1)] = pair << 1;
+                const bool ina = ia >= P.out_start && ia < P.out_end;
+                const bool inb = ib >= P.out_start && ib < P.out_end;
+                // An overflowing LOW half carries into the high half through the 32-bit adds:
+                // when target a overflows, target b is rescored as well.
+                const bool ova = LOCAL && r0 >= P.ovf_thresh;
+                const bool ovb = LOCAL && (r1 >= P.ovf_thresh || ova);
+                if (ina) {
+                    if (ova) P.ovf_list[atomicAdd(P.ovf_count, 1)] = pair << 1;
                     else P.out[ia - P.out_start] = r0;
                 }
-                if (ib >= P.out_start && ib < P.out_end) {
-                    if (LOCAL && r1 >= P.ovf_thresh) P.ovf_list[atomicAdd(P.ovf_count, 1)] = (pair << 1) | 1;
+                if (inb) {
+                    if (ovb) P.ovf_list[atomicAdd(P.ovf_count, 1)] = (pair << 1) | 1;
                     else P.out[ib - P.out_start] = r1;
                 }
             } else {
@@ -359,8 +428,8 @@ __global__ void build_profile_kernel(const KParams P, int8_t* narrow, int32_t* w
 typedef void (*search_kernel_t)(const KParams);
 
 // defined in kernels_w*_l*.cu; nullptr when the combination is not built
-search_kernel_t get_search_kernel_w16_l1(int K, bool psmem);
-search_kernel_t get_search_kernel_w16_l0(int K, bool psmem);
+search_kernel_t get_search_kernel_w16_l1(int K, bool psmem, bool tdadd);
+search_kernel_t get_search_kernel_w16_l0(int K, bool psmem, bool tdadd);
 search_kernel_t get_search_kernel_w32_l1(int K, bool psmem);
 search_kernel_t get_search_kernel_w32_l0(int K, bool psmem);
 search_kernel_t get_search_kernel_wide(bool local);  // K = 32, W = 32

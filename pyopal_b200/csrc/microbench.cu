@@ -1,7 +1,11 @@
-// pyopal_b200/csrc/microbench.cu -- integer-issue microbenchmark behind the
-// cell-update roofline: the six instructions of the 16-bit
-// cell (2x VIADDMNMX.S16x2, VIADDMNMX.S16x2.RELU, VIMNMX.S16x2.RELU,
-// VIADD.16x2, VIMNMX3.S16x2 at half rate, PRMT) on independent registers.
+// pyopal_b200/csrc/microbench.cu -- integer-ALU-pipe microbenchmark behind the
+// cell-update roofline.  Every maximum of the DP cell
+// (VIADDMNMX / VIMNMX3 / VIMNMX, 16x2 or 32 bit) and the PRMT that widens the
+// profile bytes issue down the SM's ALU pipe at one warp instruction per two
+// clocks per SM sub-partition (64 lanes/clk/SM), whatever the mix; this kernel
+// measures that rate with independent VIADDMNMX.U16x2 chains.  A 16-bit cell
+// pair needs 5.5 such instructions (kernels.cuh), its two additions being
+// IMADs on the FMA pipe, so roof = rate * 2 cells / 5.5.
 #include "../../include/pyopal_cuda.h"
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -9,24 +13,17 @@
 namespace {
 constexpr int CHAINS = 8;
 constexpr int INNER = 64;
-// one "cell" per chain per inner iteration: 6 DPX/ALU instructions + 1 PRMT
-__global__ void __launch_bounds__(256) issue_kernel(uint32_t* out, int iters, uint32_t seed) {
-    uint32_t e[CHAINS], f[CHAINS], g[CHAINS], b = 0;
-    const uint32_t negext = 0xffffffffu, open = 0x000b000bu;
+__global__ void __launch_bounds__(256) issue_kernel(uint32_t* out, int iters, uint32_t seed, uint32_t one) {
+    uint32_t e[CHAINS], f[CHAINS], g[CHAINS], b = one;
+    const uint32_t negext = 0xffffffffu;
     for (int c = 0; c < CHAINS; c++) { e[c] = seed + c; f[c] = seed * 3 + c; g[c] = seed * 7 + threadIdx.x + c; }
     for (int it = 0; it < iters; it++) {
 #pragma unroll
         for (int k = 0; k < INNER; k++) {
 #pragma unroll
             for (int c = 0; c < CHAINS; c++) {
-                uint32_t s;
-                asm volatile("prmt.b32 %0, %1, %2, 0xC480;" : "=r"(s) : "r"(g[c]), "r"(e[c]));
-                e[c] = __viaddmax_s16x2(e[c], negext, g[c]);
-                f[c] = __viaddmax_s16x2(f[c], negext, g[(c + 1) % CHAINS]);
-                uint32_t h = __viaddmax_s16x2_relu(g[c], s, e[c]);
-                h = __vimax_s16x2_relu(h, f[c]);
-                g[c] = __vsub2(h, open);
-                if (k & 1) b = __vimax3_s16x2(b, h, g[c]);
+                e[c] = __viaddmax_u16x2(e[c], negext, g[c]);
+                f[c] = __viaddmax_u16x2(f[c], negext, g[c]);
             }
         }
     }
@@ -45,12 +42,12 @@ extern "C" int pyopal_cuda_int_issue_rate(int device, double* thread_instr_per_s
     if (cudaMalloc(&d, (size_t)blocks * threads * sizeof(uint32_t)) != cudaSuccess) return PYOPAL_CUDA_ERR_NOMEM;
     cudaEvent_t a, b;
     cudaEventCreate(&a); cudaEventCreate(&b);
-    issue_kernel<<<blocks, threads>>>(d, 10, 1u);  // warm-up
+    issue_kernel<<<blocks, threads>>>(d, 10, 1u, 1u);  // warm-up
     cudaDeviceSynchronize();
     float best_ms = 1e30f;
     for (int rep = 0; rep < 5; rep++) {
         cudaEventRecord(a);
-        issue_kernel<<<blocks, threads>>>(d, iters, 1u + rep);
+        issue_kernel<<<blocks, threads>>>(d, iters, 1u + rep, 1u);
         cudaEventRecord(b);
         cudaEventSynchronize(b);
         float ms = 0;
@@ -60,8 +57,7 @@ extern "C" int pyopal_cuda_int_issue_rate(int device, double* thread_instr_per_s
     cudaError_t e = cudaGetLastError();
     cudaEventDestroy(a); cudaEventDestroy(b); cudaFree(d);
     if (e != cudaSuccess) return PYOPAL_CUDA_ERR_CUDA;
-    // 6.5 instructions per cell: E, F, H(2), G, best (every other cell), PRMT
-    const double instr = (double)blocks * threads * (double)iters * INNER * CHAINS * 6.5;
+    const double instr = (double)blocks * threads * (double)iters * INNER * CHAINS * 2.0;
     if (thread_instr_per_s) *thread_instr_per_s = instr / (best_ms * 1e-3);
     if (sm_clock_mhz) *sm_clock_mhz = prop.clockRate / 1000.0;
     return 0;

@@ -60,15 +60,16 @@ def test_subsample_and_giants_match_oracle(full, oracle, algo):
 
 
 def test_long_query_giants_overflow_ladder(full, oracle):
-    # the 5000-aa query against the giants: positive 16-bit overflow (SW) and negative (NW) escalate to 32 bit
+    # the giants against a long query (SW, NW, multi-pass tiles) and against the 100-aa query
+    # (NW scores below -32768: the static 32-bit rung)
     _, _, lengths = full["db"]
     giants = np.nonzero(lengths >= 10_000)[0]
-    q = full["queries"][4]
-    for algo in ("sw", "nw"):
+    for qi, algo in ((4, "sw"), (4, "nw"), (0, "nw"), (0, "hw")):
+        q = full["queries"][qi]
         got = gpu_scores(full, q, algo)
         want = oracle_subset(oracle, full, q, algo, giants)
-        assert np.array_equal(got[giants], want), algo
-        if algo == "nw":
+        assert np.array_equal(got[giants], want), (qi, algo)
+        if (qi, algo) == (0, "nw"):
             assert got[giants].min() < -32768
 
 

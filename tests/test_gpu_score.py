@@ -91,17 +91,19 @@ def test_empty_and_tiny_targets(cuda, oracle, algo):
 
 
 def test_sw_overflow_escalation(cuda, oracle):
-    # query = long mutated copies of targets => SW scores far above 32767: 16 -> 32 bit rescore
+    # query = long mutated copies of targets => SW scores above what the biased u16 rung holds
+    # (~65000): 16 -> 32 bit rescore; base[1] scores between 32768 and 65535 and stays at 16 bit
     rng = np.random.Generator(np.random.PCG64(51))
-    base = [synthetic.random_residues(rng, n) for n in (9000, 7000, 8000)]
+    base = [synthetic.random_residues(rng, n) for n in (24000, 7000, 8000)]
     seqs = [b.tobytes() for b in base] + [synthetic.mutate(rng, base[0]).tobytes()] + rand_seqs(52, 200, 5.5, 0.6, 10, 2000)
     aligner = pyopal.Aligner("BLOSUM62", 11, 1)
-    query = base[0][:8500].tobytes()
+    query = np.concatenate([base[0][:22000], base[1]]).tobytes()
     db = check(oracle, aligner, query, seqs, "sw")
     st = db._device_store().stats()
     assert st["escalated"] >= 2, st
     got = list(aligner.align_scores(query_str(aligner, query), db))
-    assert max(got) > 32767
+    assert max(got) > 65535
+    assert 32767 < got[1] < 65535
 
 
 @pytest.mark.parametrize("algo", ("nw", "hw", "ov"))
