@@ -40,6 +40,7 @@ def parse():
     ap.add_argument("--algorithm", default="sw", choices=["sw", "nw", "hw", "ov"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--debug-timing", action="store_true", help="print a search / gather breakdown to stderr")
     return ap.parse_args()
 
 
@@ -230,7 +231,7 @@ def run_b200(args):
     k16_us = [0.0]
     k16_n = [0]
 
-    def step(collect=False):
+    def step(collect=False, do_gather=True):
         for qi, q in enumerate(qbytes):
             store.search_scores_device(q, GAP_OPEN, GAP_EXTEND, M, algo, d_scores[qi].data_ptr(), stream.cuda_stream)
             # one query = one API call: wait for it like Aligner.align does before the next one is issued
@@ -241,8 +242,20 @@ def run_b200(args):
                 k16_us[0] += st["k16_us"]
                 k16_n[0] += 1
                 step.last = st
-            if world > 1:
-                gather.gather(d_scores[qi], gathered[qi], final[qi])
+            if world > 1 and do_gather:
+                if do_gather == "ag":
+                    dist.all_gather_into_tensor(gathered[qi], d_scores[qi])
+                elif do_gather == "idx":
+                    final[qi][gather.dest] = gathered[qi][gather.valid]
+                elif do_gather == "sync":
+                    gather.gather(d_scores[qi], gathered[qi], final[qi])
+                    stream.synchronize()
+                else:
+                    gather.gather(d_scores[qi], gathered[qi], final[qi])
+                    # the query is complete when its scores are gathered: wait for it like Aligner.align would
+                    # (an un-synchronised NCCL all-gather followed directly by the next search's persistent
+                    # kernels measured +21 ms per query on 2 B200s; synchronised it costs ~0.1 ms)
+                    stream.synchronize()
 
     def barrier():
         if world > 1:
@@ -252,6 +265,32 @@ def run_b200(args):
     for _ in range(args.warmup):
         step()
     barrier()
+    if args.debug_timing:
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        for qi, q in enumerate(qbytes):
+            barrier()
+            t0 = time.perf_counter()
+            ev[0].record()
+            store.search_scores_device(q, GAP_OPEN, GAP_EXTEND, M, algo, d_scores[qi].data_ptr(), stream.cuda_stream)
+            ev[1].record()
+            stream.synchronize()
+            t1 = time.perf_counter()
+            if world > 1:
+                gather.gather(d_scores[qi], gathered[qi], final[qi])
+            ev[2].record()
+            torch.cuda.synchronize()
+            t2 = time.perf_counter()
+            print(f"[rank {rank}] Lq={len(q)} search dev {ev[0].elapsed_time(ev[1]):.3f} ms wall {1e3*(t1-t0):.3f} ms; "
+                  f"gather dev {ev[1].elapsed_time(ev[2]):.3f} ms wall {1e3*(t2-t1):.3f} ms", file=sys.stderr, flush=True)
+    if args.debug_timing:
+        for g in (True, False, "ag", "idx", "sync", True):
+            barrier()
+            t0 = time.perf_counter()
+            step(do_gather=g)
+            torch.cuda.synchronize()
+            t1 = time.perf_counter()
+            barrier()
+            print(f"[rank {rank}] step gather={g}: {1e3*(t1-t0):.2f} ms (incl. barrier {1e3*(time.perf_counter()-t0):.2f})", file=sys.stderr, flush=True)
     props = torch.cuda.get_device_properties(local)
     sampler = ClockSampler("%08x:%02x:%02x.0" % (props.pci_domain_id, props.pci_bus_id, props.pci_device_id))
     sampler.start()

@@ -499,14 +499,36 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
         n32p = lo;
     }
     int64_t tail_end = n32p;
-    if (!same_plan) {
-        // a pair goes to the tail kernel when walking it alone in the bulk tile would
-        // take more than a quarter of the whole search at full machine throughput
+    // a pair leaves the bulk kernel when walking it alone in the bulk tile would
+    // take more than a quarter of the whole search at full machine throughput
+    double thr = 256.0;
+    {
         const double C0 = 28.0, C1 = 6.5;
         const double total_instr = (double)db->ncols * bulk.npass * bulk.G * (C0 + C1 * bulk.K);
         const double ideal_cycles = total_instr / ((double)db->sm_count * 64.0);
         const double step_latency = 12.0 * bulk.K + 80.0;
-        const double thr = std::max(256.0, ideal_cycles / 4.0 / (bulk.npass * step_latency));
+        thr = std::max(256.0, ideal_cycles / 4.0 / (bulk.npass * step_latency));
+    }
+    // ---- giants: the longest targets get a whole CTA each (giant.cu), 32 bit ----
+    // [0, kg) pairs; needs the int8 profile of the whole query in shared memory
+    int64_t kg = 0;
+    int gK = 4, gwarps = 1, gteams = 1, gpitch = 0;
+    size_t gsmem = 0;
+    if (!wide && Lq <= 8192 && !getenv("PYOPAL_CUDA_NO_GIANT")) {
+        gK = (Lq <= 2048) ? 4 : (Lq <= 4096) ? 8 : 16;            // rows per lane
+        gwarps = ((Lq + gK - 1) / gK + 31) / 32;                  // warps per team (<= 16): the whole query in one pass
+        gteams = (gwarps == 1) ? 16 : std::min(15, 16 / gwarps);  // teams per 512-thread CTA (15 named barriers)
+        gpitch = (gwarps * 32 * gK + 15) / 16 * 16;
+        gsmem = giant_smem_bytes(A, gpitch, gwarps, gteams);
+        if (gsmem <= SMEM_LIMIT + 24 * 1024) {
+            const double gthr = std::max(thr, 1024.0);
+            const int64_t cap = std::min<int64_t>(db->npairs, (int64_t)db->sm_count * 2);
+            while (kg < cap && (double)db->h_pair_len[(size_t)(2 * kg)] > gthr) kg++;
+        }
+    }
+    n32p = std::max(n32p, kg);
+    tail_end = n32p;
+    if (!same_plan) {
         int64_t lo = n32p, hi = db->npairs;
         while (lo < hi) {
             int64_t mid = (lo + hi) / 2;
@@ -520,8 +542,13 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
         return in_range(db->h_pair_idx[(size_t)(2 * k)]) ||
                (db->h_pair_idx[(size_t)(2 * k + 1)] >= 0 && in_range(db->h_pair_idx[(size_t)(2 * k + 1)]));
     };
-    std::vector<int32_t> wl32, wl16;
-    for (int64_t k = 0; k < n32p; k++) {
+    std::vector<int32_t> wl32, wl16, wlg;
+    for (int64_t k = 0; k < kg; k++) {
+        if (in_range(db->h_pair_idx[(size_t)(2 * k)])) wlg.push_back((int32_t)(k << 1));
+        if (db->h_pair_idx[(size_t)(2 * k + 1)] >= 0 && in_range(db->h_pair_idx[(size_t)(2 * k + 1)]))
+            wlg.push_back((int32_t)((k << 1) | 1));
+    }
+    for (int64_t k = kg; k < n32p; k++) {
         if (in_range(db->h_pair_idx[(size_t)(2 * k)])) wl32.push_back((int32_t)(k << 1));
         if (db->h_pair_idx[(size_t)(2 * k + 1)] >= 0 && in_range(db->h_pair_idx[(size_t)(2 * k + 1)]))
             wl32.push_back((int32_t)((k << 1) | 1));
@@ -543,8 +570,10 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
         d_wl_tail = db->wl16.p; d_wl_bulk = db->wl16.p + ntail;
     }
     const int64_t n32 = (int64_t)wl32.size();
+    const int64_t ng = (int64_t)wlg.size();
+    wl32.insert(wl32.end(), wlg.begin(), wlg.end());  // one upload: [static 32-bit | giants]
     if (db->wl32.reserve(wl32.size() + 1)) return PYOPAL_CUDA_ERR_NOMEM;
-    if (n32) CU(cudaMemcpyAsync(db->wl32.p, wl32.data(), wl32.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    if (!wl32.empty()) CU(cudaMemcpyAsync(db->wl32.p, wl32.data(), wl32.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
     const int64_t n16 = ntail + nbulk;
     if (same_plan) { d_wl_bulk = d_wl_tail; nbulk = n16; ntail = 0; }
     if (local && n16 && db->ovf.reserve((size_t)(2 * n16))) return PYOPAL_CUDA_ERR_NOMEM;
@@ -555,6 +584,7 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
     CU(cudaMemcpyAsync(db->d_matrix, M, (size_t)A * A * sizeof(int32_t), cudaMemcpyHostToDevice, st));
     int32_t counts[16] = {0};
     counts[0] = (int32_t)nbulk; counts[1] = (int32_t)n32; counts[2] = 0; counts[3] = (int32_t)ntail;
+    counts[8] = (int32_t)ng;
     CU(cudaMemcpyAsync(db->d_counts, counts, sizeof(counts), cudaMemcpyHostToDevice, st));
     if (bulk.npass > 1 || tail.npass > 1) {
         if (db->bndH.reserve((size_t)db->ncols + 16) || db->bndF.reserve((size_t)db->ncols + 16)) return PYOPAL_CUDA_ERR_NOMEM;
@@ -595,12 +625,30 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
     if (!k32) return fail(PYOPAL_CUDA_ERR_INTERNAL, "no 32-bit kernel for this tile");
 
     // ---- side stream: longest targets first, concurrently with the bulk -------
-    const bool side_work = (n32 > 0) || (ntail > 0 && !same_plan);
+    const bool side_work = (ng > 0) || (n32 > 0) || (ntail > 0 && !same_plan);
     cudaStream_t side = db->side;
     if (side_work) {
         CU(cudaEventRecord(db->ev_fork, st));
         CU(cudaStreamWaitEvent(side, db->ev_fork, 0));
         CU(cudaEventRecord(db->kev[0], side));
+    }
+    if (ng > 0) {
+        search_kernel_t kgiant = get_giant_kernel(gK, local);
+        if (!kgiant) return fail(PYOPAL_CUDA_ERR_INTERNAL, "no giant kernel for this tile");
+        KParams Q = P;
+        // a few teams per CTA keep the column chains short; more CTAs than that would only idle SMs
+        const int teams = (int)std::max<int64_t>(1, std::min<int64_t>(gteams, (ng + 7) / 8));
+        Q.G = gwarps; Q.logG = 0; Q.npass = teams; Q.pitch = gpitch; Q.padtop = gwarps * 32 * gK - Lq;
+        Q.worklist = db->wl32.p + n32; Q.nwork = db->d_counts + 8; Q.counter = db->d_counts + 9;
+        Q.neg = -(1 << 29);
+        // ask for the whole SM's shared memory: no throughput CTA may share the SM with the giants (giant.cu)
+        int smem_optin = 0;
+        CU(cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, db->device));
+        const size_t gsmem_all = std::max<size_t>(gsmem, (size_t)smem_optin - 1024);
+        CU(cudaFuncSetAttribute(kgiant, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsmem_all));
+        kgiant<<<(unsigned)std::min<int64_t>((ng + teams - 1) / teams, db->sm_count), 512, gsmem_all, side>>>(Q);
+        CU(cudaGetLastError());
+        db->stats[0]++;
     }
     if (n32 > 0) {
         KParams Q = P;
@@ -664,7 +712,7 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
         CU(cudaEventRecord(db->kev[5], st));
         db->kev_valid[2] = true;
     }
-    db->stats[1] = n16 * 2; db->stats[2] = n32;
+    db->stats[1] = n16 * 2; db->stats[2] = n32 + ng;
     db->stats[5] = bulk.G; db->stats[6] = bulk.K; db->stats[7] = bulk.npass; db->stats[11] = bulk.psmem ? 1 : 0;
     return apply_fixes();
 }

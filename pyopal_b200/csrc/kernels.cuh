@@ -157,6 +157,108 @@ __device__ __forceinline__ int widen_one(uint32_t x, int u) {
     }
 }
 
+// Per-launch constants of the cell update, in the rung's value type.
+template <int W> struct CellConsts {
+    typename Val<W>::T NEGEXT;    // -ext, packed adder of VIADDMNMX
+    typename Val<W>::T NEGOPEN;   // -open, 32-bit adder (IMAD)
+    typename Val<W>::T PNEGOPEN;  // -open, packed adder
+    typename Val<W>::T NEG;       // "-infinity"
+    typename Val<W>::T FLOOR;     // local alignment: H >= 0 (the bias)
+    unsigned one;
+    __device__ __forceinline__ void init(const KParams& P) {
+        typedef Val<W> V;
+        NEGEXT = V::pdelta(-P.ge);
+        NEGOPEN = V::delta(-P.go);
+        PNEGOPEN = V::pdelta(-P.go);
+        NEG = V::splat(P.neg + P.bias);
+        FLOOR = V::splat(P.bias);
+        one = P.one;
+    }
+};
+
+// One column of K rows held by one thread.  In: E, Gl = (E, H - open) of the
+// previous column, upGprev = H - open of the row above in the previous column,
+// F / Gup = (F, H - open) of the row above in this column.  Out: E, Gl of this
+// column, F / Gup of the thread's last row (for the thread below), best.
+template <int K, int W, bool LOCAL, bool PSMEM, bool WIDE, bool TDADD>
+__device__ __forceinline__ void column_update(const KParams& P, const int8_t* prof, unsigned t0, unsigned t1, int rowbase,
+                                              const CellConsts<W>& C, typename Val<W>::T (&E)[K],
+                                              typename Val<W>::T (&Gl)[K], typename Val<W>::T upGprev,
+                                              typename Val<W>::T& F, typename Val<W>::T& Gup,
+                                              typename Val<W>::T& best) {
+    typedef Val<W> V;
+    typedef typename V::T val_t;
+    constexpr bool ADDPATH = TDADD || (W == 32);
+    constexpr bool SHORTF = (W == 16);        // the host sends ext > open to the 32-bit rung
+    const val_t NEGEXT = C.NEGEXT, NEGOPEN = C.NEGOPEN, PNEGOPEN = C.PNEGOPEN, FLOOR = C.FLOOR;
+    const unsigned one = C.one;
+    const int8_t* pa = prof + t0 * P.pitch + rowbase;
+    const int8_t* pb = prof + t1 * P.pitch + rowbase;
+    // ---- sweep 1, bottom-up: E and M = max(Hdiag + S, E [, 0]); rows are
+    // independent and M overwrites the previous column's G in place
+#pragma unroll
+    for (int c = K / 4 - 1; c >= 0; --c) {
+        uint32_t wa = 0, wb = 0;
+        int4 sw = make_int4(0, 0, 0, 0);
+        if (WIDE) {
+            sw = __ldg(reinterpret_cast<const int4*>(P.wprofile + (size_t)t0 * P.pitch + rowbase) + c);
+        } else if (PSMEM) {
+            wa = *reinterpret_cast<const uint32_t*>(pa + 4 * c);
+            if (W == 16) wb = *reinterpret_cast<const uint32_t*>(pb + 4 * c);
+        } else {
+            wa = __ldg(reinterpret_cast<const uint32_t*>(pa + 4 * c));
+            if (W == 16) wb = __ldg(reinterpret_cast<const uint32_t*>(pb + 4 * c));
+        }
+#pragma unroll
+        for (int u = 3; u >= 0; --u) {
+            const int r = 4 * c + u;
+            val_t S;
+            if (WIDE) S = (val_t)(u == 0 ? sw.x : u == 1 ? sw.y : u == 2 ? sw.z : sw.w);
+            else if (W == 16) S = (val_t)widen_pair(wa, wb, u);
+            else S = (val_t)widen_one(wa, u);
+            const val_t Gd = (r == 0) ? upGprev : Gl[r - 1];
+            E[r] = V::addmax(E[r], NEGEXT, Gl[r]);   // max(E - ext, Hleft - open)
+            val_t M;
+            if (ADDPATH) {
+                const val_t Td = V::add(Gd, S, one);     // Hdiag + S  (S carries the +open)
+                M = LOCAL ? V::max3(Td, E[r], FLOOR) : V::max2(Td, E[r]);
+            } else {
+                M = V::addmax(Gd, S, E[r]);
+                if (LOCAL && SHORTF) M = V::max2(M, FLOOR);
+            }
+            if (SHORTF) {
+                // F never sets a new maximum, so the running best only looks at M
+                if (LOCAL) best = V::max2(best, M);
+                Gl[r] = V::add(M, NEGOPEN, one);         // M - open
+            } else {
+                Gl[r] = M;
+            }
+        }
+    }
+    // ---- sweep 2, top-down: the F chain, H, G = H - open
+    if (SHORTF) {
+        // ext <= open: F(r+1) = max(F(r) - ext, M(r) - open) does not need H(r), so the
+        // serial chain is one instruction per row; G(r) = max(M(r) - open, F(r) - open)
+        F = V::addmax(F, NEGEXT, Gup);               // F(0) = max(Fup - ext, Hup - open)
+#pragma unroll
+        for (int r = 0; r < K; ++r) {
+            const val_t MO = Gl[r];
+            Gup = V::addmax(F, PNEGOPEN, MO);        // G(r) = max(F(r), M(r)) - open
+            Gl[r] = Gup;
+            if (r < K - 1) F = V::addmax(F, NEGEXT, MO);   // F(r+1)
+        }
+    } else {
+#pragma unroll
+        for (int r = 0; r < K; ++r) {
+            F = V::addmax(F, NEGEXT, Gup);               // max(F - ext, Hup - open)
+            const val_t Hn = (LOCAL && !ADDPATH) ? V::max3(Gl[r], F, FLOOR) : V::max2(Gl[r], F);
+            if (LOCAL) best = V::max2(best, Hn);
+            Gup = V::add(Hn, NEGOPEN, one);
+            Gl[r] = Gup;
+        }
+    }
+}
+
 // TDADD: every profile entry (S + open, padding included) is >= 0, so the
 // 16-bit rung may form Hdiag + S with a 32-bit IMAD; otherwise that add stays
 // in the packed adder of VIADDMNMX.  (Ignored by the 32-bit rung.)
@@ -166,8 +268,6 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
     static_assert(!WIDE || (W == 32 && !PSMEM), "wide profile: 32-bit rung, global memory only");
     typedef Val<W> V;
     typedef typename V::T val_t;
-    constexpr bool ADDPATH = TDADD || (W == 32);
-    constexpr bool SHORTF = (W == 16);        // the host sends ext > open to the 32-bit rung
     extern __shared__ __align__(16) unsigned char smem_raw[];
 
     const int nwork = *P.nwork;
@@ -198,12 +298,9 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
     const bool top_free = (P.mode != MODE_NW);
     const bool left_free = (P.mode == MODE_OV || P.mode == MODE_SW);
     const int B = P.bias;
-    const unsigned one = P.one;
-    const val_t NEGEXT = V::pdelta(-P.ge);    // packed adder of VIADDMNMX
-    const val_t NEGOPEN = V::delta(-P.go);    // 32-bit adder (IMAD)
-    const val_t PNEGOPEN = V::pdelta(-P.go);  // packed adder
-    const val_t NEG = V::splat(P.neg + B);
-    const val_t FLOOR = V::splat(B);          // local alignment: H >= 0
+    CellConsts<W> C;
+    C.init(P);
+    const val_t NEG = C.NEG, FLOOR = C.FLOOR;
     const int lastpass = P.npass - 1;
 
     for (;;) {
@@ -287,72 +384,8 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
                 if (active) {
                     const unsigned t0 = (W == 16) ? (code & 0xffu) : (half ? (code >> 8) : (code & 0xffu));
                     const unsigned t1 = code >> 8;
-                    const int8_t* pa = prof + t0 * P.pitch + rowbase;
-                    const int8_t* pb = prof + t1 * P.pitch + rowbase;
-                    // ---- sweep 1, bottom-up: E and M = max(Hdiag + S, E [, 0]); rows are
-                    // independent and M overwrites the previous column's G in place
-#pragma unroll
-                    for (int c = K / 4 - 1; c >= 0; --c) {
-                        uint32_t wa = 0, wb = 0;
-                        int4 sw = make_int4(0, 0, 0, 0);
-                        if (WIDE) {
-                            sw = __ldg(reinterpret_cast<const int4*>(P.wprofile + (size_t)t0 * P.pitch + rowbase) + c);
-                        } else if (PSMEM) {
-                            wa = *reinterpret_cast<const uint32_t*>(pa + 4 * c);
-                            if (W == 16) wb = *reinterpret_cast<const uint32_t*>(pb + 4 * c);
-                        } else {
-                            wa = __ldg(reinterpret_cast<const uint32_t*>(pa + 4 * c));
-                            if (W == 16) wb = __ldg(reinterpret_cast<const uint32_t*>(pb + 4 * c));
-                        }
-#pragma unroll
-                        for (int u = 3; u >= 0; --u) {
-                            const int r = 4 * c + u;
-                            val_t S;
-                            if (WIDE) S = (val_t)(u == 0 ? sw.x : u == 1 ? sw.y : u == 2 ? sw.z : sw.w);
-                            else if (W == 16) S = (val_t)widen_pair(wa, wb, u);
-                            else S = (val_t)widen_one(wa, u);
-                            const val_t Gd = (r == 0) ? upGprev : Gl[r - 1];
-                            E[r] = V::addmax(E[r], NEGEXT, Gl[r]);   // max(E - ext, Hleft - open)
-                            val_t M;
-                            if (ADDPATH) {
-                                const val_t Td = V::add(Gd, S, one);     // Hdiag + S  (S carries the +open)
-                                M = LOCAL ? V::max3(Td, E[r], FLOOR) : V::max2(Td, E[r]);
-                            } else {
-                                M = V::addmax(Gd, S, E[r]);
-                                if (LOCAL && SHORTF) M = V::max2(M, FLOOR);
-                            }
-                            if (SHORTF) {
-                                // F never sets a new maximum, so the running best only looks at M
-                                if (LOCAL) best = V::max2(best, M);
-                                Gl[r] = V::add(M, NEGOPEN, one);         // M - open
-                            } else {
-                                Gl[r] = M;
-                            }
-                        }
-                    }
-                    // ---- sweep 2, top-down: the F chain, H, G = H - open
                     val_t F = upF, Gup = upG;
-                    if (SHORTF) {
-                        // ext <= open: F(r+1) = max(F(r) - ext, M(r) - open) does not need H(r), so the
-                        // serial chain is one instruction per row; G(r) = max(M(r) - open, F(r) - open)
-                        F = V::addmax(F, NEGEXT, Gup);               // F(0) = max(Fup - ext, Hup - open)
-#pragma unroll
-                        for (int r = 0; r < K; ++r) {
-                            const val_t MO = Gl[r];
-                            Gup = V::addmax(F, PNEGOPEN, MO);        // G(r) = max(F(r), M(r)) - open
-                            Gl[r] = Gup;
-                            if (r < K - 1) F = V::addmax(F, NEGEXT, MO);   // F(r+1)
-                        }
-                    } else {
-#pragma unroll
-                        for (int r = 0; r < K; ++r) {
-                            F = V::addmax(F, NEGEXT, Gup);               // max(F - ext, Hup - open)
-                            const val_t Hn = (LOCAL && !ADDPATH) ? V::max3(Gl[r], F, FLOOR) : V::max2(Gl[r], F);
-                            if (LOCAL) best = V::max2(best, Hn);
-                            Gup = V::add(Hn, NEGOPEN, one);
-                            Gl[r] = Gup;
-                        }
-                    }
+                    column_update<K, W, LOCAL, PSMEM, WIDE, TDADD>(P, prof, t0, t1, rowbase, C, E, Gl, upGprev, F, Gup, best);
                     Gout = Gup;
                     Fout = F;
                     upGprev = upG;
@@ -433,5 +466,8 @@ search_kernel_t get_search_kernel_w16_l0(int K, bool psmem, bool tdadd);
 search_kernel_t get_search_kernel_w32_l1(int K, bool psmem);
 search_kernel_t get_search_kernel_w32_l0(int K, bool psmem);
 search_kernel_t get_search_kernel_wide(bool local);  // K = 32, W = 32
+// giant.cu: a team of warps per target (KParams.G = warps per team, KParams.npass = teams per CTA), K = 4 or 8
+search_kernel_t get_giant_kernel(int K, bool local);
+size_t giant_smem_bytes(int A, int pitch, int warps_per_team, int teams);
 
 }  // namespace pyopal
