@@ -297,23 +297,58 @@ Plan finish_plan(Plan p, int Lq, int A, size_t smem_limit) {
 // length and the store's mean target length.  Per column step a thread issues
 // about C0 instructions of bookkeeping plus C1 per row; a target of L columns
 // takes L + G - 1 steps per pass.
-Plan make_plan(int Lq, int A, double mean_cols, size_t smem_limit) {
+//
+// Critical path: a pair of L columns is walked by ONE group of G lanes, pass
+// after pass, while about 448 / G groups per SM share the machine (14 resident
+// warps).  Its solo time equals the whole search's when
+//     L = L_even(G) = ncols * G / (448 * SMs)          (independent of K)
+// so a small shard (many GPUs) or a long query needs wide groups.  Pairs
+// longer than 0.6 * L_even go to the giant kernel when it is available (at
+// most `giant_cap` of them); what remains above L_even stretches the search
+// by len / L_even and is charged to the tile.
+struct GiantPolicy {
+    bool ok = false;        // giant kernel usable for this query
+    int64_t cap = 0;        // most pairs it may take
+    double col_cost = 0;    // SM time of one giant target column, in the tile cost model's units
+    int64_t kg = 0;         // out: pairs [0, kg) go to the giant kernel
+};
+
+Plan make_plan(int Lq, int A, const pyopal_cuda_db* db, size_t smem_limit, GiantPolicy* gp) {
     const double C0 = 28.0, C1 = 6.5;
+    const double mean_cols = db->mean_cols;
     Plan best;
     double best_cost = 1e300;
+    int64_t best_kg = 0;
     for (int logG = 2; logG <= 5; logG++) {
         const int G = 1 << logG;
+        const double L_even = (double)db->ncols * G / (448.0 * db->sm_count);
+        int64_t kg = 0;
+        double giant_cols = 0;
+        if (gp && gp->ok) {
+            const double gthr = std::max(1024.0, 0.6 * L_even);
+            while (kg < gp->cap && kg < db->npairs && (double)db->h_pair_len[(size_t)(2 * kg)] > gthr) {
+                giant_cols += (double)db->h_pair_len[(size_t)(2 * kg)] + (double)db->h_pair_len[(size_t)(2 * kg + 1)];
+                kg++;
+            }
+        }
+        // the giants hold whole SMs at a fraction of the bulk kernel's efficiency
+        const double giant_cost = giant_cols * (gp ? gp->col_cost : 0.0) / std::max<double>(1.0, (double)db->npairs);
+        const double longest_bulk = kg < db->npairs ? (double)db->h_pair_len[(size_t)(2 * kg)] : 0.0;
+        const double stretch = std::max(1.0, longest_bulk / std::max(L_even, 1.0));
         for (int K = 4; K <= 40; K += 4) {
             const int T = G * K;
             const int npass = (Lq + T - 1) / T;
             // several passes also pay the boundary round trip through L2 every step
-            const double cost = (double)npass * (mean_cols + G - 1) * (C0 + (npass > 1 ? 12.0 : 0.0) + C1 * K) * (double)G;
+            const double cost = stretch * (double)npass * (mean_cols + G - 1) * (C0 + (npass > 1 ? 12.0 : 0.0) + C1 * K) * (double)G +
+                                giant_cost;
             if (cost < best_cost - 1e-9) {
                 best_cost = cost;
                 best.G = G; best.logG = logG; best.K = K; best.npass = npass;
+                best_kg = kg;
             }
         }
     }
+    if (gp) gp->kg = best_kg;
     best = finish_plan(best, Lq, A, smem_limit);
     return best;
 }
@@ -463,7 +498,25 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
 
     // ---- plans -------------------------------------------------------------
     const size_t SMEM_LIMIT = (size_t)200 * 1024;
-    Plan bulk = make_plan(Lq, A, db->mean_cols, SMEM_LIMIT);
+    // giants: the longest targets get a team of warps each (giant.cu), 32 bit; needs the int8
+    // profile of the whole query in shared memory
+    GiantPolicy gpol;
+    int gK = 4, gwarps = 1, gteams = 1, gpitch = 0;
+    size_t gsmem = 0;
+    if (make_rung(M, A, go, ge, mode, 0).fits8 && Lq <= 8192 && !getenv("PYOPAL_CUDA_NO_GIANT")) {
+        gK = (Lq <= 2048) ? 4 : (Lq <= 4096) ? 8 : 16;            // rows per lane
+        gwarps = ((Lq + gK - 1) / gK + 31) / 32;                  // warps per team (<= 16): the whole query in one pass
+        gteams = (gwarps == 1) ? 16 : std::min(15, 16 / gwarps);  // teams per 512-thread CTA (15 named barriers)
+        gpitch = (gwarps * 32 * gK + 15) / 16 * 16;
+        gsmem = giant_smem_bytes(A, gpitch, gwarps, gteams);
+        gpol.ok = gsmem <= SMEM_LIMIT + 24 * 1024;
+        gpol.cap = (int64_t)db->sm_count * 8;
+        // one SM clock ~ 56 cost units (calibrated on config 2); a team advances one column in about
+        // 36 clocks per row held by a lane, 1.6 x that when the wavefront crosses warps
+        const int teams_now = (gwarps == 1) ? 16 : std::max(1, 16 / gwarps);
+        gpol.col_cost = 56.0 * 36.0 * gK * (gwarps > 1 ? 1.6 : 1.0) / teams_now;
+    }
+    Plan bulk = make_plan(Lq, A, db, SMEM_LIMIT, &gpol);
     Plan tail = make_tail_plan(Lq, A, SMEM_LIMIT);
     int smax = INT_MIN, smin = INT_MAX;
     for (int i = 0; i < A * A; i++) { smax = std::max(smax, M[i]); smin = std::min(smin, M[i]); }
@@ -509,26 +562,13 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
         const double step_latency = 12.0 * bulk.K + 80.0;
         thr = std::max(256.0, ideal_cycles / 4.0 / (bulk.npass * step_latency));
     }
-    // ---- giants: the longest targets get a whole CTA each (giant.cu), 32 bit ----
-    // [0, kg) pairs; needs the int8 profile of the whole query in shared memory
-    int64_t kg = 0;
-    int gK = 4, gwarps = 1, gteams = 1, gpitch = 0;
-    size_t gsmem = 0;
-    if (!wide && Lq <= 8192 && !getenv("PYOPAL_CUDA_NO_GIANT")) {
-        gK = (Lq <= 2048) ? 4 : (Lq <= 4096) ? 8 : 16;            // rows per lane
-        gwarps = ((Lq + gK - 1) / gK + 31) / 32;                  // warps per team (<= 16): the whole query in one pass
-        gteams = (gwarps == 1) ? 16 : std::min(15, 16 / gwarps);  // teams per 512-thread CTA (15 named barriers)
-        gpitch = (gwarps * 32 * gK + 15) / 16 * 16;
-        gsmem = giant_smem_bytes(A, gpitch, gwarps, gteams);
-        if (gsmem <= SMEM_LIMIT + 24 * 1024) {
-            const double gthr = std::max(thr, 1024.0);
-            const int64_t cap = std::min<int64_t>(db->npairs, (int64_t)db->sm_count * 2);
-            while (kg < cap && (double)db->h_pair_len[(size_t)(2 * kg)] > gthr) kg++;
-        }
-    }
+    // ---- giants: pairs [0, kg), chosen with the tile (make_plan) ----
+    const bool giants_ok = gpol.ok && bulk.psmem && !wide;
+    const int64_t kg = giants_ok ? gpol.kg : 0;
     n32p = std::max(n32p, kg);
     tail_end = n32p;
-    if (!same_plan) {
+    // the one-warp-per-pair tail kernel only remains for queries the giant kernel cannot take
+    if (!same_plan && !giants_ok) {
         int64_t lo = n32p, hi = db->npairs;
         while (lo < hi) {
             int64_t mid = (lo + hi) / 2;
