@@ -106,6 +106,17 @@ def test_sw_overflow_escalation(cuda, oracle):
     assert 32767 < got[1] < 65535
 
 
+@pytest.mark.parametrize("algo", ALGOS)
+@pytest.mark.parametrize("lq", [50, 700, 2500, 4500])
+def test_giant_teams(cuda, oracle, algo, lq):
+    # a few long targets in a small database go to giant.cu: one warp (Lq 50), a team of 6 warps with
+    # 4 rows per lane (700), 8 rows (2500), 16 rows (4500); lengths not multiples of the 4-column block
+    seqs = synthetic.as_sequences(synthetic.database(71, 400, 5.0, 0.6, 1, 1500, giants=(5003, 4001, 3002, 2999)))
+    aligner = pyopal.Aligner("BLOSUM62", 11, 1)
+    db = check(oracle, aligner, rand_query(70 + lq, lq), seqs, algo)
+    assert db._device_store().stats()["targets32"] >= 4
+
+
 @pytest.mark.parametrize("algo", ("nw", "hw", "ov"))
 def test_static_32bit_rung(cuda, oracle, algo):
     # NW of a short query against 30k+ targets goes below -32768; long identical pairs go above +32767
