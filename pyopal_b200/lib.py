@@ -16,6 +16,15 @@ import threading
 from .matrices import ScoringMatrix, as_scoring_matrix
 from .platform import cuda as _cuda
 
+try:
+    from . import _results
+except ImportError:  # not built yet: compile the host extension in-tree (gcc, one second), then import
+    import os as _os
+    import subprocess as _subprocess
+
+    _subprocess.check_call(["bash", _os.path.join(_os.path.dirname(_os.path.abspath(__file__)), "csrc", "build_host.sh")])
+    from . import _results
+
 __version__ = "0.7.3+b200"
 
 MAX_ALPHABET_SIZE = 32  # lib.pxd:28-32
@@ -554,17 +563,16 @@ class Database(BaseDatabase):
 # --- Results (lib.pyx:783-1119) -----------------------------------------------
 
 
-class ScoreResult:
-    """The results of a search in ``score`` mode."""
+class ScoreResult(_results.ResultBase):
+    """The results of a search in ``score`` mode.
 
-    # defaults of `__cinit__` (lib.pyx:787-795)
-    _target_index = -1
-    _score = None
-    _query_end = -1
-    _target_end = -1
-    _query_start = -1
-    _target_start = -1
-    _alignment = None
+    The fields (the ``OpalSearchResult`` of opal.pxd:26-34 with the defaults of
+    ``__cinit__``, lib.pyx:787-795) live in the C base class
+    ``_results.ResultBase`` (csrc/_results.c), as they live in the Cython
+    extension type of the reference (lib.pxd:113-126).
+    """
+
+    __slots__ = ()
 
     def __init__(self, target_index, score):
         self._target_index = operator.index(target_index)
@@ -600,6 +608,8 @@ class ScoreResult:
 class EndResult(ScoreResult):
     """The results of a search in ``end`` mode."""
 
+    __slots__ = ()
+
     def __init__(self, target_index, score, query_end, target_end):
         super().__init__(target_index, score)
         self._query_end = operator.index(query_end)
@@ -631,8 +641,7 @@ class EndResult(ScoreResult):
 class FullResult(EndResult):
     """The results of a search in ``full`` mode."""
 
-    _query_length = -1
-    _target_length = -1
+    __slots__ = ()
 
     def __init__(
         self,

@@ -367,36 +367,30 @@ def searchCUDA(encoded, database, mode, overflow, algorithm, gap_open, gap_exten
             if r.alignment:
                 libc.free(ctypes.cast(r.alignment, ctypes.c_void_p))
 
+    if oo is not None or mode != OPAL_SEARCH_ALIGNMENT:
+        # arrays straight from the C-ABI: the list is built natively (csrc/_results.c), the
+        # equivalent of the reference's Cython loop at pyx.in:65-72 / 95-99
+        from .. import _results
+
+        lens = None
+        if mode == OPAL_SEARCH_ALIGNMENT:
+            lens = lengths if isinstance(lengths, array.array) else array.array("i", lengths)
+        as_i32 = lambda a: a if a is None or isinstance(a, array.array) else array.array("i", a)
+        return _results.make_results(result_type, mode, start, size, as_i32(scores), as_i32(eq), as_i32(et),
+                                     as_i32(sq), as_i32(st), qlen, lens, ops, oo, as_i32(ol))
+    # generic path in full mode: one bytes object per alignment already
     new = result_type.__new__
     results = [None] * size
-    if mode == OPAL_SEARCH_SCORE:
-        for i in range(size):
-            r = new(result_type)
-            r._target_index = start + i
-            r._score = scores[i]
-            results[i] = r
-    elif mode == OPAL_SEARCH_SCORE_END:
-        for i in range(size):
-            r = new(result_type)
-            r._target_index = start + i
-            r._score = scores[i]
-            r._query_end = eq[i]
-            r._target_end = et[i]
-            results[i] = r
-    else:
-        for i in range(size):
-            r = new(result_type)
-            r._target_index = start + i
-            r._score = scores[i]
-            r._query_end = eq[i]
-            r._target_end = et[i]
-            r._query_start = sq[i]
-            r._target_start = st[i]
-            r._query_length = qlen  # pyx.in:95-99
-            r._target_length = lengths[start + i]
-            if oo is None:
-                r._alignment = ops[i]
-            else:
-                r._alignment = bytes(ops[oo[i] : oo[i] + ol[i]])
-            results[i] = r
+    for i in range(size):
+        r = new(result_type)
+        r._target_index = start + i
+        r._score = scores[i]
+        r._query_end = eq[i]
+        r._target_end = et[i]
+        r._query_start = sq[i]
+        r._target_start = st[i]
+        r._query_length = qlen  # pyx.in:95-99
+        r._target_length = lengths[start + i]
+        r._alignment = ops[i]
+        results[i] = r
     return results

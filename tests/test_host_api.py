@@ -256,3 +256,30 @@ def test_no_cpu_fallback():
         cwd=ROOT, capture_output=True, text=True, check=True,
     )
     assert out.stdout.strip() == "False"
+
+
+def test_native_result_storage():
+    # csrc/_results.c: the C base of the result classes and the bulk list constructor (pyx.in:65-72, 95-99)
+    import array
+
+    from pyopal_b200 import _results
+
+    assert issubclass(pyopal.ScoreResult, _results.ResultBase)
+    blank = pyopal.EndResult.__new__(pyopal.EndResult)
+    assert (blank._target_index, blank._score, blank._query_end, blank._target_end) == (-1, None, -1, -1)  # lib.pyx:787-795
+    assert not hasattr(blank, "__dict__")
+    scores = array.array("i", [7, -3, 0])
+    res = _results.make_results(pyopal.ScoreResult, 0, 10, 3, scores, None, None, None, None, 5, None, None, None, None)
+    assert [(r.target_index, r.score) for r in res] == [(10, 7), (11, -3), (12, 0)]
+    assert res[0] == pyopal.ScoreResult(10, 7) and repr(res[1]) == "ScoreResult(11, score=-3)"
+    ops = bytearray(b"\x00\x00\x03\x01\x02\x00")
+    full = _results.make_results(
+        pyopal.FullResult, 2, 1, 2, array.array("i", [5, 6]), array.array("i", [1, 2]), array.array("i", [3, 4]),
+        array.array("i", [0, 0]), array.array("i", [0, 1]), 7, array.array("i", [9, 8, 7]), ops,
+        array.array("q", [0, 3]), array.array("i", [3, 3]))
+    assert full[0] == pyopal.FullResult(1, 5, 1, 3, 0, 0, 7, 8, "MMX")
+    assert full[1].alignment == "DIM" and full[1].target_length == 7 and full[1].query_length == 7
+    with pytest.raises(ValueError):
+        _results.make_results(pyopal.ScoreResult, 0, 0, 4, scores, None, None, None, None, 5, None, None, None, None)
+    with pytest.raises(TypeError):
+        _results.make_results(int, 0, 0, 3, scores, None, None, None, None, 5, None, None, None, None)
