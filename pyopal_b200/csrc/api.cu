@@ -277,7 +277,7 @@ extern "C" int pyopal_cuda_db_create_from_pointers(int device, const unsigned ch
 namespace {
 
 struct Plan {
-    int G = 32, logG = 5, K = 32, npass = 1, pitch = 0, padtop = 0;
+    int G = 32, logG = 5, K = 32, npass = 1, pitch = 0, padtop = 0, kstride = 32;
     bool psmem = true;
     size_t smem = 0;
 };
@@ -285,7 +285,8 @@ struct Plan {
 Plan finish_plan(Plan p, int Lq, int A, size_t smem_limit) {
     const int T = p.G * p.K;
     p.npass = (Lq + T - 1) / T;
-    p.pitch = (p.npass * T + 15) / 16 * 16;
+    p.kstride = ((p.K / 4) % 2 == 0) ? p.K + 4 : p.K;  // odd number of words per lane chunk (kernels.cuh)
+    p.pitch = (p.npass * p.G * p.kstride + 15) / 16 * 16;
     p.padtop = p.npass * T - Lq;
     p.smem = (size_t)(A + 1) * (size_t)p.pitch;
     p.psmem = p.smem <= smem_limit;
@@ -346,6 +347,12 @@ Plan make_plan(int Lq, int A, const pyopal_cuda_db* db, size_t smem_limit, Giant
                 best.G = G; best.logG = logG; best.K = K; best.npass = npass;
                 best_kg = kg;
             }
+        }
+    }
+    if (const char* ov = getenv("PYOPAL_CUDA_PLAN")) {  // "logG,K[,threads]": tuning override
+        int lg = 0, k = 0;
+        if (sscanf(ov, "%d,%d", &lg, &k) == 2 && lg >= 2 && lg <= 5 && k >= 4 && k <= 40 && k % 4 == 0) {
+            best.G = 1 << lg; best.logG = lg; best.K = k; best.npass = (Lq + best.G * k - 1) / (best.G * k);
         }
     }
     if (gp) gp->kg = best_kg;
@@ -450,6 +457,7 @@ int launch_search(pyopal_cuda_db* db, search_kernel_t fn, const KParams& P, size
 
 void apply_plan(KParams& P, const Plan& pl) {
     P.G = pl.G; P.logG = pl.logG; P.npass = pl.npass; P.pitch = pl.pitch; P.padtop = pl.padtop;
+    P.krows = pl.K; P.kstride = pl.kstride;
 }
 
 // Enqueue a SCORE search of [start, end) on `st`; scores land in d_out (device).
@@ -507,7 +515,7 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
         gK = (Lq <= 2048) ? 4 : (Lq <= 4096) ? 8 : 16;            // rows per lane
         gwarps = ((Lq + gK - 1) / gK + 31) / 32;                  // warps per team (<= 16): the whole query in one pass
         gteams = (gwarps == 1) ? 16 : std::min(15, 16 / gwarps);  // teams per 512-thread CTA (15 named barriers)
-        gpitch = (gwarps * 32 * gK + 15) / 16 * 16;
+        gpitch = (gwarps * 32 * (gK + 4) + 15) / 16 * 16;         // gK = 4, 8, 16 words-even: chunks of gK + 4 bytes
         gsmem = giant_smem_bytes(A, gpitch, gwarps, gteams);
         gpol.ok = gsmem <= SMEM_LIMIT + 24 * 1024;
         gpol.cap = (int64_t)db->sm_count * 8;
@@ -679,6 +687,7 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
         // a few teams per CTA keep the column chains short; more CTAs than that would only idle SMs
         const int teams = (int)std::max<int64_t>(1, std::min<int64_t>(gteams, (ng + 7) / 8));
         Q.G = gwarps; Q.logG = 0; Q.npass = teams; Q.pitch = gpitch; Q.padtop = gwarps * 32 * gK - Lq;
+        Q.krows = gK; Q.kstride = (gK == 4) ? 4 : gK + 4;
         Q.worklist = db->wl32.p + n32; Q.nwork = db->d_counts + 8; Q.counter = db->d_counts + 9;
         Q.neg = -(1 << 29);
         // ask for the whole SM's shared memory: no throughput CTA may share the SM with the giants (giant.cu)
@@ -729,7 +738,11 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
             const int gpw = 32 >> bulk.logG;
             // one CTA per SM when the profile is large: use the whole register file with 16 warps
             // (with side-stream CTAs resident, 7-warp CTAs leave them registers: 2 x 224 x 128 < 64K)
-            const int threads = (bulk.smem > (size_t)110 * 1024) ? (side_work ? 480 : 512) : (side_work ? 224 : 256);
+            int threads = (bulk.smem > (size_t)110 * 1024) ? (side_work ? 480 : 512) : (side_work ? 224 : 256);
+            if (const char* ov = getenv("PYOPAL_CUDA_PLAN")) {
+                int lg = 0, k = 0, t = 0;
+                if (sscanf(ov, "%d,%d,%d", &lg, &k, &t) == 3 && t >= 32 && t <= 512 && t % 32 == 0) threads = t;
+            }
             CU(cudaEventRecord(db->kev[2], st));
             int rc = launch_search(db, kb, Q, bulk.smem, threads, (nw + gpw - 1) / gpw, st);
             if (rc) return rc;

@@ -202,7 +202,7 @@ __global__ void __launch_bounds__(512, 1) giant_kernel(const __grid_constant__ K
                 for (int c = 0; c < C; ++c) {
                     const unsigned t0 = (cw[c >> 1] >> (16 * (c & 1) + 8 * half)) & 0xffu;
                     int F = upF[c], Gup = upG[c];
-                    column_update<K, 32, LOCAL, true, false, true>(P, sp, t0, 0u, rowbase, CC, E, Gl, upGprev, F, Gup, best);
+                    column_update<K, 32, LOCAL, true, false, true>(P, sp, t0, 0u, ttid * P.kstride, CC, E, Gl, upGprev, F, Gup, best);
                     Gout[c] = Gup;
                     Fout[c] = F;
                     upGprev = upG[c];

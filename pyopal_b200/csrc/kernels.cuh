@@ -60,6 +60,7 @@ struct KParams {
     const int32_t* wprofile;  // int32 global profile for matrices / gap costs outside the int8 range
     int Lq, A, go, ge;
     int G, logG, npass, pitch, padtop;
+    int krows, kstride;       // profile layout: a lane's K rows occupy kstride >= K bytes (odd number of words)
     int mode;
     int neg;                  // "-infinity" for this rung (true value; stored as neg + bias)
     int bias;                 // W=16: values are stored as value + bias in each u16 half; W=32: 0
@@ -118,13 +119,21 @@ template <> struct Val<32> {
     static __device__ __forceinline__ int hi(T v) { return v; }
 };
 
-// Profile: prof[letter * pitch + tile_row], letter in [0, A] (A = padding
-// letter), tile_row in [0, npass*G*K).  Entry = S[q][letter] + gap_open so the
+// Profile: prof[letter * pitch + slot], letter in [0, A] (A = padding letter).
+// The tile rows are stored lane chunk by lane chunk: chunk q = tile rows
+// [q * krows, (q + 1) * krows) starts at slot q * kstride, where kstride is
+// krows or krows + 4 so that a chunk is an ODD number of 32-bit words -- the
+// lanes of a group then read their chunks of one letter from distinct banks
+// (with kstride = K = 32 the 32 lanes of a group hit only 4 banks: measured
+// 20 % slower than K = 28 or 36).  Entry = S[q][letter] + gap_open so the
 // kernel can keep H-open instead of H (one subtract per cell feeds both E and
 // F).  Tile rows < padtop are padding ABOVE the query: with a free top border
 // (HW/OV/SW) score 0 keeps them at H = 0; with NW's penalised border a score
 // of -max(open, ext) makes each of them reproduce the border row exactly.
-__device__ __forceinline__ int profile_entry(const KParams& P, int letter, int trow) {
+__device__ __forceinline__ int profile_entry(const KParams& P, int letter, int slot) {
+    const int chunk = slot / P.kstride, within = slot - chunk * P.kstride;
+    if (within >= P.krows) return 0;  // bank padding, never read
+    const int trow = chunk * P.krows + within;
     int qi = trow - P.padtop;
     if (qi < 0 || letter >= P.A) return P.pad_score;
     return P.matrix[(int)P.query[qi] * P.A + letter] + P.go;
@@ -181,7 +190,7 @@ template <int W> struct CellConsts {
 // F / Gup = (F, H - open) of the row above in this column.  Out: E, Gl of this
 // column, F / Gup of the thread's last row (for the thread below), best.
 template <int K, int W, bool LOCAL, bool PSMEM, bool WIDE, bool TDADD>
-__device__ __forceinline__ void column_update(const KParams& P, const int8_t* prof, unsigned t0, unsigned t1, int rowbase,
+__device__ __forceinline__ void column_update(const KParams& P, const int8_t* prof, unsigned t0, unsigned t1, int pslot,
                                               const CellConsts<W>& C, typename Val<W>::T (&E)[K],
                                               typename Val<W>::T (&Gl)[K], typename Val<W>::T upGprev,
                                               typename Val<W>::T& F, typename Val<W>::T& Gup,
@@ -192,8 +201,8 @@ __device__ __forceinline__ void column_update(const KParams& P, const int8_t* pr
     constexpr bool SHORTF = (W == 16);        // the host sends ext > open to the 32-bit rung
     const val_t NEGEXT = C.NEGEXT, NEGOPEN = C.NEGOPEN, PNEGOPEN = C.PNEGOPEN, FLOOR = C.FLOOR;
     const unsigned one = C.one;
-    const int8_t* pa = prof + t0 * P.pitch + rowbase;
-    const int8_t* pb = prof + t1 * P.pitch + rowbase;
+    const int8_t* pa = prof + t0 * P.pitch + pslot;   // pslot: first profile slot of this lane's chunk
+    const int8_t* pb = prof + t1 * P.pitch + pslot;
     // ---- sweep 1, bottom-up: E and M = max(Hdiag + S, E [, 0]); rows are
     // independent and M overwrites the previous column's G in place
 #pragma unroll
@@ -201,7 +210,7 @@ __device__ __forceinline__ void column_update(const KParams& P, const int8_t* pr
         uint32_t wa = 0, wb = 0;
         int4 sw = make_int4(0, 0, 0, 0);
         if (WIDE) {
-            sw = __ldg(reinterpret_cast<const int4*>(P.wprofile + (size_t)t0 * P.pitch + rowbase) + c);
+            sw = __ldg(reinterpret_cast<const int4*>(P.wprofile + (size_t)t0 * P.pitch + pslot) + c);
         } else if (PSMEM) {
             wa = *reinterpret_cast<const uint32_t*>(pa + 4 * c);
             if (W == 16) wb = *reinterpret_cast<const uint32_t*>(pb + 4 * c);
@@ -385,7 +394,7 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
                     const unsigned t0 = (W == 16) ? (code & 0xffu) : (half ? (code >> 8) : (code & 0xffu));
                     const unsigned t1 = code >> 8;
                     val_t F = upF, Gup = upG;
-                    column_update<K, W, LOCAL, PSMEM, WIDE, TDADD>(P, prof, t0, t1, rowbase, C, E, Gl, upGprev, F, Gup, best);
+                    column_update<K, W, LOCAL, PSMEM, WIDE, TDADD>(P, prof, t0, t1, (pass * G + p) * P.kstride, C, E, Gl, upGprev, F, Gup, best);
                     Gout = Gup;
                     Fout = F;
                     upGprev = upG;
