@@ -8,6 +8,8 @@
 #include "store.h"
 
 #include <algorithm>
+#include <atomic>
+#include <thread>
 #include <climits>
 #include <cstdio>
 #include <cstdlib>
@@ -199,25 +201,55 @@ static int db_build(int device, GetSeq get_seq, const int32_t* lengths, int64_t 
                 k2++;
             }
             const int64_t endc = (k2 < npairs) ? db->h_pair_off[(size_t)k2] : ncols;
-            for (int64_t q = k; q < k2; q++) {
-                uint16_t* dst = stage + (db->h_pair_off[(size_t)q] - base);
-                const int la = db->h_pair_len[(size_t)(2 * q)], lb = db->h_pair_len[(size_t)(2 * q + 1)];
-                const unsigned char* sa = get_seq(db->h_pair_idx[(size_t)(2 * q)]);
-                const unsigned char* sb = lb > 0 ? get_seq(db->h_pair_idx[(size_t)(2 * q + 1)]) : nullptr;
-                int c = 0;
+            // interleave the pairs of this chunk on several host threads (205 MB of residues for config 2)
+            std::atomic<unsigned> bad_any{0};
+            auto fill = [&](int64_t q0, int64_t q1) {
                 unsigned bad = 0;  // residues must index the profile: < A
-                for (; c < lb; c++) {
-                    bad |= (unsigned)(sa[c] >= A) | (unsigned)(sb[c] >= A);
-                    dst[c] = (uint16_t)(sa[c] | (sb[c] << 8));
+                for (int64_t q = q0; q < q1; q++) {
+                    uint16_t* dst = stage + (db->h_pair_off[(size_t)q] - base);
+                    const int la = db->h_pair_len[(size_t)(2 * q)], lb = db->h_pair_len[(size_t)(2 * q + 1)];
+                    const unsigned char* sa = get_seq(db->h_pair_idx[(size_t)(2 * q)]);
+                    const unsigned char* sb = lb > 0 ? get_seq(db->h_pair_idx[(size_t)(2 * q + 1)]) : nullptr;
+                    int c = 0;
+                    for (; c < lb; c++) {
+                        bad |= (unsigned)(sa[c] >= A) | (unsigned)(sb[c] >= A);
+                        dst[c] = (uint16_t)(sa[c] | (sb[c] << 8));
+                    }
+                    for (; c < la; c++) {
+                        bad |= (unsigned)(sa[c] >= A);
+                        dst[c] = (uint16_t)(sa[c] | (A << 8));
+                    }
+                    const int padded = (la + PAD_ALIGN_COLS - 1) / PAD_ALIGN_COLS * PAD_ALIGN_COLS;
+                    for (; c < padded; c++) dst[c] = PADPAIR;
                 }
-                for (; c < la; c++) {
-                    bad |= (unsigned)(sa[c] >= A);
-                    dst[c] = (uint16_t)(sa[c] | (A << 8));
+                if (bad) bad_any.store(1);
+            };
+            {
+                const int64_t npq = k2 - k;
+                unsigned nth = std::min<unsigned>(16u, std::max(1u, std::thread::hardware_concurrency()));
+                if ((endc - base) < ((int64_t)1 << 20)) nth = 1;
+                if (nth <= 1) {
+                    fill(k, k2);
+                } else {
+                    // pairs are sorted by length: deal contiguous ranges of about equal column count
+                    std::vector<std::thread> pool;
+                    int64_t q0 = k;
+                    for (unsigned t = 0; t < nth && q0 < k2; t++) {
+                        const int64_t want = base + (endc - base) * (int64_t)(t + 1) / nth;
+                        int64_t q1 = (t + 1 == nth) ? k2
+                                                    : std::upper_bound(db->h_pair_off.begin() + q0, db->h_pair_off.begin() + k2, want) -
+                                                          db->h_pair_off.begin();
+                        q1 = std::max(q1, q0 + (t + 1 == nth ? 0 : 1));
+                        q1 = std::min(q1, k2);
+                        pool.emplace_back(fill, q0, q1);
+                        q0 = q1;
+                    }
+                    if (q0 < k2) fill(q0, k2);
+                    for (auto& th : pool) th.join();
                 }
-                if (bad) rc = fail(PYOPAL_CUDA_ERR_ARGUMENT, "residue code outside the alphabet");
-                const int padded = (la + PAD_ALIGN_COLS - 1) / PAD_ALIGN_COLS * PAD_ALIGN_COLS;
-                for (; c < padded; c++) dst[c] = PADPAIR;
+                (void)npq;
             }
+            if (bad_any.load()) rc = fail(PYOPAL_CUDA_ERR_ARGUMENT, "residue code outside the alphabet");
             cudaError_t e = cudaMemcpy(db->d_stream + base, stage, (size_t)(endc - base) * sizeof(uint16_t),
                                        cudaMemcpyHostToDevice);
             if (e != cudaSuccess) rc = fail(PYOPAL_CUDA_ERR_CUDA, std::string("stream upload: ") + cudaGetErrorString(e));

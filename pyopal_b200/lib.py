@@ -393,6 +393,97 @@ class Database(BaseDatabase):
     def _encode(self, sequence):
         return self.alphabet.encode(sequence)
 
+    # --- Bulk ingest and persistence (additive) ---
+    #
+    # The reference appends one sequence at a time: a Python call, an encode
+    # and a heap allocation each (lib.pyx:596-636), and pickling re-appends the
+    # decoded strings one by one (lib.pyx:496-497).  These constructors take
+    # whole buffers instead.
+
+    _MAGIC = b"PYOPALDB1\n"
+
+    @classmethod
+    def from_packed(cls, residues, lengths, alphabet=None, encoded=True):
+        """Build a database from one packed buffer and the sequence lengths.
+
+        ``residues`` holds the sequences back to back: alphabet indices when
+        ``encoded`` is true, ASCII letters otherwise (translated in one call).
+        """
+        self = cls((), alphabet)
+        data = bytes(residues) if encoded else self.alphabet.encode(bytes(residues))
+        lens = [operator.index(n) for n in lengths]
+        if any(n < 0 for n in lens) or sum(lens) != len(data):
+            raise ValueError("lengths do not add up to the size of the residue buffer")
+        if encoded and data and max(data) >= self.alphabet.length:
+            raise ValueError("residue code outside the alphabet")
+        seqs = []
+        pos = 0
+        for n in lens:
+            seqs.append(data[pos : pos + n])
+            pos += n
+        with self.lock.write:
+            self._sequences = seqs
+            self._lengths = lens
+            self._touch()
+        return self
+
+    @classmethod
+    def from_fasta(cls, file, alphabet=None):
+        """Read every record of a FASTA file (path or binary file object); returns ``(database, names)``."""
+        if hasattr(file, "read"):
+            blob = file.read()
+        else:
+            with open(file, "rb") as handle:
+                blob = handle.read()
+        if isinstance(blob, str):
+            blob = blob.encode("ascii")
+        names, chunks, lengths = [], [], []
+        strip = bytes.maketrans(b"", b"")
+        for record in blob.split(b">")[1:]:
+            header, _, body = record.partition(b"\n")
+            seq = body.translate(strip, b"\r\n \t")
+            names.append(header.strip().decode("ascii", "replace"))
+            chunks.append(seq)
+            lengths.append(len(seq))
+        return cls.from_packed(b"".join(chunks), lengths, alphabet, encoded=False), names
+
+    def dump(self, file):
+        """Write the encoded database in a packed binary form (`load` reads it back without re-encoding)."""
+        with self.lock.read:
+            letters = self.alphabet.letters.encode("ascii")
+            lens = array.array("i", self._lengths)
+            payload = [self._MAGIC, len(letters).to_bytes(4, "little"), letters, len(lens).to_bytes(8, "little"),
+                       lens.tobytes(), b"".join(self._sequences)]
+        if hasattr(file, "write"):
+            for part in payload:
+                file.write(part)
+        else:
+            with open(file, "wb") as handle:
+                for part in payload:
+                    handle.write(part)
+
+    @classmethod
+    def load(cls, file):
+        """Read a database written by `dump`."""
+        if hasattr(file, "read"):
+            blob = file.read()
+        else:
+            with open(file, "rb") as handle:
+                blob = handle.read()
+        view = memoryview(blob)
+        m = len(cls._MAGIC)
+        if bytes(view[:m]) != cls._MAGIC:
+            raise ValueError("not a packed pyopal database")
+        nl = int.from_bytes(view[m : m + 4], "little")
+        letters = bytes(view[m + 4 : m + 4 + nl]).decode("ascii")
+        pos = m + 4 + nl
+        n = int.from_bytes(view[pos : pos + 8], "little")
+        pos += 8
+        lens = array.array("i")
+        lens.frombytes(view[pos : pos + 4 * n])
+        pos += 4 * n
+        return cls.from_packed(view[pos:], lens, Alphabet(letters), encoded=True)
+
     # --- Sequence interface ---
 
     def __getitem__(self, index):

@@ -283,3 +283,36 @@ def test_native_result_storage():
         _results.make_results(pyopal.ScoreResult, 0, 0, 4, scores, None, None, None, None, 5, None, None, None, None)
     with pytest.raises(TypeError):
         _results.make_results(int, 0, 0, 3, scores, None, None, None, None, 5, None, None, None, None)
+
+
+def test_database_bulk_ingest_and_persistence(tmp_path):
+    # additive constructors: packed buffers, FASTA, dump / load
+    import io
+
+    seqs = ["ACCTCG", "AACCGCTG", "", "TTATTACG"]
+    ref = pyopal.Database(seqs)
+    packed = pyopal.Database.from_packed("".join(seqs).encode(), [len(s) for s in seqs], encoded=False)
+    assert list(packed) == seqs and packed.lengths == ref.lengths
+    enc = b"".join(ref.get_sequences())
+    assert list(pyopal.Database.from_packed(enc, ref.lengths)) == seqs
+    with pytest.raises(ValueError):
+        pyopal.Database.from_packed(enc, [1, 2, 3])
+    with pytest.raises(ValueError):
+        pyopal.Database.from_packed(bytes([200]), [1])
+    with pytest.raises(ValueError):
+        pyopal.Database.from_packed(b"AC1T", [4], encoded=False)
+    fasta = b">sp|P1 first\nACCT\nCG\n>second\r\nAACCGCTG\r\n>empty\n>last\nTTATTACG"
+    db, names = pyopal.Database.from_fasta(io.BytesIO(fasta))
+    assert list(db) == seqs and names == ["sp|P1 first", "second", "empty", "last"]
+    path = tmp_path / "db.fa"
+    path.write_bytes(fasta)
+    assert list(pyopal.Database.from_fasta(str(path))[0]) == seqs
+    dna = pyopal.Database(["ACGT", "GATTACA"], pyopal.Alphabet("ACGT"))
+    dna.dump(str(tmp_path / "dna.bin"))
+    back = pyopal.Database.load(str(tmp_path / "dna.bin"))
+    assert list(back) == ["ACGT", "GATTACA"] and back.alphabet == dna.alphabet
+    buf = io.BytesIO()
+    ref.dump(buf)
+    assert list(pyopal.Database.load(io.BytesIO(buf.getvalue()))) == seqs
+    with pytest.raises(ValueError):
+        pyopal.Database.load(io.BytesIO(b"nonsense"))
