@@ -331,6 +331,9 @@ def run_b200(args):
         barrier()
         e2e_q = [0.0] * len(qbytes)
         e2e_dev = [0.0] * len(qbytes)
+        for q in qbytes:  # one untimed pass: the host-buffer path allocates its result row on first use
+            store.search(q, GAP_OPEN, GAP_EXTEND, M, 0, algo)
+        barrier()
         t0 = time.perf_counter()
         for _ in range(args.steps):
             for qi, q in enumerate(qbytes):
