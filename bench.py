@@ -76,31 +76,50 @@ def config_dict(args, db, extra=None):
 
 
 def cpu_sample(db, queries, algorithm, budget_s, threads):
-    """Time the scalar oracle on a bounded sample: query 300 aa against the first targets of the db."""
+    """Time the CPU restatement on a bounded sample of the workload.
+
+    SW (the benchmark's algorithm): oracle/opal_simd.c, an inter-sequence SIMD kernel in the style of
+    the reference's engine (16-bit lanes, overflow recomputed at full width), all host threads, the
+    300-aa and then the 1000-aa query against the first targets of the database.  Other algorithms:
+    the scalar oracle."""
     import array
     import oracle
     import pyopal_b200 as pyopal
 
     oracle.build()
     residues, offsets, lengths = db
-    q = queries[1].tobytes()
     M = pyopal.Aligner(MATRIX)._int_matrix
-    # probe the rate on a small slice, then size the sample for the budget
-    def run(n):
+
+    def run(q, n):
         n = min(n, len(lengths))
         off = array.array("q", offsets[:n].tolist())
         ln = array.array("i", lengths[:n].tolist())
         buf = residues[: int(offsets[n - 1] + lengths[n - 1])].tobytes() + b"\0"
         t0 = time.perf_counter()
-        oracle.search_flat(q, buf, off, ln, M, 24, GAP_OPEN, GAP_EXTEND, algorithm, "score", threads)
+        if algorithm == "sw":
+            oracle.sw_scores_simd(q, buf, off, ln, M, 24, GAP_OPEN, GAP_EXTEND, threads)
+        else:
+            oracle.search_flat(q, buf, off, ln, M, 24, GAP_OPEN, GAP_EXTEND, algorithm, "score", threads)
         dt = time.perf_counter() - t0
         return len(q) * int(lengths[:n].sum()), dt, n
 
-    cells, dt, n = run(2000)
+    # probe the rate on a slice, then size the sample for the budget
+    q300, q1000 = queries[1].tobytes(), queries[2].tobytes()
+    cells, dt, n = run(q300, 20000)
     rate = cells / max(dt, 1e-6)
-    n_budget = int(min(len(lengths), max(2000, rate * budget_s / (len(q) * float(lengths.mean())))))
-    cells, dt, n = run(n_budget)
-    return cells / dt / 1e9, f"oracle port, query 300 aa x first {n} targets ({cells:.3g} cells in {dt:.1f} s)"
+    per_target = float(lengths.mean())
+    total_cells, total_dt, parts = 0, 0.0, []
+    for q in (q300, q1000):
+        left = budget_s - total_dt
+        if left <= 0.5:
+            break
+        n_budget = int(min(len(lengths), max(20000, rate * left / (len(q) * per_target))))
+        cells, dt, n = run(q, n_budget)
+        total_cells += cells
+        total_dt += dt
+        parts.append(f"{len(q)} aa x first {n} targets")
+    impl = "inter-sequence SIMD port (oracle/opal_simd.c)" if algorithm == "sw" else "scalar oracle port"
+    return total_cells / total_dt / 1e9, f"{impl}, queries {' + '.join(parts)} ({total_cells:.3g} cells in {total_dt:.1f} s)"
 
 
 def run_reference(args):
@@ -123,12 +142,13 @@ def run_reference(args):
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "GCUPS", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_total / max(1, args.steps),
-        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int64 (scalar)",
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "s16 SIMD lanes (s64 rescore)",
         "data": "synthetic", "config": config_dict(args, db),
         "cpu_baseline": {"value": value, "unit": "GCUPS", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "GCUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "note": "CPU restatement (scalar C oracle, pthreads over contiguous chunks as _align.py:151-170), "
-                "not Opal SIMD: the Opal sources are absent from /root/reference (vendor/opal submodule empty)",
+        "note": "CPU restatement of the reference's inter-sequence SIMD scheme (oracle/opal_simd.c, gcc auto-vectorised "
+                "16-bit lanes, pthreads), not Opal itself: the Opal sources are absent from /root/reference "
+                "(vendor/opal submodule empty)",
     }
     print(json.dumps(line), flush=True)
 

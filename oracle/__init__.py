@@ -28,8 +28,8 @@ SEARCH = {"score": 0, "end": 1, "full": 2}
 def build(force=False):
     """Compile liboracle.so with gcc (oracle/Makefile)."""
     so = os.path.join(_HERE, "liboracle.so")
-    src = os.path.join(_HERE, "opal_oracle.c")
-    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+    srcs = [os.path.join(_HERE, f) for f in ("opal_oracle.c", "opal_simd.c", "opal_oracle.h")]
+    if force or not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s", "-B", "liboracle.so"])
     return so
 
@@ -44,6 +44,8 @@ def lib():
         vp, ci = ctypes.c_void_p, ctypes.c_int
         L.oracle_search_flat.restype = ci
         L.oracle_search_flat.argtypes = [vp, ci, vp, vp, vp, ci, ci, ci, vp, ci, ci, ci] + [vp] * 8 + [ci]
+        L.oracle_sw_scores_simd.restype = ci
+        L.oracle_sw_scores_simd.argtypes = [vp, ci, vp, vp, vp, ci, ci, ci, vp, ci, vp, ci]
         _LIB = L
     return _LIB
 
@@ -115,3 +117,15 @@ def search_flat(query, residues, offsets, lengths, matrix, alphabet_length, gap_
         out["target_start"] = list(stt)
         out["alignment"] = [bytes(ops[oo[k] : oo[k] + ol[k]]) for k in range(n)]
     return out
+
+
+def sw_scores_simd(query, residues, offsets, lengths, matrix, alphabet_length, gap_open, gap_extend, threads=1):
+    """Smith-Waterman scores with the inter-sequence SIMD baseline (opal_simd.c): the CPU arm of bench.py."""
+    n = len(lengths)
+    m = matrix if isinstance(matrix, array.array) else array.array("i", matrix)
+    scores = array.array("i", bytes(4 * n))
+    rc = lib().oracle_sw_scores_simd(_addr(query), len(query), _addr(residues), _addr(offsets), _addr(lengths), n,
+                                     gap_open, gap_extend, _addr(m), alphabet_length, _addr(scores), threads)
+    if rc != 0:
+        raise RuntimeError(f"oracle simd failed (code={rc})")
+    return scores

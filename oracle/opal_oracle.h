@@ -81,6 +81,10 @@ int oracle_search_flat(const unsigned char* query, int queryLength, const unsign
 
 void oracle_free(void* p);
 
+/* opal_simd.c: inter-sequence SIMD Smith-Waterman scores (the CPU baseline of bench.py). */
+int oracle_sw_scores_simd(const unsigned char* query, int m, const unsigned char* residues, const long long* offsets,
+                          const int* lengths, int n, int go, int ge, const int* S, int A, int* scores, int threads);
+
 #ifdef __cplusplus
 }
 #endif

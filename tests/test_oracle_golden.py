@@ -145,3 +145,28 @@ def test_reference_vectors_file(oracle):
                 assert r[key][:n] == v[key], (v["source"], key)
         if "alignment" in v:
             assert [a.translate(OPS).decode() for a in r["alignment"]][:n] == v["alignment"]
+
+
+def test_simd_baseline_equals_scalar_oracle(oracle):
+    # oracle/opal_simd.c (the CPU arm of bench.py) against the scalar restatement, overflow included
+    import array
+
+    import numpy as np
+
+    import pyopal_b200 as pyopal
+    import synthetic
+
+    M = pyopal.Aligner("BLOSUM62")._int_matrix
+    res, off, ln = synthetic.database(19, 700, 5.3, 0.7, 1, 3000)
+    buf = res.tobytes() + b"\0"
+    o, l = array.array("q", off.tolist()), array.array("i", ln.tolist())
+    for lq, go, ge in ((1, 11, 1), (45, 11, 1), (300, 3, 1), (611, 5, 2)):
+        q = synthetic.random_residues(np.random.Generator(np.random.PCG64(lq)), lq).tobytes()
+        got = list(oracle.sw_scores_simd(q, buf, o, l, M, 24, go, ge, threads=4))
+        assert got == oracle.search_flat(q, buf, o, l, M, 24, go, ge, "sw", "score", 4)["score"], (lq, go, ge)
+    base = synthetic.random_residues(np.random.Generator(np.random.PCG64(1)), 9000)
+    buf = base.tobytes() + base[:100].tobytes() + b"\0"
+    o, l = array.array("q", [0, 9000]), array.array("i", [9000, 100])
+    q = base[:8000].tobytes()
+    got = list(oracle.sw_scores_simd(q, buf, o, l, M, 24, 11, 1, threads=2))
+    assert got == oracle.search_flat(q, buf, o, l, M, 24, 11, 1, "sw", "score", 2)["score"] and got[0] > 32767
