@@ -41,6 +41,12 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--debug-timing", action="store_true", help="print a search / gather breakdown to stderr")
+    ap.add_argument("--workload", default="config2", choices=["config2", "config5"],
+                    help="config2 (default, the metric's configuration) or config5: UniRef50-shaped blocks, batched queries")
+    ap.add_argument("--blocks-per-gpu", type=int, default=8, help="config5: blocks of --block proteins per GPU (8 = 1/8 of C5)")
+    ap.add_argument("--block", type=int, default=781_250, help="config5: proteins per block")
+    ap.add_argument("--queries", type=int, default=64, help="config5: queries per batch (one step = one batch)")
+    ap.add_argument("--topk", type=int, default=1000, help="config5: hits kept per query")
     return ap.parse_args()
 
 
@@ -430,9 +436,214 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
+# --------------------------------------------------------------------------
+# Config 5 of BASELINE.json: UniRef50-shaped database (5e7 proteins at 8 GPUs), batched multi-query
+# search, block-dealt shards, NCCL gather of every query's scores.  One STEP = one batch of --queries
+# queries.  Per-GPU work is fixed (--blocks-per-gpu blocks), so this workload scales WEAKLY: N GPUs
+# search N x 6.25e6 proteins; 8 GPUs = the full 5e7-protein C5.
+
+
+def run_config5(args):
+    import numpy as np
+    import synthetic
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    queries = synthetic.config5_queries(args.queries)
+    qbytes = [np.ascontiguousarray(q).tobytes() for q in queries]
+    sum_lq = sum(len(q) for q in qbytes)
+    n_blocks = args.blocks_per_gpu * max(1, world)
+
+    def cfg(total_res, extra=None):
+        c = {"workload": f"config5: UniRef50-shaped synthetic db, {n_blocks} blocks x {args.block} proteins "
+                         f"({n_blocks * args.block} proteins, {total_res} residues), SW score mode, {MATRIX} open {GAP_OPEN} "
+                         f"ext {GAP_EXTEND}, batch of {len(qbytes)} queries of {min(map(len, qbytes))}..{max(map(len, qbytes))} aa "
+                         f"per step, top-{args.topk} hits per query",
+             "targets": n_blocks * args.block, "residues": total_res, "queries": len(qbytes), "query_residues": sum_lq,
+             "cells_per_step": sum_lq * total_res,
+             "l2": "inputs (3.5 GB pair-interleaved residue stream per GPU) exceed the 126 MB L2"}
+        if extra:
+            c.update(extra)
+        return c
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        res, lens = synthetic.config5_block(0, args.block)
+        db = synthetic.pack(lens, res)
+        threads = os.cpu_count() or 1
+        per_step = max(2.0, min(args.cpu_seconds, 150.0 / max(1, args.steps + args.warmup)))
+        vals, t_total, sample = [], 0.0, ""
+        for i in range(args.warmup + args.steps):
+            t0 = time.perf_counter()
+            v, sample = cpu_sample(db, queries, "sw", per_step, threads)
+            if i >= args.warmup:
+                vals.append(v)
+                t_total += time.perf_counter() - t0
+        value = sum(vals) / len(vals)
+        total_res = None
+        print(json.dumps({
+            "impl": "reference", "metric": METRIC, "value": value, "unit": "GCUPS", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_total / max(1, args.steps),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "s16 SIMD lanes (s64 rescore)",
+            "data": "synthetic", "config": cfg(int(lens.sum()) * n_blocks, {"note": "residues extrapolated from block 0"}),
+            "cpu_baseline": {"value": value, "unit": "GCUPS", "cores": threads, "kind": "port", "sample": sample + " of block 0"},
+            "e2e": {"value": value, "unit": "GCUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}), flush=True)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    import pyopal_b200 as pyopal
+    from pyopal_b200 import sharding
+    from pyopal_b200.platform import cuda
+
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    t0 = time.perf_counter()
+    sr, so, sl, mine = synthetic.config5_shard(rank, world, n_blocks, args.block)
+    t_gen = time.perf_counter() - t0
+    res_mine = int(sl.sum())
+    t0 = time.perf_counter()
+    store = cuda.DeviceStore(sr, so, np.ascontiguousarray(sl), 24, device=local)
+    t_build = time.perf_counter() - t0
+    del sr
+    M = pyopal.Aligner(MATRIX, GAP_OPEN, GAP_EXTEND)._int_matrix
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    gather = sharding.BlockGather(args.block, args.blocks_per_gpu, world, "cuda")
+    d_local = gather.new_local()
+    gathered = torch.empty(world * gather.n_local, dtype=torch.int32, device="cuda") if world > 1 else None
+    final = torch.empty(gather.n_all, dtype=torch.int32, device="cuda") if world > 1 else None
+    k = min(args.topk, gather.n_all)
+    top_v = torch.empty((len(qbytes), k), dtype=torch.int32, device="cuda")
+    top_i = torch.empty((len(qbytes), k), dtype=torch.int64, device="cuda")
+    host_v = torch.empty((len(qbytes), k), dtype=torch.int32).pin_memory()
+    host_i = torch.empty((len(qbytes), k), dtype=torch.int64).pin_memory()
+    tot = torch.tensor([float(res_mine)], dtype=torch.float64, device="cuda")
+    mx = tot.clone()
+    if world > 1:
+        dist.all_reduce(tot)
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    total_res = int(tot.item())
+    imbalance = float(mx.item()) * world / total_res - 1.0
+
+    acc = {"k16_us": 0.0, "launches": 0, "passes_cols": 0.0}
+
+    def batch(to_host=False, collect=False):
+        for qi, q in enumerate(qbytes):
+            store.search_scores_device(q, GAP_OPEN, GAP_EXTEND, M, 3, d_local.data_ptr(), stream.cuda_stream)
+            stream.synchronize()  # the store's per-search workspace is reused by the next query
+            if collect:
+                st = store.stats()
+                acc["k16_us"] += st["k16_us"]
+                acc["launches"] += st["launches"]
+                acc["passes_cols"] += st["passes"]
+            scores = gather.gather(d_local, gathered, final)
+            v, i = torch.topk(scores, k)
+            top_v[qi].copy_(v)
+            top_i[qi].copy_(i)
+            if to_host:
+                host_v[qi].copy_(top_v[qi], non_blocking=True)
+                host_i[qi].copy_(top_i[qi], non_blocking=True)
+            if world > 1:
+                stream.synchronize()  # see run_b200: an un-synchronised all-gather delays the next search
+        stream.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        batch()
+    barrier()
+    props = torch.cuda.get_device_properties(local)
+    sampler = ClockSampler("%08x:%02x:%02x.0" % (props.pci_domain_id, props.pci_bus_id, props.pci_device_id))
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        batch(collect=True)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.finish()
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    cells_step = sum_lq * total_res
+    value = cells_step * args.steps / (ms * 1e-3) / 1e9
+    # end to end: host queries in (H2D inside the C-ABI call), top-k hits out to pinned host memory
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        batch(to_host=True)
+    torch.cuda.synchronize()
+    dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    e2e_value = cells_step * args.steps / float(dt.item()) / 1e9
+    checksum = int(host_v.to(torch.int64).sum().item())
+
+    if rank == 0:
+        import ctypes
+        rate = None
+        r, c = ctypes.c_double(0), ctypes.c_double(0)
+        if cuda.load_library().pyopal_cuda_int_issue_rate(local, ctypes.byref(r), ctypes.byref(c)) == 0:
+            rate = r.value
+        roof = rate * 2 / ALU_INSTR_PER_CELL_PAIR / 1e9 if rate else None
+        gcups_k = sum_lq * res_mine * args.steps / max(acc["k16_us"], 1) / 1e3
+        try:
+            hbm_peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 6650.0)
+        except Exception:
+            hbm_peak = 6650.0
+        bytes_k = acc["passes_cols"] * int(store.device_bytes())
+        line = {
+            "metric": METRIC, "value": value, "unit": "GCUPS", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u16x2 (s32 rescore)", "data": "synthetic",
+            "config": cfg(total_res, {"parallelism": f"blocks dealt round-robin over {world} GPU(s), NCCL all-gather of every "
+                                                     f"query's scores, top-{k} on the device",
+                                      "generate_s": round(t_gen, 2), "store_build_s": round(t_build, 2),
+                                      "store_bytes_per_gpu": int(store.device_bytes()),
+                                      "shard_residue_imbalance": round(imbalance, 5)}),
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": "GCUPS", "h2d_bytes_per_step": sum_lq + len(qbytes) * (24 * 24 * 4 + 64),
+                    "d2h_bytes_per_step": len(qbytes) * k * 12,
+                    "api": "DeviceStore.search_scores_device (host query in) + BlockGather + top-k, hits to pinned host; wall clock"},
+            "roofline": {"bound": "int_alu", "achieved": gcups_k, "peak": roof, "unit": "GCUPS",
+                         "frac": (gcups_k / roof) if roof else None, "traffic": None,
+                         "alu_thread_instr_per_s": rate, "alu_instr_per_cell_pair": ALU_INSTR_PER_CELL_PAIR,
+                         "peak_source": "pyopal_cuda_int_issue_rate (measured on this GPU in this run)"},
+            "roofline_hbm": {"bound": "hbm", "achieved": bytes_k / max(acc["k16_us"], 1) / 1e3, "peak": hbm_peak, "unit": "GB/s",
+                             "frac": bytes_k / max(acc["k16_us"], 1) / 1e3 / hbm_peak, "traffic": None,
+                             "note": "residue stream once per pass of the 16-bit kernel on rank 0"},
+            "top_hits_checksum": checksum,
+            "gpu_launches": int(acc["launches"]),
+        }
+        if not args.no_cpu_baseline and world == 1:
+            bres, blens = synthetic.config5_block(0, args.block)
+            v, sample = cpu_sample(synthetic.pack(blens, bres), queries, "sw", args.cpu_seconds, os.cpu_count() or 1)
+            line["cpu_baseline"] = {"value": v, "unit": "GCUPS", "cores": os.cpu_count() or 1, "kind": "port",
+                                    "sample": sample + " of block 0"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def main():
     args = parse()
-    if args.impl == "reference":
+    if args.workload == "config5":
+        run_config5(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_b200(args)

@@ -90,6 +90,8 @@ void pyopal_cuda_db_destroy(pyopal_cuda_db* db) {
     if (db->ev_fork) cudaEventDestroy(db->ev_fork);
     if (db->ev_join) cudaEventDestroy(db->ev_join);
     if (db->side) cudaStreamDestroy(db->side);
+    if (db->side2) cudaStreamDestroy(db->side2);
+    if (db->ev_join2) cudaEventDestroy(db->ev_join2);
     for (int i = 0; i < 6; i++) if (db->kev[i]) cudaEventDestroy(db->kev[i]);
     if (db->ev0) cudaEventDestroy(db->ev0);
     if (db->ev1) cudaEventDestroy(db->ev1);
@@ -278,9 +280,11 @@ static int db_build(int device, GetSeq get_seq, const int32_t* lengths, int64_t 
         int lo_prio = 0, hi_prio = 0;
         CU(cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio));
         CU(cudaStreamCreateWithPriority(&db->side, cudaStreamNonBlocking, hi_prio));
+        CU(cudaStreamCreateWithPriority(&db->side2, cudaStreamNonBlocking, hi_prio));
     }
     CU(cudaEventCreateWithFlags(&db->ev_fork, cudaEventDisableTiming));
     CU(cudaEventCreateWithFlags(&db->ev_join, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&db->ev_join2, cudaEventDisableTiming));
     CU(cudaEventCreate(&db->ev0));
     CU(cudaEventCreate(&db->ev1));
     for (int i = 0; i < 6; i++) CU(cudaEventCreate(&db->kev[i]));
@@ -556,6 +560,34 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
         const int teams_now = (gwarps == 1) ? 16 : std::max(1, 16 / gwarps);
         gpol.col_cost = 56.0 * 36.0 * gK * (gwarps > 1 ? 1.6 : 1.0) / teams_now;
     }
+    const bool old_giants_ok = gpol.ok;
+    // transposed giants (tgiant.cu): the target over the lanes, the query streamed; needs the short F chain
+    bool use_t = false;
+    int tK = 32, tNW = 4, tpitch = 0, tsplit_override = -1;
+    size_t tsmem = 0;
+    int smem_optin = 0;
+    CU(cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, db->device));
+    if (make_rung(M, A, go, ge, mode, 0).fits8 && ge <= go && !getenv("PYOPAL_CUDA_NO_TGIANT") &&
+        !getenv("PYOPAL_CUDA_NO_GIANT")) {
+        if (const char* ov = getenv("PYOPAL_CUDA_TGIANT")) {  // "warps,K": tuning override
+            int a = 0, b = 0, c = -1;
+            const int got = sscanf(ov, "%d,%d,%d", &a, &b, &c);
+            if (got >= 2 && a >= 1 && a <= 8 && (b == 16 || b == 32)) { tNW = a; tK = b; }
+            if (got == 3 && c >= 0) tsplit_override = c;
+        }
+        tpitch = tNW * 32 * (tK + 4);
+        tsmem = tgiant_smem_bytes(A, tpitch, tNW, Lq);
+        // one warp per scheduler issues a 32-row step in ~820 clocks: faster than giant.cu up to ~1500 rows
+        use_t = tsmem + 1024 <= (size_t)smem_optin && (Lq <= 1536 || getenv("PYOPAL_CUDA_TGIANT"));
+        if (use_t && !old_giants_ok) {
+            gpol.ok = true;
+            gpol.cap = (int64_t)db->sm_count * 8;
+            // a revolution of Lq + 32 * warps - 1 steps covers 32 * warps * K target columns; a step costs
+            // about 25 clocks per row held by a lane (measured); 56 cost units per SM clock
+            const double step_clk = 25.0 * tK + 20.0;
+            gpol.col_cost = 56.0 * step_clk * (double)(Lq + tNW * 32 - 1) / (double)(tNW * 32 * tK);
+        }
+    }
     Plan bulk = make_plan(Lq, A, db, SMEM_LIMIT, &gpol);
     Plan tail = make_tail_plan(Lq, A, SMEM_LIMIT);
     int smax = INT_MIN, smin = INT_MAX;
@@ -622,11 +654,17 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
         return in_range(db->h_pair_idx[(size_t)(2 * k)]) ||
                (db->h_pair_idx[(size_t)(2 * k + 1)] >= 0 && in_range(db->h_pair_idx[(size_t)(2 * k + 1)]));
     };
-    std::vector<int32_t> wl32, wl16, wlg;
+    std::vector<int32_t> wl32, wl16, wlg, wlt;
+    // giants longer than one slab of the transposed kernel go to tgiant.cu, the others to giant.cu
+    const int tsplit = !use_t ? INT32_MAX : tsplit_override >= 0 ? tsplit_override : tNW * 32 * tK;
     for (int64_t k = 0; k < kg; k++) {
-        if (in_range(db->h_pair_idx[(size_t)(2 * k)])) wlg.push_back((int32_t)(k << 1));
-        if (db->h_pair_idx[(size_t)(2 * k + 1)] >= 0 && in_range(db->h_pair_idx[(size_t)(2 * k + 1)]))
-            wlg.push_back((int32_t)((k << 1) | 1));
+        for (int h = 0; h < 2; h++) {
+            const int32_t ix = db->h_pair_idx[(size_t)(2 * k + h)];
+            if (ix < 0 || !in_range(ix)) continue;
+            const int32_t e = (int32_t)((k << 1) | h);
+            if (db->h_pair_len[(size_t)(2 * k + h)] > tsplit || !old_giants_ok) wlt.push_back(e);
+            else wlg.push_back(e);
+        }
     }
     for (int64_t k = kg; k < n32p; k++) {
         if (in_range(db->h_pair_idx[(size_t)(2 * k)])) wl32.push_back((int32_t)(k << 1));
@@ -650,8 +688,9 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
         d_wl_tail = db->wl16.p; d_wl_bulk = db->wl16.p + ntail;
     }
     const int64_t n32 = (int64_t)wl32.size();
-    const int64_t ng = (int64_t)wlg.size();
-    wl32.insert(wl32.end(), wlg.begin(), wlg.end());  // one upload: [static 32-bit | giants]
+    const int64_t ng = (int64_t)wlg.size(), nt = (int64_t)wlt.size();
+    wl32.insert(wl32.end(), wlg.begin(), wlg.end());  // one upload: [static 32-bit | giants | transposed giants]
+    wl32.insert(wl32.end(), wlt.begin(), wlt.end());
     if (db->wl32.reserve(wl32.size() + 1)) return PYOPAL_CUDA_ERR_NOMEM;
     if (!wl32.empty()) CU(cudaMemcpyAsync(db->wl32.p, wl32.data(), wl32.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
     const int64_t n16 = ntail + nbulk;
@@ -664,7 +703,7 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
     CU(cudaMemcpyAsync(db->d_matrix, M, (size_t)A * A * sizeof(int32_t), cudaMemcpyHostToDevice, st));
     int32_t counts[16] = {0};
     counts[0] = (int32_t)nbulk; counts[1] = (int32_t)n32; counts[2] = 0; counts[3] = (int32_t)ntail;
-    counts[8] = (int32_t)ng;
+    counts[8] = (int32_t)ng; counts[10] = (int32_t)nt;
     CU(cudaMemcpyAsync(db->d_counts, counts, sizeof(counts), cudaMemcpyHostToDevice, st));
     if (bulk.npass > 1 || tail.npass > 1) {
         if (db->bndH.reserve((size_t)db->ncols + 16) || db->bndF.reserve((size_t)db->ncols + 16)) return PYOPAL_CUDA_ERR_NOMEM;
@@ -705,12 +744,32 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
     if (!k32) return fail(PYOPAL_CUDA_ERR_INTERNAL, "no 32-bit kernel for this tile");
 
     // ---- side stream: longest targets first, concurrently with the bulk -------
-    const bool side_work = (ng > 0) || (n32 > 0) || (ntail > 0 && !same_plan);
+    const bool side_work = (ng > 0) || (nt > 0) || (n32 > 0) || (ntail > 0 && !same_plan);
     cudaStream_t side = db->side;
     if (side_work) {
         CU(cudaEventRecord(db->ev_fork, st));
         CU(cudaStreamWaitEvent(side, db->ev_fork, 0));
         CU(cudaEventRecord(db->kev[0], side));
+    }
+    if (nt > 0) {
+        search_kernel_t kt = get_tgiant_kernel(tK, local);
+        if (!kt) return fail(PYOPAL_CUDA_ERR_INTERNAL, "no transposed giant kernel for this tile");
+        KParams Q = P;
+        Q.G = tNW; Q.logG = 0; Q.npass = 1; Q.pitch = tpitch; Q.padtop = 0;
+        Q.krows = tK; Q.kstride = tK + 4;
+        // padding rows above target position 0 reproduce the border H[i][-1] (kernels.cuh, profile_entry)
+        Q.pad_score = ((mode == MODE_NW || mode == MODE_HW) ? -std::max(go, ge) : 0) + go;
+        Q.worklist = db->wl32.p + n32 + ng; Q.nwork = db->d_counts + 10; Q.counter = db->d_counts + 11;
+        Q.neg = -(1 << 29);
+        // the whole SM's shared memory: no throughput CTA shares the SM with a giant (giant.cu)
+        const size_t smem_all = std::max<size_t>(tsmem, (size_t)smem_optin - 1024);
+        CU(cudaFuncSetAttribute(kt, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_all));
+        // its own stream: the few longest targets start at once, beside giant.cu's medium ones
+        CU(cudaStreamWaitEvent(db->side2, db->ev_fork, 0));
+        kt<<<(unsigned)std::min<int64_t>(nt, db->sm_count), tNW * 32, smem_all, db->side2>>>(Q);
+        CU(cudaGetLastError());
+        CU(cudaEventRecord(db->ev_join2, db->side2));
+        db->stats[0]++;
     }
     if (ng > 0) {
         search_kernel_t kgiant = get_giant_kernel(gK, local);
@@ -723,11 +782,12 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
         Q.worklist = db->wl32.p + n32; Q.nwork = db->d_counts + 8; Q.counter = db->d_counts + 9;
         Q.neg = -(1 << 29);
         // ask for the whole SM's shared memory: no throughput CTA may share the SM with the giants (giant.cu)
-        int smem_optin = 0;
-        CU(cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, db->device));
         const size_t gsmem_all = std::max<size_t>(gsmem, (size_t)smem_optin - 1024);
         CU(cudaFuncSetAttribute(kgiant, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsmem_all));
-        kgiant<<<(unsigned)std::min<int64_t>((ng + teams - 1) / teams, db->sm_count), 512, gsmem_all, side>>>(Q);
+        // with the longest targets on tgiant.cu, what is left here is many medium targets: a quarter of the
+        // SMs is enough for their latency and leaves the rest to the bulk kernel from the start
+        const int64_t gcap = use_t ? std::max<int64_t>(8, db->sm_count / 4) : db->sm_count;
+        kgiant<<<(unsigned)std::min<int64_t>((ng + teams - 1) / teams, gcap), 512, gsmem_all, side>>>(Q);
         CU(cudaGetLastError());
         db->stats[0]++;
     }
@@ -751,6 +811,7 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
         if (rc) return rc;
     }
     if (side_work) {
+        if (nt > 0) CU(cudaStreamWaitEvent(side, db->ev_join2, 0));  // joins only after everything is launched
         CU(cudaEventRecord(db->kev[1], side));
         db->kev_valid[0] = true;
         CU(cudaEventRecord(db->ev_join, side));
@@ -797,7 +858,7 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
         CU(cudaEventRecord(db->kev[5], st));
         db->kev_valid[2] = true;
     }
-    db->stats[1] = n16 * 2; db->stats[2] = n32 + ng;
+    db->stats[1] = n16 * 2; db->stats[2] = n32 + ng + nt;
     db->stats[5] = bulk.G; db->stats[6] = bulk.K; db->stats[7] = bulk.npass; db->stats[11] = bulk.psmem ? 1 : 0;
     return apply_fixes();
 }

@@ -189,7 +189,7 @@ template <int W> struct CellConsts {
 // previous column, upGprev = H - open of the row above in the previous column,
 // F / Gup = (F, H - open) of the row above in this column.  Out: E, Gl of this
 // column, F / Gup of the thread's last row (for the thread below), best.
-template <int K, int W, bool LOCAL, bool PSMEM, bool WIDE, bool TDADD>
+template <int K, int W, bool LOCAL, bool PSMEM, bool WIDE, bool TDADD, bool SHORTF_ = (W == 16)>
 __device__ __forceinline__ void column_update(const KParams& P, const int8_t* prof, unsigned t0, unsigned t1, int pslot,
                                               const CellConsts<W>& C, typename Val<W>::T (&E)[K],
                                               typename Val<W>::T (&Gl)[K], typename Val<W>::T upGprev,
@@ -198,7 +198,7 @@ __device__ __forceinline__ void column_update(const KParams& P, const int8_t* pr
     typedef Val<W> V;
     typedef typename V::T val_t;
     constexpr bool ADDPATH = TDADD || (W == 32);
-    constexpr bool SHORTF = (W == 16);        // the host sends ext > open to the 32-bit rung
+    constexpr bool SHORTF = SHORTF_;          // one-instruction F chain: needs ext <= open (the host checks)
     const val_t NEGEXT = C.NEGEXT, NEGOPEN = C.NEGOPEN, PNEGOPEN = C.PNEGOPEN, FLOOR = C.FLOOR;
     const unsigned one = C.one;
     const int8_t* pa = prof + t0 * P.pitch + pslot;   // pslot: first profile slot of this lane's chunk
@@ -478,5 +478,8 @@ search_kernel_t get_search_kernel_wide(bool local);  // K = 32, W = 32
 // giant.cu: a team of warps per target (KParams.G = warps per team, KParams.npass = teams per CTA), K = 4 or 8
 search_kernel_t get_giant_kernel(int K, bool local);
 size_t giant_smem_bytes(int A, int pitch, int warps_per_team, int teams);
+// tgiant.cu: the longest targets with the TARGET laid over the lanes of a team (KParams.G = warps), K = 16 or 32
+search_kernel_t get_tgiant_kernel(int K, bool local);
+size_t tgiant_smem_bytes(int A, int pitch, int warps, int Lq);
 
 }  // namespace pyopal

@@ -83,8 +83,8 @@ struct pyopal_cuda_db {
     pyopal::DevBuf<int8_t> gprofile;
     pyopal::DevBuf<int32_t> wprofile;
     pyopal::DevBuf<uint32_t> bndH, bndF, bnd32H, bnd32F;
-    cudaStream_t side = nullptr;
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaStream_t side = nullptr, side2 = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_join2 = nullptr;
     int32_t* d_matrix = nullptr;  // 32*32
     int32_t* d_counts = nullptr;  // [0..2] list sizes, [4..6] task counters
     int64_t stats[12] = {0};

@@ -95,3 +95,42 @@ class ScoreGather:
             out = torch.empty(self.n_all, dtype=torch.int32, device=self.device)
         out[self.dest] = gathered[self.valid]
         return out
+
+
+class BlockGather:
+    """Score gather for a database dealt to the ranks in equal BLOCKS (block b -> rank b % world).
+
+    Used for databases too large to length-sort globally on one host (config 5 of
+    BASELINE.json, 5e7 targets): every rank draws / loads its own blocks, scores them
+    in local order, and database order is recovered from the all-gathered buffer by a
+    strided view -- no index arrays (the 5e7-entry permutation of ScoreGather would
+    cost 400 MB per rank).  `blocks_per_rank * world` blocks of `block` targets each.
+    """
+
+    def __init__(self, block, blocks_per_rank, world, device, group=None):
+        import torch
+        import torch.distributed as dist
+
+        self.block, self.nb, self.world = int(block), int(blocks_per_rank), int(world)
+        self.n_local = self.block * self.nb
+        self.n_all = self.n_local * self.world
+        self.group = group
+        self.device = device
+        self._torch, self._dist = torch, dist
+
+    def new_local(self):
+        return self._torch.zeros(self.n_local, dtype=self._torch.int32, device=self.device)
+
+    def gather(self, local, gathered=None, out=None):
+        """All-gather ``local`` (n_local int32); returns the scores in database order."""
+        torch = self._torch
+        if self.world == 1:
+            return local
+        if gathered is None:
+            gathered = torch.empty(self.world * self.n_local, dtype=torch.int32, device=self.device)
+        self._dist.all_gather_into_tensor(gathered, local, group=self.group)
+        if out is None:
+            out = torch.empty(self.n_all, dtype=torch.int32, device=self.device)
+        # gathered[r, k, i] is target (k * world + r) * block + i
+        out.view(self.nb, self.world, self.block).copy_(gathered.view(self.world, self.nb, self.block).permute(1, 0, 2))
+        return out

@@ -117,6 +117,38 @@ def test_giant_teams(cuda, oracle, algo, lq):
     assert db._device_store().stats()["targets32"] >= 4
 
 
+@pytest.mark.parametrize("algo", ALGOS)
+@pytest.mark.parametrize("shape", ["1,16,0", "2,16,0", "3,32,0", "4,32,0", "8,16,0", "4,32"])
+@pytest.mark.parametrize("lq", [1, 37, 300, 1100])
+def test_transposed_giants(cuda, oracle, monkeypatch, algo, shape, lq):
+    # tgiant.cu: the target over the lanes of a team of 1..8 warps (16 / 32 positions per lane), the
+    # query streamed; lengths around the slab sizes (512 .. 4096) so that one-slab, multi-slab
+    # (boundary FIFO), partly idle teams and the warp-to-warp ring are all taken
+    monkeypatch.setenv("PYOPAL_CUDA_TGIANT", shape)
+    giants = (9001, 4097, 4096, 4095, 3073, 2049, 2048, 1537, 1100, 1025)
+    seqs = synthetic.as_sequences(synthetic.database(81, 300, 5.0, 0.6, 1, 1000, giants=giants))
+    aligner = pyopal.Aligner("BLOSUM62", 11, 1)
+    db = check(oracle, aligner, rand_query(80 + lq, lq), seqs, algo)
+    assert db._device_store().stats()["targets32"] >= len(giants)
+
+
+def test_transposed_giants_match_query_teams(cuda, oracle, monkeypatch):
+    # the two giant kernels (query over the lanes / target over the lanes) agree on a high-scoring homolog
+    rng = np.random.Generator(np.random.PCG64(83))
+    big = synthetic.random_residues(rng, 12000)
+    seqs = [big.tobytes(), synthetic.mutate(rng, big).tobytes()] + rand_seqs(84, 200, 5.0, 0.6, 1, 900)
+    aligner = pyopal.Aligner("BLOSUM50", 10, 2)
+    q = big[3000:5200].tobytes()
+    for algo in ALGOS:
+        monkeypatch.delenv("PYOPAL_CUDA_NO_TGIANT", raising=False)
+        a = list(aligner.align_scores(query_str(aligner, q), make_db(seqs, aligner.alphabet), algorithm=algo))
+        monkeypatch.setenv("PYOPAL_CUDA_NO_TGIANT", "1")
+        b = list(aligner.align_scores(query_str(aligner, q), make_db(seqs, aligner.alphabet), algorithm=algo))
+        assert a == b, algo
+    monkeypatch.delenv("PYOPAL_CUDA_NO_TGIANT", raising=False)
+    check(oracle, aligner, q, seqs, "sw")
+
+
 @pytest.mark.parametrize("algo", ("nw", "hw", "ov"))
 def test_static_32bit_rung(cuda, oracle, algo):
     # NW of a short query against 30k+ targets goes below -32768; long identical pairs go above +32767
