@@ -401,6 +401,21 @@ def run_b200(args):
         gcups_k = cells_k / tot_us / 1e3
         bytes_k = sum(p["passes"] * int(store.device_bytes()) for p in per_q)
         roof_gcups = rate * 2 / ALU_INSTR_PER_CELL_PAIR / 1e9 if rate else None
+        # DRAM traffic of the bulk kernel from the committed ncu --set full capture (config 2, one GPU):
+        # the launch of the longest query captured, next to its algorithmic bytes
+        traffic = traffic_note = None
+        try:
+            tr = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))["launches"]
+            if args.workload == "config2" and world == 1 and args.targets == 570_000:
+                t = max(tr, key=lambda x: x["query_length"])
+                pq = [p for p in per_q if p["Lq"] == t["query_length"]][0]
+                algo_bytes = pq["passes"] * int(store.device_bytes())
+                traffic = t["dram_bytes_per_launch"]
+                traffic_note = (f"bulk launch of the {t['query_length']}-aa query: {traffic} B measured by ncu vs {algo_bytes} B "
+                                f"algorithmic (residue stream x {pq['passes']} passes); the excess is the pass-boundary rows "
+                                f"(16 B per column per extra pass) that spill out of L2")
+        except Exception:
+            pass
         line = {
             "metric": METRIC, "value": value, "unit": "GCUPS", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
@@ -414,11 +429,11 @@ def run_b200(args):
             # cores: achieved = algorithmic cell updates of the 16-bit kernel / its CUDA-event
             # time; peak = ALU-pipe instruction rate measured in this run (VIADDMNMX.U16x2 stream) x 2 cells / 5.5
             "roofline": {"bound": "int_alu", "achieved": gcups_k, "peak": roof_gcups, "unit": "GCUPS",
-                         "frac": (gcups_k / roof_gcups) if roof_gcups else None, "traffic": None,
+                         "frac": (gcups_k / roof_gcups) if roof_gcups else None, "traffic": traffic,
                          "alu_thread_instr_per_s": rate, "alu_instr_per_cell_pair": ALU_INSTR_PER_CELL_PAIR,
                          "peak_source": "pyopal_cuda_int_issue_rate (measured on this GPU in this run)"},
             "roofline_hbm": {"bound": "hbm", "achieved": bytes_k / tot_us / 1e3, "peak": hbm_peak, "unit": "GB/s",
-                             "frac": bytes_k / tot_us / 1e3 / hbm_peak, "traffic": None,
+                             "frac": bytes_k / tot_us / 1e3 / hbm_peak, "traffic": traffic, "traffic_note": traffic_note,
                              "note": "residue stream (2 B per pair column per pass) of the 16-bit kernel; "
                                      "1/Lq byte per cell, so HBM is not the binding roof",
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback"},
