@@ -322,7 +322,11 @@ Plan finish_plan(Plan p, int Lq, int A, size_t smem_limit) {
     const int T = p.G * p.K;
     p.npass = (Lq + T - 1) / T;
     p.kstride = ((p.K / 4) % 2 == 0) ? p.K + 4 : p.K;  // odd number of words per lane chunk (kernels.cuh)
-    p.pitch = (p.npass * p.G * p.kstride + 15) / 16 * 16;
+    // Letter rows start 16 (mod 32) bytes apart, i.e. 4 (mod 8) words: the rows of the letters then start in 8
+    // different bank quads while lanes p = 0..3 of a group (lane chunks an odd number of words apart) stay in
+    // different residues mod 4, so only lanes with the same p in different groups can collide.  Measured on
+    // config 2: a pitch that is a multiple of 128 bytes is 28 % slower, an odd number of words 3-4 % slower.
+    p.pitch = (p.npass * p.G * p.kstride + 15) / 32 * 32 + 16;
     p.padtop = p.npass * T - Lq;
     p.smem = (size_t)(A + 1) * (size_t)p.pitch;
     p.psmem = p.smem <= smem_limit;
@@ -837,6 +841,10 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
                 if (sscanf(ov, "%d,%d,%d", &lg, &k, &t) == 3 && t >= 32 && t <= 512 && t % 32 == 0) threads = t;
             }
             CU(cudaEventRecord(db->kev[2], st));
+            if (getenv("PYOPAL_CUDA_DEBUG"))
+                fprintf(stderr, "[pyopal_cuda] Lq=%d bulk: G=%d K=%d npass=%d pairs=%lld | giants=%lld tgiants=%lld static32=%lld threads=%d smem=%zu\n",
+                        Lq, bulk.G, bulk.K, bulk.npass, (long long)nw, (long long)ng, (long long)nt, (long long)n32, threads,
+                        bulk.smem);
             int rc = launch_search(db, kb, Q, bulk.smem, threads, (nw + gpw - 1) / gpw, st);
             if (rc) return rc;
             CU(cudaEventRecord(db->kev[3], st));
