@@ -115,7 +115,8 @@ def cpu_sample(db, queries, algorithm, budget_s, threads):
     rate = cells / max(dt, 1e-6)
     per_target = float(lengths.mean())
     total_cells, total_dt, parts = 0, 0.0, []
-    for q in (q300, q1000):
+    extra = [q.tobytes() for q in queries[3:5]] if len(queries) >= 5 else []
+    for q in [q300, q1000] + extra + [q1000, q300] * 8:  # keep going until the budget is used
         left = budget_s - total_dt
         if left <= 0.5:
             break
@@ -124,6 +125,10 @@ def cpu_sample(db, queries, algorithm, budget_s, threads):
         total_cells += cells
         total_dt += dt
         parts.append(f"{len(q)} aa x first {n} targets")
+    seen = {}
+    for p_ in parts:
+        seen[p_] = seen.get(p_, 0) + 1
+    parts = [p_ if c == 1 else f"{c} x ({p_})" for p_, c in seen.items()]
     impl = "inter-sequence SIMD port (oracle/opal_simd.c)" if algorithm == "sw" else "scalar oracle port"
     return total_cells / total_dt / 1e9, f"{impl}, queries {' + '.join(parts)} ({total_cells:.3g} cells in {total_dt:.1f} s)"
 

@@ -127,3 +127,24 @@ def test_batch_equals_single_full_size(full):
     n = full["store"].size
     for i, q in enumerate(qs):
         assert np.array_equal(flat[i * n: (i + 1) * n], gpu_scores(full, q, "sw")), i
+
+
+def test_config5_block_batch(cuda, oracle):
+    # config 5's shape on one rank: two blocks dealt to "rank 1 of 2", the batched search, the block gather's
+    # view-based order (world 1 = identity) and the oracle on a subsample incl. the longest targets
+    block = 60_000
+    sr, so, sl, mine = synthetic.config5_shard(1, 2, 4, block)
+    assert mine == [1, 3] and len(sl) == 2 * block
+    store = cuda.DeviceStore(sr, so, np.ascontiguousarray(sl), 24, device=0)
+    M = pyopal.Aligner("BLOSUM62", GO, GE)._int_matrix
+    queries = [q.tobytes() for q in synthetic.config5_queries(6)]
+    rows = np.frombuffer(store.search_batch(queries, GO, GE, M, 3), dtype=np.int32).reshape(len(queries), -1)
+    rng = np.random.Generator(np.random.PCG64(55))
+    idx = np.unique(np.concatenate([rng.choice(len(sl), 1500, replace=False), np.argsort(sl)[-20:], np.argsort(sl)[:20]]))
+    sub_r, sub_o, sub_l = sharding.pack_shard(sr, so, sl, idx)
+    for qi, q in enumerate(queries):
+        want = oracle.search_flat(q, sub_r.tobytes() + b"\0", array.array("q", sub_o.tolist()),
+                                  array.array("i", sub_l.tolist()), M, 24, GO, GE, "sw", "score", 8)["score"]
+        assert rows[qi][idx].tolist() == list(want), qi
+        single = np.frombuffer(store.search(q, GO, GE, M, 0, 3)[0], dtype=np.int32)
+        assert np.array_equal(single, rows[qi])

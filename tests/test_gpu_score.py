@@ -247,3 +247,28 @@ def test_mutation_invalidates_device_store(cuda):
     assert len(res) == 2 and res[1].score == 5 + 13 + 13 + 5 + 13 + 8
     db[0] = "TTTT"
     assert aligner.align("ACCTCG", db)[0].score == 5
+
+
+def test_concurrent_aligners_share_a_database(cuda, oracle):
+    # the reference's documented pattern (README.md:116-144): a ThreadPool of queries against ONE Database;
+    # the store's workspace is serialised inside the library, results must equal the sequential ones
+    from multiprocessing.pool import ThreadPool
+
+    seqs = rand_seqs(301, 900, 5.0, 0.6, 1, 1500) + [rand_query(302, 5000)]
+    aligner = pyopal.Aligner("BLOSUM62", 11, 1)
+    db = make_db(seqs, aligner.alphabet)
+    queries = [rand_query(310 + i, n) for i, n in enumerate((40, 90, 150, 260, 400, 700, 33, 1200))]
+    algos = ["sw", "nw", "hw", "ov", "sw", "sw", "ov", "nw"]
+
+    def one(args):
+        q, algo = args
+        return list(aligner.align_scores(query_str(aligner, q), db, algorithm=algo))
+
+    with ThreadPool(4) as pool:
+        got = pool.map(one, list(zip(queries, algos)) * 3)
+    want = [oracle.search(q, seqs, aligner._int_matrix, 24, 11, 1, a, "score", threads=8)["score"] for q, a in zip(queries, algos)]
+    for k, row in enumerate(got):
+        assert row == want[k % len(queries)], (k, algos[k % len(queries)])
+    # result objects from threads as well (pyopal.align(threads=...) maps onto the same call)
+    res = list(pyopal.align(query_str(aligner, queries[2]), db, "BLOSUM62", gap_open=11, gap_extend=1, algorithm=algos[2], threads=3, ordered=True))
+    assert [r.score for r in res] == want[2]
