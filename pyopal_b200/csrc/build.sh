@@ -15,4 +15,4 @@ done
 for p in "${pids[@]}"; do wait $p; done
 $NVCC -gencode arch=compute_100a,code=sm_100a -shared -o ../libpyopal_cuda.so build/*.o -lcudart_static -lpthread -ldl -lrt
 echo built $(pwd)/../libpyopal_cuda.so
-bash "$(dirname "$0")/build_host.sh"
+bash "$(pwd)/build_host.sh"

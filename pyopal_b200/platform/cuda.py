@@ -58,6 +58,12 @@ class OpalSearchResult(ctypes.Structure):
     ]
 
 
+try:  # Cython binding of the hot call, built in-tree by csrc/build_host.sh; ctypes otherwise
+    from . import _cuda_cy as _cy
+except ImportError:  # pragma: no cover - extension not built
+    _cy = None
+
+
 def library_path():
     return os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), _LIB_NAME)
 
@@ -249,11 +255,16 @@ class DeviceStore:
             ops = bytearray(total + 1)
         matrix = int_matrix if isinstance(int_matrix, array.array) else array.array("i", int_matrix)
         alen = int(round(len(matrix) ** 0.5))
-        rc = self._lib.pyopal_cuda_search(
-            self._handle, _addr(query), len(query), gap_open, gap_extend, _addr(matrix), alen, search_type,
-            algorithm, overflow, start, end, _addr(scores), _addr(eq), _addr(et), _addr(sq), _addr(st),
-            _addr(ops), _addr(oo), _addr(ol),
-        )
+        if _cy is not None and isinstance(query, (bytes, bytearray)):
+            # the Cython binding (platform/_cuda_cy.pyx): typed memoryviews, `with nogil` around the C call
+            rc = _cy.search(self._handle.value or 0, query, gap_open, gap_extend, matrix, alen, search_type, algorithm,
+                            overflow, start, end, scores, eq, et, sq, st, ops, oo, ol)
+        else:
+            rc = self._lib.pyopal_cuda_search(
+                self._handle, _addr(query), len(query), gap_open, gap_extend, _addr(matrix), alen, search_type,
+                algorithm, overflow, start, end, _addr(scores), _addr(eq), _addr(et), _addr(sq), _addr(st),
+                _addr(ops), _addr(oo), _addr(ol),
+            )
         check(rc)
         return scores, eq, et, sq, st, ops, oo, ol
 

@@ -316,3 +316,21 @@ def test_database_bulk_ingest_and_persistence(tmp_path):
     assert list(pyopal.Database.load(io.BytesIO(buf.getvalue()))) == seqs
     with pytest.raises(ValueError):
         pyopal.Database.load(io.BytesIO(b"nonsense"))
+
+
+def test_cython_binding_loads_and_reports_errors():
+    # platform/_cuda_cy.pyx: the Cython `with nogil` binding of pyopal_cuda_search (pyx.in:76-91 equivalent).
+    # Without a GPU only the argument / error path can be exercised: a null handle must come back as a
+    # non-zero return code with a message, never a crash.
+    import array
+
+    from pyopal_b200.platform import _cuda_cy, cuda
+
+    assert cuda._cy is _cuda_cy
+    assert _cuda_cy.device_count() == cuda.device_count()
+    matrix = array.array("i", [1] * (24 * 24))
+    scores = array.array("i", [0] * 4)
+    rc = _cuda_cy.search(0, b"\x00\x01", 11, 1, matrix, 24, 0, 3, 0, 0, 4, scores)
+    assert rc != 0 and _cuda_cy.last_error()
+    with pytest.raises(RuntimeError):
+        cuda.check(rc)
