@@ -529,17 +529,16 @@ def run_config5(args):
     t_gen = time.perf_counter() - t0
     res_mine = int(sl.sum())
     t0 = time.perf_counter()
-    store = cuda.DeviceStore(sr, so, np.ascontiguousarray(sl), 24, device=local)
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    # the repo's multi-GPU API: this rank's blocks on its GPU + the block gather (pyopal_b200/sharding.py)
+    sdb = sharding.ShardedDatabase.from_blocks((sr, so, sl), args.block, args.blocks_per_gpu, 24, device=local, stream=stream)
+    store = sdb.store
     t_build = time.perf_counter() - t0
     del sr
     M = pyopal.Aligner(MATRIX, GAP_OPEN, GAP_EXTEND)._int_matrix
-    stream = torch.cuda.Stream()
-    torch.cuda.set_stream(stream)
-    gather = sharding.BlockGather(args.block, args.blocks_per_gpu, world, "cuda")
-    d_local = gather.new_local()
-    gathered = torch.empty(world * gather.n_local, dtype=torch.int32, device="cuda") if world > 1 else None
-    final = torch.empty(gather.n_all, dtype=torch.int32, device="cuda") if world > 1 else None
-    k = min(args.topk, gather.n_all)
+    final = torch.empty(sdb.n_all, dtype=torch.int32, device="cuda") if world > 1 else None
+    k = min(args.topk, sdb.n_all)
     top_v = torch.empty((len(qbytes), k), dtype=torch.int32, device="cuda")
     top_i = torch.empty((len(qbytes), k), dtype=torch.int64, device="cuda")
     host_v = torch.empty((len(qbytes), k), dtype=torch.int32).pin_memory()
@@ -556,22 +555,19 @@ def run_config5(args):
 
     def batch(to_host=False, collect=False):
         for qi, q in enumerate(qbytes):
-            store.search_scores_device(q, GAP_OPEN, GAP_EXTEND, M, 3, d_local.data_ptr(), stream.cuda_stream)
-            stream.synchronize()  # the store's per-search workspace is reused by the next query
+            # search + all-gather + database order, complete on return (like Aligner.align)
+            scores = sdb.search_scores(q, GAP_OPEN, GAP_EXTEND, M, 3, out=final)
             if collect:
                 st = store.stats()
                 acc["k16_us"] += st["k16_us"]
                 acc["launches"] += st["launches"]
                 acc["passes_cols"] += st["passes"]
-            scores = gather.gather(d_local, gathered, final)
             v, i = torch.topk(scores, k)
             top_v[qi].copy_(v)
             top_i[qi].copy_(i)
             if to_host:
                 host_v[qi].copy_(top_v[qi], non_blocking=True)
                 host_i[qi].copy_(top_i[qi], non_blocking=True)
-            if world > 1:
-                stream.synchronize()  # see run_b200: an un-synchronised all-gather delays the next search
         stream.synchronize()
 
     def barrier():
@@ -637,7 +633,7 @@ def run_config5(args):
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "GCUPS", "h2d_bytes_per_step": sum_lq + len(qbytes) * (24 * 24 * 4 + 64),
                     "d2h_bytes_per_step": len(qbytes) * k * 12,
-                    "api": "DeviceStore.search_scores_device (host query in) + BlockGather + top-k, hits to pinned host; wall clock"},
+                    "api": "sharding.ShardedDatabase.search_scores (host query in, NCCL gather) + device top-k, hits to pinned host; wall clock"},
             "roofline": {"bound": "int_alu", "achieved": gcups_k, "peak": roof, "unit": "GCUPS",
                          "frac": (gcups_k / roof) if roof else None, "traffic": None,
                          "alu_thread_instr_per_s": rate, "alu_instr_per_cell_pair": ALU_INSTR_PER_CELL_PAIR,

@@ -134,3 +134,99 @@ class BlockGather:
         # gathered[r, k, i] is target (k * world + r) * block + i
         out.view(self.nb, self.world, self.block).copy_(gathered.view(self.world, self.nb, self.block).permute(1, 0, 2))
         return out
+
+
+class ShardedDatabase:
+    """This rank's shard of a database on its GPU, plus the gather: the multi-GPU form of a score search.
+
+    One process per GPU (``torch.distributed`` initialised by the caller, NCCL backend; a single process
+    without a process group is world size 1).  Two ways to shard:
+
+    * ``ShardedDatabase.deal(residues, offsets, lengths)`` -- every rank holds the packed database on the
+      host; targets are dealt by cumulative cells in snake order over the length-sorted list (config 2);
+    * ``ShardedDatabase.from_blocks(shard, block, blocks_per_rank)`` -- every rank brings its own blocks
+      (block b -> rank b mod world) of a database too large to sort in one place (config 5).
+
+    ``search_scores`` returns the scores of ALL targets in database order as a device tensor on every rank;
+    ``search_topk`` adds a device top-k per query and copies only the hits to the host.
+    """
+
+    def __init__(self, store, gather, n_local, stream=None):
+        import torch
+
+        self.store, self.gather, self.n_local = store, gather, n_local
+        self.world = gather.world
+        self.n_all = gather.n_all
+        self.stream = stream or torch.cuda.current_stream()
+        self._local = gather.new_local()
+        self._gathered = (torch.empty(self.world * len(self._local), dtype=torch.int32, device="cuda")
+                          if self.world > 1 else None)
+        self._torch = torch
+
+    @staticmethod
+    def _world(group=None):
+        import torch.distributed as dist
+
+        if dist.is_available() and dist.is_initialized():
+            return dist.get_world_size(group), dist.get_rank(group)
+        return 1, 0
+
+    @classmethod
+    def deal(cls, residues, offsets, lengths, alphabet_length=24, device=None, group=None, stream=None):
+        from .platform import cuda
+
+        world, rank = cls._world(group)
+        lengths = np.asarray(lengths)
+        mine = shard_indices(lengths, world, rank) if world > 1 else np.arange(len(lengths))
+        sr, so, sl = pack_shard(residues, offsets, lengths, mine) if world > 1 else (residues, offsets, lengths)
+        store = cuda.DeviceStore(sr, so, np.ascontiguousarray(sl), alphabet_length, device=device)
+        self = cls(store, ScoreGather(mine, len(lengths), world, "cuda", group), len(mine), stream)
+        self.local_residues = int(np.asarray(sl, dtype=np.int64).sum())
+        return self
+
+    @classmethod
+    def from_blocks(cls, shard, block, blocks_per_rank, alphabet_length=24, device=None, group=None, stream=None):
+        from .platform import cuda
+
+        world, _ = cls._world(group)
+        residues, offsets, lengths = shard[:3]
+        if len(lengths) != block * blocks_per_rank:
+            raise ValueError("shard does not hold blocks_per_rank blocks")
+        store = cuda.DeviceStore(residues, offsets, np.ascontiguousarray(lengths), alphabet_length, device=device)
+        self = cls(store, BlockGather(block, blocks_per_rank, world, "cuda", group), len(lengths), stream)
+        self.local_residues = int(np.asarray(lengths, dtype=np.int64).sum())
+        return self
+
+    def search_scores(self, query, gap_open, gap_extend, int_matrix, algorithm=3, out=None):
+        """Score ``query`` (encoded bytes) against the whole database; int32 device tensor in database order.
+
+        The call is complete when it returns (search, gather and un-permutation synchronised), like
+        ``Aligner.align``: an un-synchronised all-gather followed by the next search's persistent kernels
+        measured +21 ms per query on two B200s."""
+        self.store.search_scores_device(query, gap_open, gap_extend, int_matrix, algorithm, self._local.data_ptr(),
+                                        self.stream.cuda_stream)
+        self.stream.synchronize()  # the store's per-search workspace is reused by the next query
+        if self.world == 1:  # the local order is the database order; the tensor is reused by the next search
+            return self._local[: self.n_all]
+        res = self.gather.gather(self._local, self._gathered, out)
+        self.stream.synchronize()
+        return res
+
+    def search_topk(self, queries, gap_open, gap_extend, int_matrix, k, algorithm=3, to_host=True):
+        """Batched search: the ``k`` best (score, database index) per query; only the hits leave the device."""
+        torch = self._torch
+        k = min(k, self.n_all)
+        vals = torch.empty((len(queries), k), dtype=torch.int32, device="cuda")
+        idx = torch.empty((len(queries), k), dtype=torch.int64, device="cuda")
+        for qi, q in enumerate(queries):
+            v, i = torch.topk(self.search_scores(q, gap_open, gap_extend, int_matrix, algorithm), k)
+            vals[qi].copy_(v)
+            idx[qi].copy_(i)
+        if not to_host:
+            return vals, idx
+        hv = torch.empty(vals.shape, dtype=vals.dtype).pin_memory()
+        hi = torch.empty(idx.shape, dtype=idx.dtype).pin_memory()
+        hv.copy_(vals, non_blocking=True)
+        hi.copy_(idx, non_blocking=True)
+        self.stream.synchronize()
+        return hv, hi

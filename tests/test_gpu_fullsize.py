@@ -148,3 +148,28 @@ def test_config5_block_batch(cuda, oracle):
         assert rows[qi][idx].tolist() == list(want), qi
         single = np.frombuffer(store.search(q, GO, GE, M, 0, 3)[0], dtype=np.int32)
         assert np.array_equal(single, rows[qi])
+
+
+def test_sharded_database_api_single_rank(cuda, oracle):
+    # sharding.ShardedDatabase at world size 1 (no process group): both ways of sharding, scores in database
+    # order and the batched top-k; the N > 1 gather is covered on CPU by tests/test_sharding_gloo.py
+    import torch
+
+    residues, offsets, lengths = synthetic.database(77, 3000, 5.0, 0.7, 1, 2500, giants=(6000, 4500))
+    M = pyopal.Aligner("BLOSUM62", GO, GE)._int_matrix
+    queries = [q.tobytes() for q in synthetic.config5_queries(3)]
+    sdb = sharding.ShardedDatabase.deal(residues, offsets, lengths, device=0)
+    assert sdb.world == 1 and sdb.n_all == len(lengths)
+    want = [oracle.search_flat(q, residues.tobytes() + b"\0", array.array("q", offsets.tolist()),
+                               array.array("i", lengths.tolist()), M, 24, GO, GE, "sw", "score", 8)["score"] for q in queries]
+    for q, w in zip(queries, want):
+        assert sdb.search_scores(q, GO, GE, M).cpu().tolist() == list(w)
+    vals, idx = sdb.search_topk(queries, GO, GE, M, 10)
+    for qi, w in enumerate(want):
+        w = torch.tensor(list(w))
+        assert vals[qi].tolist() == torch.topk(w, 10).values.tolist()
+        assert w[idx[qi]].tolist() == vals[qi].tolist()
+    blk = sharding.ShardedDatabase.from_blocks((residues, offsets, lengths), 1500, 2, device=0)
+    assert blk.search_scores(queries[0], GO, GE, M).cpu().tolist() == list(want[0])
+    with pytest.raises(ValueError):
+        sharding.ShardedDatabase.from_blocks((residues, offsets, lengths), 1000, 2, device=0)
