@@ -134,6 +134,21 @@ int pyopal_cuda_search_batch(pyopal_cuda_db* db, const unsigned char* queries, c
                              const int32_t* q_lengths, int nq, int gapOpen, int gapExt,
                              const int* scoreMatrix, int alphabetLength, int mode, int32_t* scores);
 
+/* The k best hits of a SCORE-mode search, selected on the device (topk.cu): `scores` / `indices` are HOST
+ * buffers of k entries, filled with min(k, end - start) hits sorted by score descending, ties by ascending
+ * database index (absolute, like ScoreResult.target_index, pyx.in:69); *n_hits receives their number.
+ * Additive: the reference returns every target (pyx.in:65-72) and leaves the sort to the caller
+ * (docs/examples/abc.ipynb cells 23-24). */
+int pyopal_cuda_search_topk(pyopal_cuda_db* db, const unsigned char* query, int queryLength, int gapOpen,
+                            int gapExt, const int* scoreMatrix, int alphabetLength, int mode, int64_t start,
+                            int64_t end, int k, int32_t* scores, int32_t* indices, int32_t* n_hits);
+
+/* The same selection over a DEVICE array of n int32 scores (e.g. the gathered scores of a sharded search):
+ * d_scores_out / d_indices_out are DEVICE buffers of k entries, written UNSORTED (every score above the k-th
+ * largest, then the lowest-index ties); k <= n.  Enqueued on `stream`. */
+int pyopal_cuda_topk_device(pyopal_cuda_db* db, const int32_t* d_scores, int64_t n, int k, int32_t* d_scores_out,
+                            int32_t* d_indices_out, void* stream);
+
 /* Statistics of the last search on this handle (for bench.py / profiles):
  * stats[0]=kernel launches, [1]=targets scored at 16 bit, [2]=targets scored
  * at 32 bit (static), [3]=targets escalated 16->32 after overflow,

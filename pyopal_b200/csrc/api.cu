@@ -87,6 +87,7 @@ void pyopal_cuda_db_destroy(pyopal_cuda_db* db) {
     db->query.release(); db->gprofile.release(); db->wprofile.release();
     db->bndH.release(); db->bndF.release(); db->bnd32H.release(); db->bnd32F.release();
     db->pd_i32.release(); db->pd_tb.release(); db->pd_ops.release(); db->pd_bnd.release(); db->pd_jobs.release();
+    db->tk_ws.release(); db->tk_vals.release(); db->tk_idx.release();
     if (db->ev_fork) cudaEventDestroy(db->ev_fork);
     if (db->ev_join) cudaEventDestroy(db->ev_join);
     if (db->side) cudaStreamDestroy(db->side);
@@ -992,6 +993,60 @@ extern "C" int pyopal_cuda_search_batch(pyopal_cuda_db* db, const unsigned char*
 #undef CUB
     cleanup();
     return rc;
+}
+
+extern "C" int pyopal_cuda_topk_device(pyopal_cuda_db* db, const int32_t* d_scores, int64_t n, int k,
+                                       int32_t* d_scores_out, int32_t* d_indices_out, void* stream) {
+    if (!db || (n > 0 && k > 0 && (!d_scores || !d_scores_out || !d_indices_out))) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null argument");
+    if (k < 0 || n < 0 || k > n || n > INT32_MAX) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "top-k needs 0 <= k <= n < 2^31");
+    std::lock_guard<std::mutex> lock(db->mu);
+    CU(cudaSetDevice(db->device));
+    if (db->tk_ws.reserve(topk_workspace_words())) return PYOPAL_CUDA_ERR_NOMEM;
+    return topk_device(d_scores, n, k, d_scores_out, d_indices_out, db->tk_ws.p, db->sm_count, (cudaStream_t)stream);
+}
+
+extern "C" int pyopal_cuda_search_topk(pyopal_cuda_db* db, const unsigned char* query, int queryLength, int gapOpen,
+                                       int gapExt, const int* scoreMatrix, int alphabetLength, int mode, int64_t start,
+                                       int64_t end, int k, int32_t* scores, int32_t* indices, int32_t* n_hits) {
+    int rc = check_search_args(db, query, queryLength, gapOpen, gapExt, scoreMatrix, alphabetLength, mode, &start, &end);
+    if (rc) return rc;
+    if (k < 0) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "negative k");
+    const int64_t nout = end - start;
+    const int kk = (int)std::min<int64_t>(k, nout);
+    if (n_hits) *n_hits = kk > 0 ? kk : 0;
+    if (kk <= 0) return 0;
+    if (!scores || !indices) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null output");
+    std::lock_guard<std::mutex> lock(db->mu);
+    CU(cudaSetDevice(db->device));
+    if (db->out.reserve((size_t)nout) || db->tk_ws.reserve(topk_workspace_words()) || db->tk_vals.reserve((size_t)kk) ||
+        db->tk_idx.reserve((size_t)kk))
+        return PYOPAL_CUDA_ERR_NOMEM;
+    CU(cudaEventRecord(db->ev0, db->stream));
+    rc = enqueue_score_search(db, query, queryLength, gapOpen, gapExt, scoreMatrix, alphabetLength, mode, start, end,
+                              db->out.p, db->stream);
+    if (rc) return rc;
+    rc = topk_device(db->out.p, nout, kk, db->tk_vals.p, db->tk_idx.p, db->tk_ws.p, db->sm_count, db->stream);
+    if (rc) return rc;
+    db->stats[0] += 9;
+    std::vector<int32_t> v((size_t)kk), ix((size_t)kk);
+    CU(cudaMemcpyAsync(v.data(), db->tk_vals.p, (size_t)kk * sizeof(int32_t), cudaMemcpyDeviceToHost, db->stream));
+    CU(cudaMemcpyAsync(ix.data(), db->tk_idx.p, (size_t)kk * sizeof(int32_t), cudaMemcpyDeviceToHost, db->stream));
+    CU(cudaEventRecord(db->ev1, db->stream));
+    CU(cudaStreamSynchronize(db->stream));
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, db->ev0, db->ev1));
+    db->stats[4] = (int64_t)(ms * 1000.0f);
+    // the k hits: score descending, ties by ascending database index
+    std::vector<int32_t> order((size_t)kk);
+    std::iota(order.begin(), order.end(), 0);
+    std::sort(order.begin(), order.end(), [&](int32_t a, int32_t b) {
+        return v[(size_t)a] != v[(size_t)b] ? v[(size_t)a] > v[(size_t)b] : ix[(size_t)a] < ix[(size_t)b];
+    });
+    for (int i = 0; i < kk; i++) {
+        scores[i] = v[(size_t)order[(size_t)i]];
+        indices[i] = (int32_t)(ix[(size_t)order[(size_t)i]] + start);
+    }
+    return 0;
 }
 
 // Generic path with the reference's own signature (opal.pxd:40-54): stage the

@@ -7,6 +7,7 @@
 #include "kernels.cuh"
 
 #include <cuda_runtime.h>
+#include <algorithm>
 #include <cstdint>
 #include <mutex>
 #include <string>
@@ -52,6 +53,11 @@ struct DevBuf {
 
 constexpr int PAD_ALIGN_COLS = 8;  // pair streams start on 16-byte boundaries
 
+// topk.cu: exact device-side selection of the k best scores (ties to the lower index)
+size_t topk_workspace_words();
+int topk_device(const int32_t* d_scores, int64_t n, int k, int32_t* d_vals, int32_t* d_idx, uint32_t* ws, int sm_count,
+                cudaStream_t st);
+
 }  // namespace pyopal
 
 struct pyopal_cuda_db {
@@ -96,6 +102,9 @@ struct pyopal_cuda_db {
     pyopal::DevBuf<uint8_t> pd_ops;     // alignment operations
     pyopal::DevBuf<int32_t> pd_bnd;     // pass boundary rows (H, F)
     pyopal::DevBuf<uint8_t> pd_jobs;    // PairJob records
+    // top-k selection (topk.cu)
+    pyopal::DevBuf<uint32_t> tk_ws;
+    pyopal::DevBuf<int32_t> tk_vals, tk_idx;
 };
 
 

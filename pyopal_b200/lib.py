@@ -1021,6 +1021,37 @@ class Aligner:
             return store.search(encoded, self.gap_open, self.gap_extend, self._int_matrix,
                                 _cuda.OPAL_SEARCH_SCORE, _algo, start=start, end=end)[0]
 
+    def align_topk(self, query, database, k, *, algorithm="sw", start=0, end=UINT32_MAX):
+        """The ``k`` best targets for ``query``: a list of `ScoreResult` sorted by score (descending), ties by
+        target index.
+
+        Additive to the reference API.  The reference returns one object per target
+        (pyx.in:65-72) and the caller sorts them to pick the hits worth re-aligning in ``"full"`` mode
+        (docs/examples/abc.ipynb); here the selection runs on the device (csrc/topk.cu) and only ``k``
+        (score, index) pairs come back.
+        """
+        if not isinstance(database, Database):
+            raise TypeError("align_topk needs a pyopal Database (device-resident store)")
+        if k < 0:
+            raise ValueError("k must be non-negative")
+        _, _, _algo = self._validate("score", "buckets", algorithm)
+        if database.alphabet != self.alphabet:
+            raise ValueError("database and score matrix have different alphabets")
+        encoded = database.alphabet.encode(query)
+        with database.lock.read:
+            size = database.get_size()
+            if end < start:
+                raise IndexError("database slice end is lower than start")
+            end = min(end, size)
+            if start > end:
+                raise IndexError("database slice start is past the end")
+            if end == start or k == 0:
+                return []
+            store = database._device_store()
+            scores, indices = store.search_topk(encoded, self.gap_open, self.gap_extend, self._int_matrix, _algo, k,
+                                                start=start, end=end)
+        return [ScoreResult(int(i), int(s)) for s, i in zip(scores, indices)]
+
     def align_batch(self, queries, database, *, algorithm="sw"):
         """Score several queries against the whole database in one device-side pipeline.
 

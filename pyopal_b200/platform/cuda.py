@@ -105,6 +105,10 @@ def load_library():
         lib.pyopal_cuda_search_scores_device.argtypes = [vp, vp, ci, ci, ci, vp, ci, ci, i64, i64, vp, vp]
         lib.pyopal_cuda_search_batch.restype = ci
         lib.pyopal_cuda_search_batch.argtypes = [vp, vp, vp, vp, ci, ci, ci, vp, ci, ci, vp]
+        lib.pyopal_cuda_search_topk.restype = ci
+        lib.pyopal_cuda_search_topk.argtypes = [vp, vp, ci, ci, ci, vp, ci, ci, i64, i64, ci, vp, vp, ctypes.POINTER(ci)]
+        lib.pyopal_cuda_topk_device.restype = ci
+        lib.pyopal_cuda_topk_device.argtypes = [vp, vp, i64, ci, vp, vp, vp]
         lib.pyopal_cuda_last_stats.restype = ci
         lib.pyopal_cuda_last_stats.argtypes = [vp, _c_i64p, ci]
         lib.pyopal_cuda_int_issue_rate.restype = ci
@@ -280,6 +284,28 @@ class DeviceStore:
                 start, end, d_scores, stream,
             )
         )
+
+    def search_topk(self, query, gap_open, gap_extend, int_matrix, algorithm, k, start=0, end=None):
+        """The ``k`` best hits of a score search, selected on the device: ``(scores, indices)`` as
+        ``array('i')``, score descending, ties by ascending (absolute) database index."""
+        end = self.size if end is None or end > self.size else end
+        k = max(0, min(int(k), max(end - start, 0)))
+        scores = array.array("i", bytes(4 * k))
+        indices = array.array("i", bytes(4 * k))
+        matrix = int_matrix if isinstance(int_matrix, array.array) else array.array("i", int_matrix)
+        alen = int(round(len(matrix) ** 0.5))
+        n_hits = ctypes.c_int(0)
+        check(
+            self._lib.pyopal_cuda_search_topk(
+                self._handle, _addr(query), len(query), gap_open, gap_extend, _addr(matrix), alen, algorithm,
+                start, end, k, _addr(scores), _addr(indices), ctypes.byref(n_hits),
+            )
+        )
+        return scores[: n_hits.value], indices[: n_hits.value]
+
+    def topk_device(self, d_scores, n, k, d_scores_out, d_indices_out, stream=0):
+        """Device-side selection over ``n`` int32 scores at device pointer ``d_scores`` (unsorted output)."""
+        check(self._lib.pyopal_cuda_topk_device(self._handle, d_scores, n, k, d_scores_out, d_indices_out, stream))
 
     def kernel_times(self):
         """Resolve the per-kernel CUDA events of the last search (call after synchronising its stream)."""

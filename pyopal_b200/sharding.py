@@ -217,16 +217,20 @@ class ShardedDatabase:
         torch = self._torch
         k = min(k, self.n_all)
         vals = torch.empty((len(queries), k), dtype=torch.int32, device="cuda")
-        idx = torch.empty((len(queries), k), dtype=torch.int64, device="cuda")
+        idx = torch.empty((len(queries), k), dtype=torch.int32, device="cuda")
         for qi, q in enumerate(queries):
-            v, i = torch.topk(self.search_scores(q, gap_open, gap_extend, int_matrix, algorithm), k)
-            vals[qi].copy_(v)
-            idx[qi].copy_(i)
+            scores = self.search_scores(q, gap_open, gap_extend, int_matrix, algorithm)
+            # exact radix select on the device (csrc/topk.cu), unsorted; ties go to the lower database index
+            self.store.topk_device(scores.data_ptr(), self.n_all, k, vals[qi].data_ptr(), idx[qi].data_ptr(),
+                                   self.stream.cuda_stream)
         if not to_host:
+            self.stream.synchronize()
             return vals, idx
         hv = torch.empty(vals.shape, dtype=vals.dtype).pin_memory()
         hi = torch.empty(idx.shape, dtype=idx.dtype).pin_memory()
         hv.copy_(vals, non_blocking=True)
         hi.copy_(idx, non_blocking=True)
         self.stream.synchronize()
-        return hv, hi
+        # order the k hits of every query: score descending, ties by ascending index
+        order = np.lexsort((hi.numpy(), -hv.numpy().astype(np.int64)), axis=1)
+        return torch.from_numpy(np.take_along_axis(hv.numpy(), order, 1)), torch.from_numpy(np.take_along_axis(hi.numpy(), order, 1))

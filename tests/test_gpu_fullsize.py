@@ -168,7 +168,7 @@ def test_sharded_database_api_single_rank(cuda, oracle):
     for qi, w in enumerate(want):
         w = torch.tensor(list(w))
         assert vals[qi].tolist() == torch.topk(w, 10).values.tolist()
-        assert w[idx[qi]].tolist() == vals[qi].tolist()
+        assert w[idx[qi].long()].tolist() == vals[qi].tolist()
     blk = sharding.ShardedDatabase.from_blocks((residues, offsets, lengths), 1500, 2, device=0)
     assert blk.search_scores(queries[0], GO, GE, M).cpu().tolist() == list(want[0])
     with pytest.raises(ValueError):

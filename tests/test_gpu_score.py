@@ -272,3 +272,56 @@ def test_concurrent_aligners_share_a_database(cuda, oracle):
     # result objects from threads as well (pyopal.align(threads=...) maps onto the same call)
     res = list(pyopal.align(query_str(aligner, queries[2]), db, "BLOSUM62", gap_open=11, gap_extend=1, algorithm=algos[2], threads=3, ordered=True))
     assert [r.score for r in res] == want[2]
+
+
+def _expected_topk(scores, k):
+    order = sorted(range(len(scores)), key=lambda i: (-scores[i], i))[:k]
+    return [scores[i] for i in order], order
+
+
+@pytest.mark.parametrize("algo", ALGOS)
+def test_topk_matches_sorted_oracle(cuda, oracle, algo):
+    # csrc/topk.cu: exact radix select on the device; ties go to the lower database index.  Short queries give
+    # many equal scores, NW/HW give negative ones (the key is order-preserving over the whole int32 range)
+    seqs = rand_seqs(401, 5000, 4.5, 0.7, 0, 900) + [b""]
+    aligner = pyopal.Aligner("BLOSUM62", 11, 1)
+    db = make_db(seqs, aligner.alphabet)
+    for lq in (7, 120):
+        q = rand_query(410 + lq, lq)
+        want = oracle.search(q, seqs, aligner._int_matrix, 24, 11, 1, algo, "score", threads=8)["score"]
+        for k in (1, 10, 257, 5000, len(seqs), len(seqs) + 5):
+            hits = aligner.align_topk(query_str(aligner, q), db, k, algorithm=algo)
+            ws, wi = _expected_topk(want, k)
+            assert [h.score for h in hits] == ws, (algo, lq, k)
+            assert [h.target_index for h in hits] == wi, (algo, lq, k)
+    # slices report absolute indices
+    q = rand_query(499, 60)
+    want = oracle.search(q, seqs, aligner._int_matrix, 24, 11, 1, algo, "score", threads=8)["score"]
+    hits = aligner.align_topk(query_str(aligner, q), db, 25, algorithm=algo, start=1000, end=3000)
+    ws, wi = _expected_topk(want[1000:3000], 25)
+    assert [h.score for h in hits] == ws and [h.target_index for h in hits] == [i + 1000 for i in wi]
+    assert aligner.align_topk(query_str(aligner, q), db, 0) == []
+
+
+def test_topk_all_equal_and_large(cuda):
+    # every target identical: the k lowest indices; and a 2e6-entry device array through the device entry
+    aligner = pyopal.Aligner("BLOSUM62", 11, 1)
+    db = make_db([rand_query(5, 50)] * 3000, aligner.alphabet)
+    hits = aligner.align_topk(query_str(aligner, rand_query(5, 50)), db, 40)
+    assert [h.target_index for h in hits] == list(range(40)) and len({h.score for h in hits}) == 1
+    import torch
+
+    g = torch.Generator().manual_seed(3)
+    scores = torch.randint(-70000, 70000, (2_000_003,), generator=g, dtype=torch.int32)
+    scores[::7] = 123  # a fat tie class
+    d = scores.cuda()
+    store = db._device_store()
+    for k in (1, 1000, 300_000):
+        vals = torch.empty(k, dtype=torch.int32, device="cuda")
+        idx = torch.empty(k, dtype=torch.int32, device="cuda")
+        store.topk_device(d.data_ptr(), d.numel(), k, vals.data_ptr(), idx.data_ptr(), torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        v, i = vals.cpu().numpy(), idx.cpu().numpy()
+        order = np.lexsort((i, -v.astype(np.int64)))
+        ref = np.lexsort((np.arange(scores.numel()), -scores.numpy().astype(np.int64)))[:k]
+        assert np.array_equal(i[order], ref) and np.array_equal(v[order], scores.numpy()[ref])
