@@ -552,7 +552,10 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
     GiantPolicy gpol;
     int gK = 4, gwarps = 1, gteams = 1, gpitch = 0;
     size_t gsmem = 0;
-    if (make_rung(M, A, go, ge, mode, 0).fits8 && Lq <= 8192 && !getenv("PYOPAL_CUDA_NO_GIANT")) {
+    // gap_extend > gap_open: NW's padding rows need the border fix of the 32-bit kernel (kernels.cuh, BFIX); the
+    // giant kernels do not carry it, so everything stays on search_kernel then
+    const bool bfix = (mode == MODE_NW && ge > go);
+    if (make_rung(M, A, go, ge, mode, 0).fits8 && Lq <= 8192 && !bfix && !getenv("PYOPAL_CUDA_NO_GIANT")) {
         gK = (Lq <= 2048) ? 4 : (Lq <= 4096) ? 8 : 16;            // rows per lane
         gwarps = ((Lq + gK - 1) / gK + 31) / 32;                  // warps per team (<= 16): the whole query in one pass
         gteams = (gwarps == 1) ? 16 : std::min(15, 16 / gwarps);  // teams per 512-thread CTA (15 named barriers)
@@ -600,7 +603,7 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
     const int Lp = std::max(bulk.npass * bulk.G * bulk.K, tail.npass * tail.G * tail.K);
     Rung rung = make_rung(M, A, go, ge, mode, Lp);
     const bool wide = !rung.fits8;
-    if (wide || !bulk.psmem || !tail.psmem) {
+    if (wide || bfix || !bulk.psmem || !tail.psmem) {
         // profile in global memory: one tile shape (32 x 32) for every launch
         bulk = make_forced_plan(Lq);
         tail = bulk;
@@ -735,7 +738,7 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
         P.wprofile = db->wprofile.p;
         build_profile_kernel<<<64, 256, 0, st>>>(P, nullptr, db->wprofile.p);
         CU(cudaGetLastError());
-        k32 = get_search_kernel_wide(local);
+        k32 = bfix ? get_search_kernel_bfix(true) : get_search_kernel_wide(local);
     } else {
         if (!tail.psmem) {
             apply_plan(P, tail);
@@ -744,7 +747,7 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
             build_profile_kernel<<<64, 256, 0, st>>>(P, db->gprofile.p, nullptr);
             CU(cudaGetLastError());
         }
-        k32 = pick_kernel(tail.K, 32, local, tail.psmem);
+        k32 = bfix ? get_search_kernel_bfix(false) : pick_kernel(tail.K, 32, local, tail.psmem);
     }
     if (!k32) return fail(PYOPAL_CUDA_ERR_INTERNAL, "no 32-bit kernel for this tile");
 

@@ -189,12 +189,19 @@ template <int W> struct CellConsts {
 // previous column, upGprev = H - open of the row above in the previous column,
 // F / Gup = (F, H - open) of the row above in this column.  Out: E, Gl of this
 // column, F / Gup of the thread's last row (for the thread below), best.
-template <int K, int W, bool LOCAL, bool PSMEM, bool WIDE, bool TDADD, bool SHORTF_ = (W == 16)>
+//
+// BFIX (long F chain only): with gap_extend > gap_open the padding rows above query row 0 cannot reproduce NW's
+// penalised top border (re-opening a gap is then cheaper than extending it, so their E path beats the border
+// value); the thread that holds the LAST padding row (register `fixrow`) overwrites its output with the border
+// H[-1][j] - open (`fixG`) and an empty F, which is exactly what the first query row must see.
+template <int K, int W, bool LOCAL, bool PSMEM, bool WIDE, bool TDADD, bool SHORTF_ = (W == 16), bool BFIX = false>
 __device__ __forceinline__ void column_update(const KParams& P, const int8_t* prof, unsigned t0, unsigned t1, int pslot,
                                               const CellConsts<W>& C, typename Val<W>::T (&E)[K],
                                               typename Val<W>::T (&Gl)[K], typename Val<W>::T upGprev,
                                               typename Val<W>::T& F, typename Val<W>::T& Gup,
-                                              typename Val<W>::T& best) {
+                                              typename Val<W>::T& best, int fixrow = -1,
+                                              typename Val<W>::T fixG = 0) {
+    static_assert(!BFIX || !SHORTF_, "the border fix lives in the long F chain");
     typedef Val<W> V;
     typedef typename V::T val_t;
     constexpr bool ADDPATH = TDADD || (W == 32);
@@ -263,6 +270,7 @@ __device__ __forceinline__ void column_update(const KParams& P, const int8_t* pr
             const val_t Hn = (LOCAL && !ADDPATH) ? V::max3(Gl[r], F, FLOOR) : V::max2(Gl[r], F);
             if (LOCAL) best = V::max2(best, Hn);
             Gup = V::add(Hn, NEGOPEN, one);
+            if (BFIX && r == fixrow) { Gup = fixG; F = C.NEG; }
             Gl[r] = Gup;
         }
     }
@@ -271,8 +279,9 @@ __device__ __forceinline__ void column_update(const KParams& P, const int8_t* pr
 // TDADD: every profile entry (S + open, padding included) is >= 0, so the
 // 16-bit rung may form Hdiag + S with a 32-bit IMAD; otherwise that add stays
 // in the packed adder of VIADDMNMX.  (Ignored by the 32-bit rung.)
-template <int K, int W, bool LOCAL, bool PSMEM, bool WIDE = false, bool TDADD = true>
+template <int K, int W, bool LOCAL, bool PSMEM, bool WIDE = false, bool TDADD = true, bool BFIX = false>
 __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KParams P) {
+    static_assert(!BFIX || (W == 32 && !LOCAL), "border fix: 32-bit rung, NW");
     static_assert(K % 4 == 0, "K must be a multiple of 4");
     static_assert(!WIDE || (W == 32 && !PSMEM), "wide profile: 32-bit rung, global memory only");
     typedef Val<W> V;
@@ -394,7 +403,15 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
                     const unsigned t0 = (W == 16) ? (code & 0xffu) : (half ? (code >> 8) : (code & 0xffu));
                     const unsigned t1 = code >> 8;
                     val_t F = upF, Gup = upG;
-                    column_update<K, W, LOCAL, PSMEM, WIDE, TDADD>(P, prof, t0, t1, (pass * G + p) * P.kstride, C, E, Gl, upGprev, F, Gup, best);
+                    if (BFIX) {
+                        const int fr = P.padtop - 1 - rowbase;  // register that holds the last padding row, if any
+                        const bool mine = (pass == 0) && (fr >= 0) && (fr < K);
+                        column_update<K, W, LOCAL, PSMEM, WIDE, TDADD, false, BFIX>(
+                            P, prof, t0, t1, (pass * G + p) * P.kstride, C, E, Gl, upGprev, F, Gup, best, mine ? fr : -1,
+                            V::splat(-(P.go + j * P.ge) - P.go + B));
+                    } else {
+                        column_update<K, W, LOCAL, PSMEM, WIDE, TDADD>(P, prof, t0, t1, (pass * G + p) * P.kstride, C, E, Gl, upGprev, F, Gup, best);
+                    }
                     Gout = Gup;
                     Fout = F;
                     upGprev = upG;
@@ -475,6 +492,8 @@ search_kernel_t get_search_kernel_w16_l0(int K, bool psmem, bool tdadd);
 search_kernel_t get_search_kernel_w32_l1(int K, bool psmem);
 search_kernel_t get_search_kernel_w32_l0(int K, bool psmem);
 search_kernel_t get_search_kernel_wide(bool local);  // K = 32, W = 32
+// NW with gap_extend > gap_open: K = 32, W = 32, profile in global memory (int8, or int32 when `wide`)
+search_kernel_t get_search_kernel_bfix(bool wide);
 // giant.cu: a team of warps per target (KParams.G = warps per team, KParams.npass = teams per CTA), K = 4 or 8
 search_kernel_t get_giant_kernel(int K, bool local);
 size_t giant_smem_bytes(int A, int pitch, int warps_per_team, int teams);

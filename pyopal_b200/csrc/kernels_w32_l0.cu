@@ -17,4 +17,7 @@ search_kernel_t get_search_kernel_w32_l0(int K, bool psmem) {
         default: return nullptr;
     }
 }
+search_kernel_t get_search_kernel_bfix(bool wide) {
+    return wide ? search_kernel<32, 32, false, false, true, true, true> : search_kernel<32, 32, false, false, false, true, true>;
+}
 }  // namespace pyopal

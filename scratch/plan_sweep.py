@@ -27,5 +27,5 @@ if len(sys.argv) > 1 and sys.argv[1] == "worker":
             except Exception as e:
                 print(f"Lq={len(q)} plan={plan} failed: {e}", flush=True)
 else:
-    plans = ["", "2,36,224", "2,32,256", "2,32,320", "2,28,320", "3,40,224", "3,32,256", "3,32,320", "3,36,224", "3,28,320", "3,24,384", "4,32,256", "4,40,224", "5,40,224", "5,32,256"]
+    plans = ["", "2,36,224", "2,36,256", "2,36,192", "2,32,256", "2,32,288", "2,40,224", "2,40,256", "3,36,224", "3,36,256", "3,40,224", "3,40,256"]
     subprocess.check_call([sys.executable, __file__, "worker", json.dumps(plans)])
