@@ -105,3 +105,77 @@ def test_fuzz_end_full(cuda, oracle, seed):
                         aligner.align(alphabet.decode(query), make_db(seqs, alphabet), algorithm=algo, mode=mode)
                     continue
             check_mode(oracle, aligner, query, seqs, algo, mode, db=make_db(seqs, alphabet))
+
+
+@pytest.mark.parametrize("seed", range(max(30, N_SCORE // 2)))
+def test_fuzz_forced_tiles(cuda, oracle, monkeypatch, seed):
+    # the same cases under a FORCED bulk tile (PYOPAL_CUDA_PLAN=logG,K): narrow tiles turn a 300-row query into
+    # dozens of passes (boundary rows through the L2 buffer, padding rows above row 0), wide ones leave most lanes
+    # of a group on padding; slices and the transposed-giant shapes are drawn as well
+    rng = np.random.Generator(np.random.PCG64(9000 + seed))
+    letters, rows, go, ge, query, seqs = _case(2000 + seed)
+    monkeypatch.setenv("PYOPAL_CUDA_PLAN", f"{int(rng.integers(2, 6))},{4 * int(rng.integers(1, 11))}")
+    if rng.random() < 0.5:
+        monkeypatch.setenv("PYOPAL_CUDA_TGIANT", f"{int(rng.integers(1, 9))},{int(rng.choice([16, 32]))},{int(rng.choice([0, 700, 2000]))}")
+    alphabet = pyopal.Alphabet(letters)
+    aligner = pyopal.Aligner(pyopal.ScoringMatrix(rows, letters), go, ge)
+    db = make_db(seqs, alphabet)
+    flat = [int(v) for row in rows for v in row]
+    lo = int(rng.integers(0, len(seqs)))
+    hi = int(rng.integers(lo, len(seqs) + 1))
+    for algo in ALGOS:
+        want = oracle.search(query, seqs, flat, len(letters), go, ge, algo, "score", threads=8)["score"]
+        got = list(aligner.align_scores(alphabet.decode(query), db, algorithm=algo))
+        assert got == want, (seed, algo, go, ge, os.environ["PYOPAL_CUDA_PLAN"])
+        part = list(aligner.align_scores(alphabet.decode(query), db, algorithm=algo, start=lo, end=hi))
+        assert part == want[lo:hi], (seed, algo, lo, hi)
+        k = int(rng.integers(1, len(seqs) + 2))
+        hits = aligner.align_topk(alphabet.decode(query), db, k, algorithm=algo)
+        order = sorted(range(len(want)), key=lambda i: (-want[i], i))[:k]
+        assert [(h.target_index, h.score) for h in hits] == [(i, want[i]) for i in order], (seed, algo, k)
+
+
+def test_sw_overflow_threshold_is_exact(cuda, oracle):
+    # scores spread densely around the 16 -> 32 bit escalation threshold (65535 - 129 - bias): pairs where the low
+    # target, the high target, both or neither overflow must all come back exact
+    import synthetic
+
+    aligner = pyopal.Aligner("BLOSUM62", 11, 1)
+    W, C = synthetic.ALPHABET.index("W"), synthetic.ALPHABET.index("C")  # 11 and 9 on the diagonal
+    rng = np.random.Generator(np.random.PCG64(77))
+    query = np.full(6300, W, dtype=np.uint8)
+    query[rng.choice(6300, 930, replace=False)] = C
+    seqs = []
+    for n in range(5950, 6300, 3):  # identical prefixes: score = sum of the diagonal, 63.7k .. 67.4k in steps of ~30
+        seqs.append(query[:n].tobytes())
+    for n in rng.integers(6040, 6140, size=40):  # and prefixes with a few mismatches: every residue class
+        t = query[: int(n)].copy()
+        t[rng.choice(int(n), int(rng.integers(1, 6)), replace=False)] = synthetic.ALPHABET.index("A")
+        seqs.append(t.tobytes())
+    db = make_db(seqs, aligner.alphabet)
+    got = list(aligner.align_scores(aligner.alphabet.decode(query.tobytes()), db))
+    want = oracle.search(query.tobytes(), seqs, aligner._int_matrix, 24, 11, 1, "sw", "score", threads=8)["score"]
+    assert got == want
+    assert min(want) < 64500 and max(want) > 65800
+    st = db._device_store().stats()
+    assert st["escalated"] > 0 or st["targets32"] > 0
+
+
+@pytest.mark.parametrize("algo", ("nw", "hw", "ov"))
+@pytest.mark.parametrize("gaps", [(11, 4), (3, 2), (20, 8)])
+def test_static_16bit_bound_edge(cuda, oracle, algo, gaps):
+    # NW / HW / OV: targets whose length straddles the static bound up to which the 16-bit rung is exact
+    # (|score| ~ open + len * ext close to 32768 - slack); both sides of the cut must be exact
+    import synthetic
+
+    go, ge = gaps
+    aligner = pyopal.Aligner("BLOSUM62", go, ge)
+    rng = np.random.Generator(np.random.PCG64(88))
+    cut = (32768 - ge - 512 - 3 * go) // ge
+    lens = list(range(cut - 420, cut + 60, 23)) + [cut - 130 + d for d in range(-3, 4)] + [200, 5, 900]
+    seqs = [synthetic.random_residues(rng, n).tobytes() for n in lens]
+    for lq in (100, 260):
+        q = synthetic.random_residues(rng, lq).tobytes()
+        got = list(aligner.align_scores(aligner.alphabet.decode(q), make_db(seqs, aligner.alphabet), algorithm=algo))
+        want = oracle.search(q, seqs, aligner._int_matrix, 24, go, ge, algo, "score", threads=8)["score"]
+        assert got == want, (algo, gaps, lq, [(i, a, b, lens[i]) for i, (a, b) in enumerate(zip(got, want)) if a != b][:5])
