@@ -503,14 +503,16 @@ void apply_plan(KParams& P, const Plan& pl) {
 
 // Enqueue a SCORE search of [start, end) on `st`; scores land in d_out (device).
 //
-// Up to four launches:
-//   bulk  : 16-bit rung, throughput tile (make_plan), 256-thread CTAs, on `st`
-//   tail  : 16-bit rung for the longest pairs, one warp per pair with the
-//           latency tile (32 threads x few rows), on the side stream
-//   wide32: 32-bit rung for pairs the 16-bit rung cannot hold exactly
-//           (NW/HW/OV static bound), latency tile, side stream
-//   rescue: 32-bit rescore of SW targets whose 16-bit running max overflowed;
-//           its work list is produced on the device by bulk/tail.
+// Launches (all optional but the bulk):
+//   tgiants: targets longer than one slab of tgiant.cu when the query is short enough for it, 32 bit, one CTA
+//            per target, on the second high-priority stream
+//   giants : the other "long" pairs chosen with the tile (make_plan), giant.cu, 32 bit, high-priority side stream
+//   wide32 : 32-bit rung for pairs the 16-bit rung cannot hold exactly (NW/HW/OV static bound, or gap costs /
+//            scores outside its range: then every pair), latency tile, side stream
+//   tail   : 16-bit rung for the longest pairs, one warp per pair, only when no giant kernel can take the query
+//   bulk   : 16-bit rung, throughput tile (make_plan), persistent 224/480-thread CTAs, on `st`
+//   rescue : 32-bit rescore of SW targets whose 16-bit running max overflowed; its work list is produced on the
+//            device by bulk/tail.
 int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq, int go, int ge,
                          const int* M, int A, int mode, int64_t start, int64_t end, int32_t* d_out,
                          cudaStream_t st) {
