@@ -363,7 +363,11 @@ Plan make_plan(int Lq, int A, const pyopal_cuda_db* db, size_t smem_limit, Giant
     int64_t best_kg = 0;
     for (int logG = 2; logG <= 5; logG++) {
         const int G = 1 << logG;
-        const double L_even = (double)db->ncols * G / (448.0 * db->sm_count);
+        // calibrated on 1/2, 1/4 and 1/8 shards of config 2 (scratch/shard_sweep.py): groups of 8+ lanes reach the
+        // critical path about 25 % earlier than 448 / G groups per SM suggest; 4-lane groups do not
+        static const double solo_env = getenv("PYOPAL_CUDA_SOLO") ? atof(getenv("PYOPAL_CUDA_SOLO")) : 0.0;
+        const double solo = solo_env > 0 ? solo_env : (G == 4 ? 448.0 : 560.0);
+        const double L_even = (double)db->ncols * G / (solo * db->sm_count);
         int64_t kg = 0;
         double giant_cols = 0;
         if (gp && gp->ok) {
@@ -568,7 +572,8 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
         // one SM clock ~ 56 cost units (calibrated on config 2); a team advances one column in about
         // 36 clocks per row held by a lane, 1.6 x that when the wavefront crosses warps
         const int teams_now = (gwarps == 1) ? 16 : std::max(1, 16 / gwarps);
-        gpol.col_cost = 56.0 * 36.0 * gK * (gwarps > 1 ? 1.6 : 1.0) / teams_now;
+        static const double gmul = getenv("PYOPAL_CUDA_GMUL") ? atof(getenv("PYOPAL_CUDA_GMUL")) : 1.0;
+        gpol.col_cost = gmul * 56.0 * 36.0 * gK * (gwarps > 1 ? 1.6 : 1.0) / teams_now;
     }
     const bool old_giants_ok = gpol.ok;
     // transposed giants (tgiant.cu): the target over the lanes, the query streamed; needs the short F chain
