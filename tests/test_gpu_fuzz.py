@@ -179,3 +179,44 @@ def test_static_16bit_bound_edge(cuda, oracle, algo, gaps):
         got = list(aligner.align_scores(aligner.alphabet.decode(q), make_db(seqs, aligner.alphabet), algorithm=algo))
         want = oracle.search(q, seqs, aligner._int_matrix, 24, go, ge, algo, "score", threads=8)["score"]
         assert got == want, (algo, gaps, lq, [(i, a, b, lens[i]) for i, (a, b) in enumerate(zip(got, want)) if a != b][:5])
+
+
+@pytest.mark.parametrize("algo", ALGOS)
+@pytest.mark.parametrize("mode", ("score", "end", "full"))
+def test_degenerate_inputs(cuda, oracle, algo, mode):
+    # empty query, empty / one-residue targets, a database of only empty targets: closed forms on the host side
+    # of the library (api.cu degenerate_score, pairdp.cu) against the oracle's m == 0 || n == 0 branches
+    aligner = pyopal.Aligner("BLOSUM62", 11, 1)
+    rng = np.random.Generator(np.random.PCG64(123))
+    some = [b"", b"\x03", b"", rng.integers(0, 20, 40, dtype=np.uint8).tobytes(), b"\x00\x00", b""]
+    for seqs in (some, [b"", b""], [b"\x05"]):
+        for query in (b"", b"\x07", rng.integers(0, 20, 33, dtype=np.uint8).tobytes()):
+            if mode == "score":
+                got = list(aligner.align_scores(aligner.alphabet.decode(query), make_db(seqs, aligner.alphabet), algorithm=algo))
+                want = oracle.search(query, seqs, aligner._int_matrix, 24, 11, 1, algo, "score", threads=2)["score"]
+                assert got == want, (algo, len(query), [len(s) for s in seqs])
+            else:
+                check_mode(oracle, aligner, query, seqs, algo, mode)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_fuzz_end_full_long(cuda, oracle, seed):
+    # end / full on longer pairs: several passes of the pair kernel (more than 32 x K query rows), long gaps,
+    # direction matrices of a few MB per pair
+    rng = np.random.Generator(np.random.PCG64(7000 + seed))
+    aligner = pyopal.Aligner(*[("BLOSUM62", 11, 1), ("BLOSUM50", 3, 1), ("BLOSUM62", 5, 5)][seed % 3])
+    lq = int(rng.choice([900, 1700, 2600]))
+    query = rng.integers(0, 20, lq, dtype=np.uint8)
+    seqs = []
+    for _ in range(6):
+        n = int(rng.integers(300, 2400))
+        t = rng.integers(0, 20, n, dtype=np.uint8)
+        if rng.random() < 0.7:  # a homologous stretch with an indel
+            a = int(rng.integers(0, lq // 2))
+            piece = np.delete(query[a: a + lq // 3], slice(40, 40 + int(rng.integers(1, 30))))
+            b = int(rng.integers(0, max(1, n - len(piece))))
+            t = np.concatenate([t[:b], piece, t[b:]])
+        seqs.append(t.tobytes())
+    for algo in ALGOS:
+        for mode in ("end", "full"):
+            check_mode(oracle, aligner, query.tobytes(), seqs, algo, mode)
