@@ -86,7 +86,7 @@ void pyopal_cuda_db_destroy(pyopal_cuda_db* db) {
     db->wl16.release(); db->wl32.release(); db->ovf.release(); db->out.release(); db->fixes.release();
     db->query.release(); db->gprofile.release(); db->wprofile.release();
     db->bndH.release(); db->bndF.release(); db->bnd32H.release(); db->bnd32F.release();
-    db->pd_i32.release(); db->pd_tb.release(); db->pd_ops.release(); db->pd_bnd.release(); db->pd_jobs.release();
+    db->pd_i32.release(); db->pd_tb.release(); db->pd_ops.release(); db->pd_bnd.release(); db->pd_jobs.release(); db->pd_team.release();
     db->tk_ws.release(); db->tk_vals.release(); db->tk_idx.release();
     if (db->ev_fork) cudaEventDestroy(db->ev_fork);
     if (db->ev_join) cudaEventDestroy(db->ev_join);

@@ -15,10 +15,12 @@
 //             byte per cell, then one thread per target walks it backwards
 //             and emits the operations (M=0 D=1 I=2 X=3, lib.pyx:991-996).
 //
-// A warp holds 32*K consecutive query rows (K per lane) in registers and the
-// target streams through it as an anti-diagonal wavefront (two shuffles per
-// step); longer queries take several passes whose last row round-trips
-// through global memory.  Tie-breaks are those of oracle/opal_oracle.c.
+// A warp holds 32*K consecutive query rows (K per lane, K = 4 .. 32 picked from
+// the query length) in registers and the target streams through it as an
+// anti-diagonal wavefront (two shuffles per step for the carried row, one for
+// the prefetched residue); longer queries take several passes whose last row
+// round-trips through global memory.  Tie-breaks are those of
+// oracle/opal_oracle.c.
 #include "store.h"
 
 #include <algorithm>
@@ -59,7 +61,16 @@ struct PairParams {
     int32_t* bndF;
     uint8_t* tb;
     int32_t* err;
+    // bands: a job whose query needs `maxpass` > 1 passes is walked by that many warps at once, pass p one chunk of
+    // columns behind pass p - 1 (task = job * maxpass + pass)
+    int maxpass;
+    int32_t* prog;   // [task]  columns of this band whose last row is in bndH / bndF
+    int32_t* done;   // [job]   bands finished
+    int32_t* cut;    // [job]   reverse pass: columns still worth walking (INT_MAX until `expect` is met)
+    int32_t* slots;  // [task][5] per-band candidates, merged by the band that finishes last
 };
+
+__device__ __forceinline__ int ld_volatile(const int32_t* p) { return *reinterpret_cast<const volatile int32_t*>(p); }
 
 __device__ __forceinline__ int border_val(int is_free, int k, int go, int ge) {
     if (k < 0) return 0;
@@ -71,181 +82,327 @@ __device__ __forceinline__ bool better(int v, int c, int i, int bv, int bc, int 
     return v > bv || (v == bv && (c < bc || (c == bc && i < bi)));
 }
 
-// KIND 0: locate (forward / reverse); KIND 1: fill the direction matrix.
+// KIND_ALL: locate, every cell is a candidate (SW, forward and reverse); KIND_EDGE: locate on the last row / last
+// column / corner (NW, HW, OV, forward and reverse); KIND_FILL: fill the direction matrix.
+enum : int { KIND_ALL = 0, KIND_FILL = 1, KIND_EDGE = 2 };
+
+// One warp per job.  Values are kept as G = H - open (the "gap already opened" form of kernels.cuh), the score table
+// holds S + open, and the vertical gap is carried as f[r+1] = max(f[r] - min(open, ext), max(diag, e)[r] - open):
+// identical to F[r+1] = max(F[r] - ext, H[r] - open) with H[r] = max(diag, e, F[r]), but only ONE dependent
+// operation per row stays on the lane's serial chain - a long target is walked by a single warp, so the chain and
+// the instruction count per row are what bound it.  SW's "first maximum" is found from a per-column maximum (half
+// an instruction per row); the row is looked up only in the rare step that improves the lane's maximum.  Target
+// residues and pass-boundary rows are fetched 32 columns at a time, one chunk ahead, and handed to the lane that
+// needs them by shuffle, so no global load sits on the chain.
 template <int K, int KIND>
 __global__ void __launch_bounds__(128) pair_kernel(const __grid_constant__ PairParams P) {
     static_assert(K % 4 == 0, "K must be a multiple of 4");
-    __shared__ int sS[32 * 32];
-    for (int x = threadIdx.x; x < P.A * P.A; x += blockDim.x) sS[x] = P.matrix[x];
+    __shared__ int sS[33 * 32];
+    __shared__ int2 sbnd[128];  // per warp: the 32 boundary columns of the current chunk
+    const int go = P.go, ge = P.ge;
+    const int gmin = min(go, ge);
+    for (int x = threadIdx.x; x < P.A * P.A; x += blockDim.x) sS[x] = P.matrix[x] + go;
+    for (int x = threadIdx.x; x < P.A; x += blockDim.x) sS[P.A * P.A + x] = NEGV;  // row of the padding rows
     __syncthreads();
 
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
-    const int go = P.go, ge = P.ge;
     constexpr int T = 32 * K;
+    const int floorv = P.floor0 ? 0 : 2 * NEGV;
 
     for (;;) {
         int task = 0;
         if (lane == 0) task = atomicAdd(P.counter, 1);
         task = __shfl_sync(FULL, task, 0);
-        if (task >= P.njobs) break;
-        const PairJob jb = P.jobs[task];
+        if (task >= P.njobs * P.maxpass) break;
+        const int job = task / P.maxpass, pass = task - job * P.maxpass;
+        const PairJob jb = P.jobs[job];
         const int m = jb.m, n = jb.n;
         if (m <= 0 || n <= 0) continue;
-        const uint8_t* tbytes = reinterpret_cast<const uint8_t*>(P.stream + jb.tbase) + jb.half;
-        const int64_t bbase = 2 * jb.tbase + jb.half;
         const int npass = (m + T - 1) / T;
+        if (pass >= npass) continue;
+        const uint8_t* tbytes = reinterpret_cast<const uint8_t*>(P.stream + jb.tbase) + jb.half;
+        int32_t* bH = P.bndH + 2 * jb.tbase + jb.half;
+        int32_t* bF = P.bndF + 2 * jb.tbase + jb.half;
         const int rr = (m - 1) - (npass - 1) * T;  // tile row of the last query row in the last pass
         const int owner = rr / K, rl = rr % K;
+        const bool multi = npass > 1;
+        const bool cutting = (KIND == KIND_ALL) && P.anchored;
+        const int32_t* prog_prev = P.prog + task - 1;  // read when pass > 0 only
+        int32_t* prog_mine = P.prog + task;
+        int32_t* cutp = P.cut + job;
 
         // trackers
-        int gv = P.floor0 ? 0 : INT_MIN, gc = -1, gi = -1;              // END_ALL
+        int gv = P.floor0 ? 0 : INT_MIN, gc = -1, gi = -1;              // KIND_ALL
         int lv = INT_MIN, lc = -1;                                         // last row
         int cv = INT_MIN, ci = -1;                                         // last column
         if (P.anchored) lv = border_val(0, m - 1, go, ge);
         int ncols = n;  // may shrink once the reverse pass has met `expect`
         int corner = 0;
 
-        for (int pass = 0; pass < npass; ++pass) {
+        {
             const int i0 = pass * T + lane * K;
             const int nv = min(max(m - i0, 0), K);
-            int qa[K], Hl[K], El[K];
+            int qa[K], Gl[K], El[K];
 #pragma unroll
             for (int r = 0; r < K; ++r) {
                 const int i = i0 + r;
-                qa[r] = (r < nv) ? (int)P.query[jb.q0 + jb.qdir * i] * P.A : 0;
-                Hl[r] = border_val(P.left_free, i, go, ge);
+                qa[r] = 4 * ((r < nv) ? (int)P.query[jb.q0 + jb.qdir * i] * P.A : P.A * P.A);  // byte offset of the row in sS
+                Gl[r] = border_val(P.left_free, i, go, ge) - go;
                 El[r] = NEGV;
             }
-            int Hd0 = border_val(P.left_free, i0 - 1, go, ge);
-            int Hout = 0, Fout = NEGV;
-            int pv = INT_MIN, pc = -1, pi = -1;
+            int Gd0 = border_val(P.left_free, i0 - 1, go, ge) - go;
+            int Gout = 0, Fout = NEGV;
+            // best G of this lane in this band (KIND_ALL); a local score of 0 is "no alignment", never a candidate
+            int pvg = P.floor0 ? -go : 4 * NEGV, pc = -1, pi = -1;
             const bool last = (pass == npass - 1);
             const bool own = last && (lane == owner);
             int nsteps = ncols + 31;
             uint32_t tbw[K / 4];
 
-            for (int s = 0; s < nsteps; ++s) {
-                int upH = __shfl_up_sync(FULL, Hout, 1);
-                int upF = __shfl_up_sync(FULL, Fout, 1);
-                const int c = s - lane;
-                const bool active = (c >= 0) && (c < ncols) && (nv > 0);
-                bool hit = false;
-                if (active) {
-                    if (lane == 0) {
-                        if (pass == 0) {
-                            upH = border_val(P.top_free, c, go, ge);
-                            upF = NEGV;
-                        } else {
-                            upH = __ldcg(P.bndH + bbase + 2 * (int64_t)c);
-                            upF = __ldcg(P.bndF + bbase + 2 * (int64_t)c);
-                        }
+            // chunked prefetch: chunk k = columns [32k, 32k + 32), this lane holds column 32k + lane
+            auto load_res = [&](int col) -> int {
+                return (col < n) ? (int)tbytes[2 * (int64_t)(jb.t0 + jb.tdir * col)] : 0;
+            };
+            // boundary chunk of the band above: wait until it has published those columns, or the job was cut short
+            // (then the columns past the cut are never walked)
+            auto load_bnd = [&](int first, int& h, int& f) {
+                int need = min(first + 32, ncols);
+                while (ld_volatile(prog_prev) < need) {
+                    if (cutting) {
+                        const int cc = ld_volatile(cutp);
+                        if (cc < ncols) { ncols = cc; nsteps = min(nsteps, ncols + 31); need = min(need, ncols); }
                     }
-                    const int tl = tbytes[2 * (int64_t)(jb.t0 + jb.tdir * c)];
-                    int hd = Hd0, hu = upH, f = upF, hlast = 0;
-#pragma unroll
-                    for (int r = 0; r < K; ++r) {
-                        const int sc = sS[qa[r] + tl];
-                        const int ho = Hl[r] - go;
-                        const int e = max(El[r] - ge, ho);
-                        const int fo = hu - go;
-                        f = max(f - ge, fo);
-                        const int d = hd + sc;
-                        int h = max(d, max(e, f));
-                        if (KIND == 0) {
-                            if (P.floor0) h = max(h, 0);
-                            if (P.endrule == END_ALL) {
-                                if (r < nv && h > pv) { pv = h; pc = c; pi = i0 + r; }
-                            } else {
-                                if (r == rl) hlast = h;
-                                if (P.endrule == END_LASTROW_LASTCOL && c == n - 1 && r < nv && h > cv) {
-                                    cv = h; ci = i0 + r;
-                                }
-                            }
-                        } else {
-                            const uint32_t src = (h == d) ? 0u : (h == e) ? 1u : 2u;
-                            const uint32_t b = src | ((e == ho) ? 4u : 0u) | ((f == fo) ? 8u : 0u);
-                            if ((r & 3) == 0) tbw[r >> 2] = b;
-                            else tbw[r >> 2] |= b << (8 * (r & 3));
-                            if (r == rl) hlast = h;
-                        }
-                        hd = Hl[r];
-                        Hl[r] = h;
-                        El[r] = e;
-                        hu = h;
+                    __nanosleep(40);
+                }
+                __threadfence();
+                const int col = first + lane;
+                if (col < need) { h = __ldcg(bH + 2 * (int64_t)col); f = __ldcg(bF + 2 * (int64_t)col); }
+            };
+            int rc_prev = 0, rc_cur = load_res(lane), rc_next = load_res(32 + lane);
+            int bh_cur = 0, bf_cur = 0, bh_next = 0, bf_next = 0;
+            if (pass > 0) {
+                load_bnd(0, bh_cur, bf_cur);
+                if (32 < ncols) load_bnd(32, bh_next, bf_next);
+            }
+
+            int thr = pvg;  // KIND_ALL: best G any lane of the warp holds (candidates below it cannot win)
+            for (int s0 = 0; s0 < nsteps; s0 += 32) {
+                if (s0 > 0) {
+                    // ---- chunk boundary (every 32 steps): everything that touches global memory lives here ----
+                    if (cutting && multi) {  // another band may have met `expect`
+                        const int cc = ld_volatile(cutp);
+                        if (cc < ncols) { ncols = cc; nsteps = min(nsteps, ncols + 31); if (s0 >= nsteps) break; }
                     }
-                    Hout = hu;
-                    Fout = f;
-                    Hd0 = upH;
-                    if (lane == 31 && !last) {
-                        __stcg(P.bndH + bbase + 2 * (int64_t)c, Hout);
-                        __stcg(P.bndF + bbase + 2 * (int64_t)c, Fout);
+                    rc_prev = rc_cur; rc_cur = rc_next; rc_next = load_res(s0 + 32 + lane);
+                    if (pass > 0) {
+                        bh_cur = bh_next; bf_cur = bf_next;
+                        if (s0 + 32 < ncols) load_bnd(s0 + 32, bh_next, bf_next);
                     }
-                    if (KIND == 0) {
-                        if (P.endrule == END_ALL) {
-                            hit = P.anchored && (pv == jb.expect);
-                        } else if (own) {
-                            if (P.endrule == END_CORNER) {
-                                if (c == n - 1) { lv = hlast; lc = c; }
-                            } else if (hlast > lv) {
-                                lv = hlast; lc = c;
-                            }
-                        }
-                    } else {
-                        uint32_t* col = reinterpret_cast<uint32_t*>(P.tb + jb.tb_off + (int64_t)c * ((m + 3) & ~3) + i0);
-#pragma unroll
-                        for (int w = 0; w < K / 4; ++w)
-                            if (4 * w < nv) col[w] = tbw[w];
-                        if (own && c == n - 1) corner = hlast;
+                    if (multi && !last && lane == 31 && s0 > 31) {  // lane 31 is done with the columns below s0 - 31
+                        __threadfence();
+                        *reinterpret_cast<volatile int32_t*>(prog_mine) = min(s0 - 31, ncols);
                     }
                 }
-                if (KIND == 0 && P.endrule == END_ALL && P.anchored) {
-                    // reverse pass: stop once every lane is past the first column that reached `expect`
-                    if (__any_sync(FULL, hit)) {
-                        int cm = hit ? pc : INT_MAX;
-                        for (int d = 16; d > 0; d >>= 1) cm = min(cm, __shfl_xor_sync(FULL, cm, d));
-                        if (cm + 1 < ncols) ncols = cm + 1;
-                        nsteps = min(nsteps, ncols + 31);
+                if (pass > 0) {  // lane 0 reads the boundary row of the band above from shared memory, one column a step
+                    __syncwarp();
+                    sbnd[threadIdx.x] = make_int2(bh_cur, bf_cur);
+                    __syncwarp();
+                }
+                int lim = min(s0 + 32, nsteps);
+                for (int s = s0; s < lim; ++s) {
+                    const int sl = s - s0;
+                    int upG = __shfl_up_sync(FULL, Gout, 1);
+                    int upF = __shfl_up_sync(FULL, Fout, 1);
+                    const int tl = __shfl_sync(FULL, (lane <= sl) ? rc_cur : rc_prev, (sl - lane) & 31);
+                    const int c = s - lane;
+                    const bool active = (c >= 0) && (c < ncols) && (nv > 0);
+                    int cm = 4 * NEGV;
+                    if (active) {
+                        if (lane == 0) {
+                            if (pass == 0) {
+                                upG = border_val(P.top_free, c, go, ge) - go;
+                                upF = upG;  // F of the first row: max(-inf, H above - open)
+                            } else {
+                                const int2 bb = sbnd[(threadIdx.x & ~31) + sl];
+                                upG = bb.x;
+                                upF = bb.y;
+                            }
+                        }
+                        int gd = Gd0, gu = upG, f = upF, glast = 0;
+                        const char* const srow = reinterpret_cast<const char*>(sS) + 4 * tl;
+#pragma unroll
+                        for (int r = 0; r < K; ++r) {
+                            const int sc = *reinterpret_cast<const int*>(srow + qa[r]);
+                            const int gl = Gl[r];
+                            const int e = max(El[r] - ge, gl);
+                            const int d = max(gd + sc, floorv);
+                            const int de = max(d, e);
+                            const int deg = de - go;
+                            const int g = max(f - go, deg);  // = max(d, e, F) - open
+                            if (KIND == KIND_ALL) {
+                                cm = max(cm, g);
+                            } else if (KIND == KIND_EDGE) {
+                                if (r == rl) glast = g;
+                            } else {
+                                const int h = max(de, f);
+                                const uint32_t src = (h == d) ? 0u : (h == e) ? 1u : 2u;
+                                const uint32_t b = src | ((e == gl) ? 4u : 0u) | ((f == gu) ? 8u : 0u);
+                                if ((r & 3) == 0) tbw[r >> 2] = b;
+                                else tbw[r >> 2] |= b << (8 * (r & 3));
+                                if (r == rl) glast = g;
+                            }
+                            f = max(f - gmin, deg);
+                            gd = gl;
+                            Gl[r] = g;
+                            El[r] = e;
+                            gu = g;
+                        }
+                        const int hlast = glast + go;
+                        Gout = gu;
+                        Fout = f;
+                        Gd0 = upG;
+                        if (lane == 31 && !last) {
+                            __stcg(bH + 2 * (int64_t)c, Gout);
+                            __stcg(bF + 2 * (int64_t)c, Fout);
+                        }
+                        if (KIND == KIND_EDGE) {
+                            if (own) {
+                                if (P.endrule == END_CORNER) {
+                                    if (c == n - 1) { lv = hlast; lc = c; }
+                                } else if (hlast > lv) {
+                                    lv = hlast; lc = c;
+                                }
+                            }
+                            if (P.endrule == END_LASTROW_LASTCOL && c == n - 1) {
+#pragma unroll
+                                for (int r = 0; r < K; ++r)
+                                    if (r < nv && Gl[r] + go > cv) { cv = Gl[r] + go; ci = i0 + r; }
+                            }
+                        } else if (KIND == KIND_FILL) {
+                            uint32_t* col = reinterpret_cast<uint32_t*>(P.tb + jb.tb_off + (int64_t)c * ((m + 3) & ~3) + i0);
+#pragma unroll
+                            for (int w = 0; w < K / 4; ++w)
+                                if (4 * w < nv) col[w] = tbw[w];
+                            if (own && c == n - 1) corner = hlast;
+                        }
+                    }
+                    if (KIND == KIND_ALL) {
+                        // rare (a warp-uniform branch): some lane's column beats both its own best and the warp's
+                        const bool cand = (cm > pvg) && (cm >= thr);
+                        if (__any_sync(FULL, cand)) {
+                            if (cand) {
+                                int rf = -1;  // the first (lowest) real row of the column that holds the maximum
+#pragma unroll
+                                for (int r = K - 1; r >= 0; --r)
+                                    if (r < nv && Gl[r] == cm) rf = r;
+                                if (rf >= 0) { pvg = cm; pc = c; pi = i0 + rf; }
+                            }
+                            int w = pvg;
+                            for (int d = 16; d > 0; d >>= 1) w = max(w, __shfl_xor_sync(FULL, w, d));
+                            thr = w;
+                            if (cutting) {
+                                // reverse pass: stop once every lane is past the first column that reached `expect`
+                                const bool hit = (pc >= 0) && (pvg + go == jb.expect);
+                                if (__any_sync(FULL, hit)) {
+                                    int cmn = hit ? pc : INT_MAX;
+                                    for (int d = 16; d > 0; d >>= 1) cmn = min(cmn, __shfl_xor_sync(FULL, cmn, d));
+                                    if (cmn + 1 < ncols) {
+                                        ncols = cmn + 1;
+                                        if (multi && lane == 0) atomicMin(cutp, ncols);
+                                    }
+                                    nsteps = min(nsteps, ncols + 31);
+                                    lim = min(lim, nsteps);
+                                }
+                            }
+                        }
                     }
                 }
             }
-            if (KIND == 0 && P.endrule == END_ALL && better(pv, pc, pi, gv, gc, gi)) { gv = pv; gc = pc; gi = pi; }
+            if (multi && !last) {
+                // every column below the (possibly cut) width is in place
+                __syncwarp();
+                if (lane == 31) {
+                    __threadfence();
+                    *reinterpret_cast<volatile int32_t*>(prog_mine) = ncols;
+                }
+            }
+            if (KIND == KIND_ALL && pc >= 0 && better(pvg + go, pc, pi, gv, gc, gi)) { gv = pvg + go; gc = pc; gi = pi; }
             __syncwarp();
         }
 
-        if (KIND == 0) {
-            int score, rq, rt;
-            if (P.endrule == END_ALL) {
-                for (int d = 16; d > 0; d >>= 1) {
-                    const int ov = __shfl_xor_sync(FULL, gv, d), oc = __shfl_xor_sync(FULL, gc, d),
-                              oi = __shfl_xor_sync(FULL, gi, d);
-                    if (better(ov, oc, oi, gv, gc, gi)) { gv = ov; gc = oc; gi = oi; }
+        if (KIND == KIND_FILL) {
+            if (pass == npass - 1) {
+                corner = __shfl_sync(FULL, corner, owner);
+                if (lane == 0 && corner != jb.expect) atomicExch(P.err, 1 + jb.slot);
+            }
+            continue;
+        }
+
+        // this band's candidates: best cell (KIND_ALL), last-row best (owner lane of the last band), last-column best
+        if (KIND == KIND_ALL) {
+            for (int d = 16; d > 0; d >>= 1) {
+                const int ov = __shfl_xor_sync(FULL, gv, d), oc = __shfl_xor_sync(FULL, gc, d),
+                          oi = __shfl_xor_sync(FULL, gi, d);
+                if (better(ov, oc, oi, gv, gc, gi)) { gv = ov; gc = oc; gi = oi; }
+            }
+        } else {
+            lv = __shfl_sync(FULL, lv, owner);
+            lc = __shfl_sync(FULL, lc, owner);
+            for (int d = 16; d > 0; d >>= 1) {
+                const int ov = __shfl_xor_sync(FULL, cv, d), oi = __shfl_xor_sync(FULL, ci, d);
+                if (ov > cv || (ov == cv && oi < ci)) { cv = ov; ci = oi; }
+            }
+        }
+        if (multi) {
+            // hand the candidates to the band that finishes last
+            int lastone = 0;
+            if (lane == 0) {
+                int32_t* sl5 = P.slots + 5 * (int64_t)task;
+                if (KIND == KIND_ALL) { sl5[0] = gv; sl5[1] = gc; sl5[2] = gi; }
+                else { sl5[0] = cv; sl5[1] = ci; sl5[3] = lv; sl5[4] = lc; }
+                __threadfence();
+                lastone = (atomicAdd(P.done + job, 1) == npass - 1);
+                if (lastone) __threadfence();
+            }
+            lastone = __shfl_sync(FULL, lastone, 0);
+            if (!lastone) continue;
+            if (lane == 0) {
+                const int32_t* base = P.slots + 5 * (int64_t)job * P.maxpass;
+                if (KIND == KIND_ALL) {
+                    gv = P.floor0 ? 0 : INT_MIN; gc = -1; gi = -1;
+                    for (int p = 0; p < npass; ++p) {
+                        const int ov = __ldcg(base + 5 * p), oc = __ldcg(base + 5 * p + 1), oi = __ldcg(base + 5 * p + 2);
+                        if (better(ov, oc, oi, gv, gc, gi)) { gv = ov; gc = oc; gi = oi; }
+                    }
+                } else {
+                    cv = INT_MIN; ci = -1;
+                    for (int p = 0; p < npass; ++p) {  // bands hold ascending rows: strict > keeps the lowest row
+                        const int ov = __ldcg(base + 5 * p), oi = __ldcg(base + 5 * p + 1);
+                        if (ov > cv) { cv = ov; ci = oi; }
+                    }
+                    lv = __ldcg(base + 5 * (npass - 1) + 3);
+                    lc = __ldcg(base + 5 * (npass - 1) + 4);
                 }
+            }
+        }
+        if (lane == 0) {
+            int score, rq, rt;
+            if (KIND == KIND_ALL) {
                 score = gv; rq = gi; rt = gc;
             } else {
-                lv = __shfl_sync(FULL, lv, owner);
-                lc = __shfl_sync(FULL, lc, owner);
                 score = lv; rq = m - 1; rt = lc;
                 if (P.endrule == END_LASTROW_LASTCOL) {
                     if (P.anchored) {
                         const int tbv = border_val(0, n - 1, go, ge);
                         if (tbv > score) { score = tbv; rq = -1; rt = n - 1; }
                     }
-                    for (int d = 16; d > 0; d >>= 1) {
-                        const int ov = __shfl_xor_sync(FULL, cv, d), oi = __shfl_xor_sync(FULL, ci, d);
-                        if (ov > cv || (ov == cv && oi < ci)) { cv = ov; ci = oi; }
-                    }
                     if (cv > score) { score = cv; rq = ci; rt = n - 1; }
                 }
             }
-            if (lane == 0) {
-                P.out_score[jb.slot] = score;
-                P.out_q[jb.slot] = rq;
-                P.out_t[jb.slot] = rt;
-            }
-        } else {
-            corner = __shfl_sync(FULL, corner, owner);
-            if (lane == 0 && corner != jb.expect) atomicExch(P.err, 1 + jb.slot);
+            P.out_score[jb.slot] = score;
+            P.out_q[jb.slot] = rq;
+            P.out_t[jb.slot] = rt;
         }
     }
 }
@@ -338,22 +495,67 @@ __global__ void fill_i32(int32_t* p, int64_t n, int32_t v) {
 
 typedef void (*pair_kernel_t)(const PairParams);
 
-template <int KIND>
-pair_kernel_t pick_pair_kernel(int rows, int* K) {
-    if (rows <= 128) { *K = 4; return pair_kernel<4, KIND>; }
-    if (rows <= 256) { *K = 8; return pair_kernel<8, KIND>; }
-    if (rows <= 512) { *K = 16; return pair_kernel<16, KIND>; }
-    *K = 32;
-    return pair_kernel<32, KIND>;
+// Rows per lane.  One pass (K = rows / 32, rounded up to 4) does the least work, and is right when there are targets
+// enough to fill the machine.  With few targets the longest one is the critical path - a single warp walking it
+// column by column - so the query is cut into bands of 32 K rows walked by several warps at once, and the smallest
+// K that the rest of the work allows is best.  Both sides of that trade are modelled in clocks, with constants
+// measured on B200 (scratch/pairk_probe.py): a lone warp takes about 470 + 13 K clocks per column (its ~8.6 K + 60
+// instructions are latency-exposed), a band starts ~96 columns behind the one above it, and a full SM sustains
+// ~2.2 of those instructions per clock.
+int choose_pair_K(int rows, int64_t njobs, int64_t sum_n, int64_t nmax, int64_t table_jobs, int sm_count) {
+    const int kfit = std::min(32, std::max(4, 4 * ((rows + 127) / 128)));
+    const char* env = getenv("PYOPAL_CUDA_PAIR_K");
+    if (env && atoi(env) >= 4) return std::min(32, atoi(env) / 4 * 4);
+    double best = 1e300;
+    int bk = kfit;
+    for (int k = 4; k <= kfit; k += 4) {
+        const int64_t bands = (rows + 32 * k - 1) / (32 * k);
+        if (k < kfit && table_jobs * bands > ((int64_t)1 << 25)) continue;  // band bookkeeping: 24 B per task
+        const double step = 8.6 * k + 60.0;
+        const double crit = ((double)nmax + 96.0 * (double)(bands - 1)) * (470.0 + 13.0 * k);
+        const double thr = (double)bands * ((double)sum_n + 31.0 * (double)njobs) * step / (2.2 * sm_count);
+        const double c = std::max(crit, thr);
+        if (c < best * 0.97) { best = c; bk = k; }
+    }
+    return bk;
 }
 
-int launch_pair(pyopal_cuda_db* db, pair_kernel_t fn, const PairParams& P, cudaStream_t st) {
+template <int KIND>
+pair_kernel_t pair_kernel_for(int k) {
+    switch (k) {
+        case 4: return pair_kernel<4, KIND>;
+        case 8: return pair_kernel<8, KIND>;
+        case 12: return pair_kernel<12, KIND>;
+        case 16: return pair_kernel<16, KIND>;
+        case 20: return pair_kernel<20, KIND>;
+        case 24: return pair_kernel<24, KIND>;
+        case 28: return pair_kernel<28, KIND>;
+        default: return pair_kernel<32, KIND>;
+    }
+}
+
+// Reset the band bookkeeping for `P.njobs` jobs of at most `rows` query rows and launch.
+int launch_pair(pyopal_cuda_db* db, pair_kernel_t fn, PairParams P, int rows, int K, cudaStream_t st) {
     if (P.njobs <= 0) return 0;
+    P.maxpass = std::max(1, (rows + 32 * K - 1) / (32 * K));
+    const int64_t ntasks = (int64_t)P.njobs * P.maxpass;
+    if (ntasks >= ((int64_t)1 << 31) - 1024) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "too many target x band tasks");
+    P.prog = P.done = P.cut = P.slots = nullptr;
+    if (P.maxpass > 1) {
+        if (db->pd_team.reserve((size_t)(6 * ntasks + 2 * (int64_t)P.njobs + 16))) return PYOPAL_CUDA_ERR_NOMEM;
+        P.prog = db->pd_team.p;
+        P.done = P.prog + ntasks;
+        P.cut = P.done + P.njobs;
+        P.slots = P.cut + P.njobs;
+        CU(cudaMemsetAsync(P.prog, 0, (size_t)(ntasks + P.njobs) * sizeof(int32_t), st));
+        fill_i32<<<256, 256, 0, st>>>(P.cut, P.njobs, INT_MAX);
+    }
     CU(cudaMemsetAsync(P.counter, 0, sizeof(int32_t), st));
     int per_sm = 0;
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 128, 0));
     if (per_sm < 1) return fail(PYOPAL_CUDA_ERR_INTERNAL, "pair kernel does not fit on an SM");
-    int64_t grid = std::min<int64_t>((int64_t)db->sm_count * per_sm, ((int64_t)P.njobs + 3) / 4);
+    // every block is resident (a band may wait for the band above it, which was claimed earlier)
+    int64_t grid = std::min<int64_t>((int64_t)db->sm_count * per_sm, (ntasks + 3) / 4);
     fn<<<(unsigned)std::max<int64_t>(grid, 1), 128, 0, st>>>(P);
     CU(cudaGetLastError());
     db->stats[0]++;
@@ -425,8 +627,15 @@ int pyopal_end_full_search(pyopal_cuda_db* db, const unsigned char* query, int L
         if (db->query.reserve((size_t)Lq)) return PYOPAL_CUDA_ERR_NOMEM;
         d_res = db->pd_i32.p;
         d_jobs = reinterpret_cast<PairJob*>(db->pd_jobs.p);
-        int K = 4;
-        pair_kernel_t kloc = pick_pair_kernel<0>(Lq, &K);
+        int64_t sum_n = 0, nmax = 0, nlive = 0;
+        for (int64_t k = 0; k < nout; k++) {
+            const int64_t len = db->h_lengths[(size_t)(start + k)];
+            sum_n += len; nmax = std::max(nmax, len); nlive += (len > 0);
+        }
+        const int K = choose_pair_K(Lq, nlive, sum_n, nmax, njobs, db->sm_count);
+        pair_kernel_t kloc = (cfg_for_mode(mode).endrule == END_ALL) ? pair_kernel_for<KIND_ALL>(K) : pair_kernel_for<KIND_EDGE>(K);
+        db->stats[6] = K;
+        db->stats[7] = (Lq + 32 * K - 1) / (32 * K);
         if (Lq > 32 * K) {
             if (db->bnd32H.reserve((size_t)db->ncols * 2 + 16) || db->bnd32F.reserve((size_t)db->ncols * 2 + 16))
                 return PYOPAL_CUDA_ERR_NOMEM;
@@ -447,7 +656,7 @@ int pyopal_end_full_search(pyopal_cuda_db* db, const unsigned char* query, int L
         const ModeCfg c = cfg_for_mode(mode);
         P.top_free = c.top_free; P.left_free = c.left_free; P.floor0 = c.floor0; P.endrule = c.endrule; P.anchored = 0;
         P.out_score = d_res; P.out_q = d_res + nout; P.out_t = d_res + 2 * nout;
-        int rc = launch_pair(db, kloc, P, st);
+        int rc = launch_pair(db, kloc, P, Lq, K, st);
         if (rc) return rc;
         if (full && mode != MODE_NW) {
             make_reverse_jobs<<<(njobs + tpb - 1) / tpb, tpb, 0, st>>>(d_jobs, njobs, d_res, d_res + nout, d_res + 2 * nout);
@@ -455,7 +664,7 @@ int pyopal_end_full_search(pyopal_cuda_db* db, const unsigned char* query, int L
             PairParams R = P;
             R.top_free = 0; R.left_free = 0; R.floor0 = 0; R.anchored = 1;
             R.out_score = d_res + 3 * nout; R.out_q = d_res + 4 * nout; R.out_t = d_res + 5 * nout;
-            rc = launch_pair(db, kloc, R, st);
+            rc = launch_pair(db, kloc, R, Lq, K, st);
             if (rc) return rc;
         }
         CU(cudaMemcpyAsync(h_sc.data(), d_res, (size_t)nout * 4, cudaMemcpyDeviceToHost, st));
@@ -536,7 +745,7 @@ int pyopal_end_full_search(pyopal_cuda_db* db, const unsigned char* query, int L
     std::vector<unsigned char> hops;
     while (pos < todo.size()) {
         hjobs.clear();
-        int64_t tb_bytes = 0, ops_bytes = 0;
+        int64_t tb_bytes = 0, ops_bytes = 0, sum_tn = 0, max_tn = 0;
         int maxm = 0;
         size_t p2 = pos;
         while (p2 < todo.size()) {
@@ -560,6 +769,8 @@ int pyopal_end_full_search(pyopal_cuda_db* db, const unsigned char* query, int L
             hjobs.push_back(jb);
             tb_bytes += need;
             maxm = std::max(maxm, t.m);
+            sum_tn += t.n;
+            max_tn = std::max<int64_t>(max_tn, t.n);
             p2++;
         }
         const int nb = (int)hjobs.size();
@@ -569,8 +780,8 @@ int pyopal_end_full_search(pyopal_cuda_db* db, const unsigned char* query, int L
         d_jobs = reinterpret_cast<PairJob*>(db->pd_jobs.p);
         int32_t* d_len = db->pd_i32.p;
         int32_t* d_ctl = d_len + nb;
-        int K = 4;
-        pair_kernel_t kfill = pick_pair_kernel<1>(maxm, &K);
+        const int K = choose_pair_K(maxm, nb, sum_tn, max_tn, nb, db->sm_count);
+        pair_kernel_t kfill = pair_kernel_for<KIND_FILL>(K);
         if (maxm > 32 * K)
             if (db->bnd32H.reserve((size_t)db->ncols * 2 + 16) || db->bnd32F.reserve((size_t)db->ncols * 2 + 16))
                 return PYOPAL_CUDA_ERR_NOMEM;
@@ -583,7 +794,7 @@ int pyopal_end_full_search(pyopal_cuda_db* db, const unsigned char* query, int L
         F.bndH = reinterpret_cast<int32_t*>(db->bnd32H.p); F.bndF = reinterpret_cast<int32_t*>(db->bnd32F.p);
         F.top_free = 0; F.left_free = 0; F.floor0 = 0; F.endrule = END_CORNER; F.anchored = 0;
         F.tb = db->pd_tb.p;
-        int rc = launch_pair(db, kfill, F, st);
+        int rc = launch_pair(db, kfill, F, maxm, K, st);
         if (rc) return rc;
         walk_kernel<<<(nb + 63) / 64, 64, 0, st>>>(F, db->pd_ops.p, d_len);
         CU(cudaGetLastError());

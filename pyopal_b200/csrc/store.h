@@ -102,6 +102,7 @@ struct pyopal_cuda_db {
     pyopal::DevBuf<uint8_t> pd_ops;     // alignment operations
     pyopal::DevBuf<int32_t> pd_bnd;     // pass boundary rows (H, F)
     pyopal::DevBuf<uint8_t> pd_jobs;    // PairJob records
+    pyopal::DevBuf<int32_t> pd_team;    // band bookkeeping of pairdp.cu (progress, finished bands, cut, candidates)
     // top-k selection (topk.cu)
     pyopal::DevBuf<uint32_t> tk_ws;
     pyopal::DevBuf<int32_t> tk_vals, tk_idx;

@@ -1,0 +1,3 @@
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_gpu_endfull.py tests/test_gpu_fuzz.py -x -q > gpurun_out/t_ef.log 2>&1; echo "rc=$?" >> gpurun_out/t_ef.log
+timeout 500 python scratch/pairk_probe.py > gpurun_out/pairk.log 2>&1

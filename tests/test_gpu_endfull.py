@@ -229,3 +229,42 @@ def test_reference_vectors_on_gpu(cuda):
         for key, want in v.items():
             if key in got:
                 assert got[key][:n] == want, (v["source"], key)
+
+
+@pytest.mark.parametrize("algo", ALGOS)
+@pytest.mark.parametrize("pair_k", ["4", "12", "32"])
+def test_band_teams_match_oracle(cuda, oracle, monkeypatch, algo, pair_k):
+    # pairdp.cu walks a long query as bands of 32 K rows on several warps at once (pass p one chunk of columns
+    # behind pass p - 1, results merged by the band that finishes last); the band height is normally picked by a
+    # cost model, here it is forced: 700 rows = 6 bands of K = 4, 2 of K = 12, 1 of K = 32.  Homologs give the
+    # reverse pass something to cut short, and equal scores in different bands exercise the merge order.
+    monkeypatch.setenv("PYOPAL_CUDA_PAIR_K", pair_k)
+    rng = np.random.Generator(np.random.PCG64(977 + int(pair_k)))
+    qarr = synthetic.random_residues(rng, 700)
+    query = qarr.tobytes()
+    seqs = rand_seqs(978, 60, 5.5, 0.8, 1, 3000)
+    for k in range(0, 60, 5):
+        a = int(rng.integers(0, 500))
+        piece = synthetic.mutate(rng, qarr[a : a + int(rng.integers(60, 200))])
+        t = np.frombuffer(seqs[k], dtype=np.uint8)
+        pos = int(rng.integers(0, len(t) + 1))
+        seqs[k] = np.concatenate([t[:pos], piece, t[pos:]]).astype(np.uint8).tobytes()
+    seqs[7] = seqs[3]  # duplicates: identical candidates
+    aligner = pyopal.Aligner("BLOSUM62", 11, 1)
+    db = None
+    for mode in ("end", "full"):
+        db = check_mode(oracle, aligner, query, seqs, algo, mode, db=db)
+
+
+def test_band_teams_repeats_tie_across_bands(cuda, oracle, monkeypatch):
+    # a periodic query against a periodic target: the same maximum in every band and many columns, so the first one
+    # in (column, row) order must win whichever band finishes last
+    monkeypatch.setenv("PYOPAL_CUDA_PAIR_K", "4")
+    unit = np.array([0, 4, 7, 10, 13, 16, 19, 3], dtype=np.uint8)
+    query = np.tile(unit, 64).tobytes()  # 512 rows = 4 bands
+    seqs = [np.tile(unit, r).tobytes() for r in (1, 2, 5, 40, 64, 100)] + [np.tile(unit[::-1], 30).tobytes()]
+    aligner = pyopal.Aligner("BLOSUM62", 11, 1)
+    for algo in ALGOS:
+        db = None
+        for mode in ("end", "full"):
+            db = check_mode(oracle, aligner, query, seqs, algo, mode, db=db)
