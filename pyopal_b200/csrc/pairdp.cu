@@ -94,11 +94,12 @@ enum : int { KIND_ALL = 0, KIND_FILL = 1, KIND_EDGE = 2 };
 // an instruction per row); the row is looked up only in the rare step that improves the lane's maximum.  Target
 // residues and pass-boundary rows are fetched 32 columns at a time, one chunk ahead, and handed to the lane that
 // needs them by shuffle, so no global load sits on the chain.
-template <int K, int KIND>
+template <int K, int KIND, int C>
 __global__ void __launch_bounds__(128) pair_kernel(const __grid_constant__ PairParams P) {
     static_assert(K % 4 == 0, "K must be a multiple of 4");
+    static_assert(C == 1 || C == 2 || C == 4, "columns per step");
     __shared__ int sS[33 * 32];
-    __shared__ int2 sbnd[128];  // per warp: the 32 boundary columns of the current chunk
+    __shared__ int2 sbnd[128 * C];  // per warp: the 32 C boundary columns of the current chunk
     const int go = P.go, ge = P.ge;
     const int gmin = min(go, ge);
     for (int x = threadIdx.x; x < P.A * P.A; x += blockDim.x) sS[x] = P.matrix[x] + go;
@@ -152,39 +153,55 @@ __global__ void __launch_bounds__(128) pair_kernel(const __grid_constant__ PairP
                 El[r] = NEGV;
             }
             int Gd0 = border_val(P.left_free, i0 - 1, go, ge) - go;
-            int Gout = 0, Fout = NEGV;
+            int Gout[C], Fout[C];
+#pragma unroll
+            for (int cc = 0; cc < C; ++cc) { Gout[cc] = 0; Fout[cc] = NEGV; }
             // best G of this lane in this band (KIND_ALL); a local score of 0 is "no alignment", never a candidate
             int pvg = P.floor0 ? -go : 4 * NEGV, pc = -1, pi = -1;
             const bool last = (pass == npass - 1);
             const bool own = last && (lane == owner);
-            int nsteps = ncols + 31;
+            // a step takes a lane through a group of C consecutive columns; lane l is one group behind lane l - 1
+            auto steps_for = [](int cols) { return (cols + C - 1) / C + 31; };
+            int nsteps = steps_for(ncols);
             uint32_t tbw[K / 4];
 
-            // chunked prefetch: chunk k = columns [32k, 32k + 32), this lane holds column 32k + lane
-            auto load_res = [&](int col) -> int {
-                return (col < n) ? (int)tbytes[2 * (int64_t)(jb.t0 + jb.tdir * col)] : 0;
+            // chunked prefetch: chunk k = groups [32k, 32k + 32), this lane holds group 32k + lane (C residues, packed)
+            auto load_res = [&](int grp) -> uint32_t {
+                uint32_t w = 0;
+#pragma unroll
+                for (int cc = 0; cc < C; ++cc) {
+                    const int col = C * grp + cc;
+                    if (col < n) w |= (uint32_t)tbytes[2 * (int64_t)(jb.t0 + jb.tdir * col)] << (8 * cc);
+                }
+                return w;
             };
-            // boundary chunk of the band above: wait until it has published those columns, or the job was cut short
-            // (then the columns past the cut are never walked)
-            auto load_bnd = [&](int first, int& h, int& f) {
-                int need = min(first + 32, ncols);
+            // boundary chunk of the band above (32 C columns, this lane takes columns lane, lane + 32, ...): wait until
+            // it has published them, or the job was cut short (then the columns past the cut are never walked)
+            auto load_bnd = [&](int firstgrp, int (&h)[C], int (&f)[C]) {
+                int need = min(C * (firstgrp + 32), ncols);
                 while (ld_volatile(prog_prev) < need) {
                     if (cutting) {
                         const int cc = ld_volatile(cutp);
-                        if (cc < ncols) { ncols = cc; nsteps = min(nsteps, ncols + 31); need = min(need, ncols); }
+                        if (cc < ncols) { ncols = cc; nsteps = min(nsteps, steps_for(ncols)); need = min(need, ncols); }
                     }
                     __nanosleep(40);
                 }
                 __threadfence();
-                const int col = first + lane;
-                if (col < need) { h = __ldcg(bH + 2 * (int64_t)col); f = __ldcg(bF + 2 * (int64_t)col); }
+#pragma unroll
+                for (int cc = 0; cc < C; ++cc) {
+                    const int col = C * firstgrp + lane + 32 * cc;
+                    if (col < need) { h[cc] = __ldcg(bH + 2 * (int64_t)col); f[cc] = __ldcg(bF + 2 * (int64_t)col); }
+                }
             };
-            int rc_prev = 0, rc_cur = load_res(lane), rc_next = load_res(32 + lane);
-            int bh_cur = 0, bf_cur = 0, bh_next = 0, bf_next = 0;
+            uint32_t rc_prev = 0, rc_cur = load_res(lane), rc_next = load_res(32 + lane);
+            int bh_cur[C], bf_cur[C], bh_next[C], bf_next[C];
+#pragma unroll
+            for (int cc = 0; cc < C; ++cc) { bh_cur[cc] = bf_cur[cc] = bh_next[cc] = bf_next[cc] = 0; }
             if (pass > 0) {
                 load_bnd(0, bh_cur, bf_cur);
-                if (32 < ncols) load_bnd(32, bh_next, bf_next);
+                if (C * 32 < ncols) load_bnd(32, bh_next, bf_next);
             }
+            int2* const wbnd = sbnd + (threadIdx.x & ~31) * C;  // this warp's 32 C boundary columns
 
             int thr = pvg;  // KIND_ALL: best G any lane of the warp holds (candidates below it cannot win)
             for (int s0 = 0; s0 < nsteps; s0 += 32) {
@@ -192,111 +209,139 @@ __global__ void __launch_bounds__(128) pair_kernel(const __grid_constant__ PairP
                     // ---- chunk boundary (every 32 steps): everything that touches global memory lives here ----
                     if (cutting && multi) {  // another band may have met `expect`
                         const int cc = ld_volatile(cutp);
-                        if (cc < ncols) { ncols = cc; nsteps = min(nsteps, ncols + 31); if (s0 >= nsteps) break; }
+                        if (cc < ncols) { ncols = cc; nsteps = min(nsteps, steps_for(ncols)); if (s0 >= nsteps) break; }
                     }
                     rc_prev = rc_cur; rc_cur = rc_next; rc_next = load_res(s0 + 32 + lane);
                     if (pass > 0) {
-                        bh_cur = bh_next; bf_cur = bf_next;
-                        if (s0 + 32 < ncols) load_bnd(s0 + 32, bh_next, bf_next);
+#pragma unroll
+                        for (int cc = 0; cc < C; ++cc) { bh_cur[cc] = bh_next[cc]; bf_cur[cc] = bf_next[cc]; }
+                        if (C * (s0 + 32) < ncols) load_bnd(s0 + 32, bh_next, bf_next);
                     }
-                    if (multi && !last && lane == 31 && s0 > 31) {  // lane 31 is done with the columns below s0 - 31
+                    if (multi && !last && lane == 31 && s0 > 31) {  // lane 31 is done with the groups below s0 - 31
                         __threadfence();
-                        *reinterpret_cast<volatile int32_t*>(prog_mine) = min(s0 - 31, ncols);
+                        *reinterpret_cast<volatile int32_t*>(prog_mine) = min(C * (s0 - 31), ncols);
                     }
                 }
-                if (pass > 0) {  // lane 0 reads the boundary row of the band above from shared memory, one column a step
+                if (pass > 0) {  // lane 0 reads the boundary row of the band above from shared memory
                     __syncwarp();
-                    sbnd[threadIdx.x] = make_int2(bh_cur, bf_cur);
+#pragma unroll
+                    for (int cc = 0; cc < C; ++cc) wbnd[lane + 32 * cc] = make_int2(bh_cur[cc], bf_cur[cc]);
                     __syncwarp();
                 }
                 int lim = min(s0 + 32, nsteps);
                 for (int s = s0; s < lim; ++s) {
                     const int sl = s - s0;
-                    int upG = __shfl_up_sync(FULL, Gout, 1);
-                    int upF = __shfl_up_sync(FULL, Fout, 1);
-                    const int tl = __shfl_sync(FULL, (lane <= sl) ? rc_cur : rc_prev, (sl - lane) & 31);
-                    const int c = s - lane;
-                    const bool active = (c >= 0) && (c < ncols) && (nv > 0);
+                    int upG[C], upF[C];
+#pragma unroll
+                    for (int cc = 0; cc < C; ++cc) {
+                        upG[cc] = __shfl_up_sync(FULL, Gout[cc], 1);
+                        upF[cc] = __shfl_up_sync(FULL, Fout[cc], 1);
+                    }
+                    const uint32_t tw = __shfl_sync(FULL, (lane <= sl) ? rc_cur : rc_prev, (sl - lane) & 31);
+                    const int grp = s - lane;
+                    const int c0 = C * grp;
+                    const bool active = (grp >= 0) && (c0 < ncols) && (nv > 0);
                     int cm = 4 * NEGV;
+                    int Gs[C][K];  // KIND_ALL: the columns of this step, for the rare path
                     if (active) {
                         if (lane == 0) {
                             if (pass == 0) {
-                                upG = border_val(P.top_free, c, go, ge) - go;
-                                upF = upG;  // F of the first row: max(-inf, H above - open)
-                            } else {
-                                const int2 bb = sbnd[(threadIdx.x & ~31) + sl];
-                                upG = bb.x;
-                                upF = bb.y;
-                            }
-                        }
-                        int gd = Gd0, gu = upG, f = upF, glast = 0;
-                        const char* const srow = reinterpret_cast<const char*>(sS) + 4 * tl;
 #pragma unroll
-                        for (int r = 0; r < K; ++r) {
-                            const int sc = *reinterpret_cast<const int*>(srow + qa[r]);
-                            const int gl = Gl[r];
-                            const int e = max(El[r] - ge, gl);
-                            const int d = max(gd + sc, floorv);
-                            const int de = max(d, e);
-                            const int deg = de - go;
-                            const int g = max(f - go, deg);  // = max(d, e, F) - open
-                            if (KIND == KIND_ALL) {
-                                cm = max(cm, g);
-                            } else if (KIND == KIND_EDGE) {
-                                if (r == rl) glast = g;
+                                for (int cc = 0; cc < C; ++cc) {
+                                    upG[cc] = border_val(P.top_free, c0 + cc, go, ge) - go;
+                                    upF[cc] = upG[cc];  // F of the first row: max(-inf, H above - open)
+                                }
                             } else {
-                                const int h = max(de, f);
-                                const uint32_t src = (h == d) ? 0u : (h == e) ? 1u : 2u;
-                                const uint32_t b = src | ((e == gl) ? 4u : 0u) | ((f == gu) ? 8u : 0u);
-                                if ((r & 3) == 0) tbw[r >> 2] = b;
-                                else tbw[r >> 2] |= b << (8 * (r & 3));
-                                if (r == rl) glast = g;
-                            }
-                            f = max(f - gmin, deg);
-                            gd = gl;
-                            Gl[r] = g;
-                            El[r] = e;
-                            gu = g;
-                        }
-                        const int hlast = glast + go;
-                        Gout = gu;
-                        Fout = f;
-                        Gd0 = upG;
-                        if (lane == 31 && !last) {
-                            __stcg(bH + 2 * (int64_t)c, Gout);
-                            __stcg(bF + 2 * (int64_t)c, Fout);
-                        }
-                        if (KIND == KIND_EDGE) {
-                            if (own) {
-                                if (P.endrule == END_CORNER) {
-                                    if (c == n - 1) { lv = hlast; lc = c; }
-                                } else if (hlast > lv) {
-                                    lv = hlast; lc = c;
+#pragma unroll
+                                for (int cc = 0; cc < C; ++cc) {
+                                    const int2 bb = wbnd[C * sl + cc];
+                                    upG[cc] = bb.x;
+                                    upF[cc] = bb.y;
                                 }
                             }
-                            if (P.endrule == END_LASTROW_LASTCOL && c == n - 1) {
-#pragma unroll
-                                for (int r = 0; r < K; ++r)
-                                    if (r < nv && Gl[r] + go > cv) { cv = Gl[r] + go; ci = i0 + r; }
-                            }
-                        } else if (KIND == KIND_FILL) {
-                            uint32_t* col = reinterpret_cast<uint32_t*>(P.tb + jb.tb_off + (int64_t)c * ((m + 3) & ~3) + i0);
-#pragma unroll
-                            for (int w = 0; w < K / 4; ++w)
-                                if (4 * w < nv) col[w] = tbw[w];
-                            if (own && c == n - 1) corner = hlast;
                         }
+#pragma unroll
+                        for (int cc = 0; cc < C; ++cc) {
+                            const int c = c0 + cc;
+                            const bool colok = (C == 1) || (c < ncols);  // the last group may run past the target
+                            const int tl = (C == 1) ? (int)tw : (int)((tw >> (8 * cc)) & 255u);
+                            int gd = (cc == 0) ? Gd0 : upG[cc > 0 ? cc - 1 : 0];
+                            int gu = upG[cc], f = upF[cc], glast = 0, cmc = 4 * NEGV;
+                            const char* const srow = reinterpret_cast<const char*>(sS) + 4 * tl;
+#pragma unroll
+                            for (int r = 0; r < K; ++r) {
+                                const int sc = *reinterpret_cast<const int*>(srow + qa[r]);
+                                const int gl = Gl[r];
+                                const int e = max(El[r] - ge, gl);
+                                const int d = max(gd + sc, floorv);
+                                const int de = max(d, e);
+                                const int deg = de - go;
+                                const int g = max(f - go, deg);  // = max(d, e, F) - open
+                                if (KIND == KIND_ALL) {
+                                    cmc = max(cmc, g);
+                                    Gs[cc][r] = g;
+                                } else if (KIND == KIND_EDGE) {
+                                    if (r == rl) glast = g;
+                                } else {
+                                    const int h = max(de, f);
+                                    const uint32_t src = (h == d) ? 0u : (h == e) ? 1u : 2u;
+                                    const uint32_t b = src | ((e == gl) ? 4u : 0u) | ((f == gu) ? 8u : 0u);
+                                    if ((r & 3) == 0) tbw[r >> 2] = b;
+                                    else tbw[r >> 2] |= b << (8 * (r & 3));
+                                    if (r == rl) glast = g;
+                                }
+                                f = max(f - gmin, deg);
+                                gd = gl;
+                                Gl[r] = g;
+                                El[r] = e;
+                                gu = g;
+                            }
+                            const int hlast = glast + go;
+                            Gout[cc] = gu;
+                            Fout[cc] = f;
+                            if (lane == 31 && !last && colok) {
+                                __stcg(bH + 2 * (int64_t)c, gu);
+                                __stcg(bF + 2 * (int64_t)c, f);
+                            }
+                            if (KIND == KIND_ALL) {
+                                cm = max(cm, colok ? cmc : 4 * NEGV);
+                            } else if (KIND == KIND_EDGE) {
+                                if (own && colok) {
+                                    if (P.endrule == END_CORNER) {
+                                        if (c == n - 1) { lv = hlast; lc = c; }
+                                    } else if (hlast > lv) {
+                                        lv = hlast; lc = c;
+                                    }
+                                }
+                                if (P.endrule == END_LASTROW_LASTCOL && c == n - 1) {
+#pragma unroll
+                                    for (int r = 0; r < K; ++r)
+                                        if (r < nv && Gl[r] + go > cv) { cv = Gl[r] + go; ci = i0 + r; }
+                                }
+                            } else {
+                                if (colok) {
+                                    uint32_t* col = reinterpret_cast<uint32_t*>(P.tb + jb.tb_off + (int64_t)c * ((m + 3) & ~3) + i0);
+#pragma unroll
+                                    for (int w = 0; w < K / 4; ++w)
+                                        if (4 * w < nv) col[w] = tbw[w];
+                                }
+                                if (own && c == n - 1) corner = hlast;
+                            }
+                        }
+                        Gd0 = upG[C - 1];
                     }
                     if (KIND == KIND_ALL) {
-                        // rare (a warp-uniform branch): some lane's column beats both its own best and the warp's
+                        // rare (a warp-uniform branch): some lane's group beats both its own best and the warp's
                         const bool cand = (cm > pvg) && (cm >= thr);
                         if (__any_sync(FULL, cand)) {
                             if (cand) {
-                                int rf = -1;  // the first (lowest) real row of the column that holds the maximum
+                                int rf = -1, rc = 0;  // the first cell in (column, row) order that holds the maximum
 #pragma unroll
-                                for (int r = K - 1; r >= 0; --r)
-                                    if (r < nv && Gl[r] == cm) rf = r;
-                                if (rf >= 0) { pvg = cm; pc = c; pi = i0 + rf; }
+                                for (int cc = C - 1; cc >= 0; --cc)
+#pragma unroll
+                                    for (int r = K - 1; r >= 0; --r)
+                                        if (r < nv && (C == 1 || c0 + cc < ncols) && Gs[cc][r] == cm) { rf = r; rc = cc; }
+                                if (rf >= 0) { pvg = cm; pc = c0 + rc; pi = i0 + rf; }
                             }
                             int w = pvg;
                             for (int d = 16; d > 0; d >>= 1) w = max(w, __shfl_xor_sync(FULL, w, d));
@@ -311,7 +356,7 @@ __global__ void __launch_bounds__(128) pair_kernel(const __grid_constant__ PairP
                                         ncols = cmn + 1;
                                         if (multi && lane == 0) atomicMin(cutp, ncols);
                                     }
-                                    nsteps = min(nsteps, ncols + 31);
+                                    nsteps = min(nsteps, steps_for(ncols));
                                     lim = min(lim, nsteps);
                                 }
                             }
@@ -495,42 +540,56 @@ __global__ void fill_i32(int32_t* p, int64_t n, int32_t v) {
 
 typedef void (*pair_kernel_t)(const PairParams);
 
-// Rows per lane.  One pass (K = rows / 32, rounded up to 4) does the least work, and is right when there are targets
-// enough to fill the machine.  With few targets the longest one is the critical path - a single warp walking it
-// column by column - so the query is cut into bands of 32 K rows walked by several warps at once, and the smallest
-// K that the rest of the work allows is best.  Both sides of that trade are modelled in clocks, with constants
-// measured on B200 (scratch/pairk_probe.py): a lone warp takes about 470 + 13 K clocks per column (its ~8.6 K + 60
-// instructions are latency-exposed), a band starts ~96 columns behind the one above it, and a full SM sustains
-// ~2.2 of those instructions per clock.
-int choose_pair_K(int rows, int64_t njobs, int64_t sum_n, int64_t nmax, int64_t table_jobs, int sm_count) {
+// Rows per lane (K) and columns per step (C).  One pass (K = rows / 32, rounded up to 4) does the least work, and is
+// right when there are targets enough to fill the machine.  With few targets the longest one is the critical path -
+// a single warp walking it column by column - so the query is cut into bands of 32 K rows walked by several warps
+// at once, and a lane takes C = 4 columns a step, which spreads the per-step latencies (shuffle round trip,
+// branches, shared-memory loads) over four columns.  Both sides of that trade are modelled in clocks, with
+// constants measured on B200 (scratch/pairk_probe.py): a lone warp takes about 470 + 13 K clocks per step at C = 1
+// and 1090 + 42 K at C = 4, a band starts ~96 steps behind the one above it, a step issues about 8.6 K C + 60
+// (+ 40 at C = 4) instructions and a full SM sustains ~2.2 of them per clock; the two terms add because the long
+// target's warps share their SMs with everybody else's.
+int choose_pair_K(int rows, int64_t njobs, int64_t sum_n, int64_t nmax, int64_t table_jobs, int sm_count, int* C) {
+    *C = 1;
     const int kfit = std::min(32, std::max(4, 4 * ((rows + 127) / 128)));
     const char* env = getenv("PYOPAL_CUDA_PAIR_K");
-    if (env && atoi(env) >= 4) return std::min(32, atoi(env) / 4 * 4);
+    const char* envc = getenv("PYOPAL_CUDA_PAIR_C");
+    if (env && atoi(env) >= 4) {
+        const int k = std::min(32, atoi(env) / 4 * 4);
+        if (envc && atoi(envc) == 4 && k <= 8) *C = 4;
+        return k;
+    }
     double best = 1e300;
     int bk = kfit;
-    for (int k = 4; k <= kfit; k += 4) {
-        const int64_t bands = (rows + 32 * k - 1) / (32 * k);
-        if (k < kfit && table_jobs * bands > ((int64_t)1 << 25)) continue;  // band bookkeeping: 24 B per task
-        const double step = 8.6 * k + 60.0;
-        const double crit = ((double)nmax + 96.0 * (double)(bands - 1)) * (470.0 + 13.0 * k);
-        const double thr = (double)bands * ((double)sum_n + 31.0 * (double)njobs) * step / (2.2 * sm_count);
-        const double c = std::max(crit, thr);
-        if (c < best * 0.97) { best = c; bk = k; }
+    for (int c = 1; c <= 4; c += 3) {
+        for (int k = 4; k <= (c == 1 ? kfit : std::min(kfit, 8)); k += 4) {
+            const int64_t bands = (rows + 32 * k - 1) / (32 * k);
+            if (k < kfit && table_jobs * bands > ((int64_t)1 << 25)) continue;  // band bookkeeping: 24 B per task
+            if (c == 4 && bands > 24) continue;
+            const double step = (c == 1) ? 470.0 + 13.0 * k : 1090.0 + 42.0 * k;
+            const double instr = 8.6 * k * c + (c == 1 ? 60.0 : 100.0);
+            const double crit = ((double)nmax / c + 96.0 * (double)(bands - 1)) * step;
+            const double thr = (double)bands * ((double)sum_n / c + 31.0 * (double)njobs) * instr / (2.2 * sm_count);
+            const double cost = crit + thr;
+            if (cost < best * 0.97) { best = cost; bk = k; *C = c; }
+        }
     }
     return bk;
 }
 
 template <int KIND>
-pair_kernel_t pair_kernel_for(int k) {
+pair_kernel_t pair_kernel_for(int k, int c) {
+    if (c == 4 && k == 4) return pair_kernel<4, KIND, 4>;
+    if (c == 4 && k == 8) return pair_kernel<8, KIND, 4>;
     switch (k) {
-        case 4: return pair_kernel<4, KIND>;
-        case 8: return pair_kernel<8, KIND>;
-        case 12: return pair_kernel<12, KIND>;
-        case 16: return pair_kernel<16, KIND>;
-        case 20: return pair_kernel<20, KIND>;
-        case 24: return pair_kernel<24, KIND>;
-        case 28: return pair_kernel<28, KIND>;
-        default: return pair_kernel<32, KIND>;
+        case 4: return pair_kernel<4, KIND, 1>;
+        case 8: return pair_kernel<8, KIND, 1>;
+        case 12: return pair_kernel<12, KIND, 1>;
+        case 16: return pair_kernel<16, KIND, 1>;
+        case 20: return pair_kernel<20, KIND, 1>;
+        case 24: return pair_kernel<24, KIND, 1>;
+        case 28: return pair_kernel<28, KIND, 1>;
+        default: return pair_kernel<32, KIND, 1>;
     }
 }
 
@@ -632,8 +691,10 @@ int pyopal_end_full_search(pyopal_cuda_db* db, const unsigned char* query, int L
             const int64_t len = db->h_lengths[(size_t)(start + k)];
             sum_n += len; nmax = std::max(nmax, len); nlive += (len > 0);
         }
-        const int K = choose_pair_K(Lq, nlive, sum_n, nmax, njobs, db->sm_count);
-        pair_kernel_t kloc = (cfg_for_mode(mode).endrule == END_ALL) ? pair_kernel_for<KIND_ALL>(K) : pair_kernel_for<KIND_EDGE>(K);
+        int Cc = 1;
+        const int K = choose_pair_K(Lq, nlive, sum_n, nmax, njobs, db->sm_count, &Cc);
+        pair_kernel_t kloc = (cfg_for_mode(mode).endrule == END_ALL) ? pair_kernel_for<KIND_ALL>(K, Cc) : pair_kernel_for<KIND_EDGE>(K, Cc);
+        db->stats[5] = Cc;
         db->stats[6] = K;
         db->stats[7] = (Lq + 32 * K - 1) / (32 * K);
         if (Lq > 32 * K) {
@@ -780,8 +841,9 @@ int pyopal_end_full_search(pyopal_cuda_db* db, const unsigned char* query, int L
         d_jobs = reinterpret_cast<PairJob*>(db->pd_jobs.p);
         int32_t* d_len = db->pd_i32.p;
         int32_t* d_ctl = d_len + nb;
-        const int K = choose_pair_K(maxm, nb, sum_tn, max_tn, nb, db->sm_count);
-        pair_kernel_t kfill = pair_kernel_for<KIND_FILL>(K);
+        int Cc = 1;
+        const int K = choose_pair_K(maxm, nb, sum_tn, max_tn, nb, db->sm_count, &Cc);
+        pair_kernel_t kfill = pair_kernel_for<KIND_FILL>(K, Cc);
         if (maxm > 32 * K)
             if (db->bnd32H.reserve((size_t)db->ncols * 2 + 16) || db->bnd32F.reserve((size_t)db->ncols * 2 + 16))
                 return PYOPAL_CUDA_ERR_NOMEM;

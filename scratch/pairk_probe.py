@@ -17,12 +17,13 @@ for qi in (1, 2, 4):
     top = np.sort(np.argsort(-sc, kind="stable")[:1000])
     sr, so, sl = sharding.pack_shard(res2, off2, ln2, top)
     sub = cuda.DeviceStore(sr, so, sl, 24, device=0)
-    for k in ("", "4", "8", "12", "16", "24", "32"):
-        if k: os.environ["PYOPAL_CUDA_PAIR_K"] = k
-        else: os.environ.pop("PYOPAL_CUDA_PAIR_K", None)
+    for k in ("", "4", "4x4", "8", "8x4", "12", "16", "32"):
+        kk, _, cc = k.partition("x")
+        if kk: os.environ["PYOPAL_CUDA_PAIR_K"] = kk; os.environ["PYOPAL_CUDA_PAIR_C"] = cc or "1"
+        else: os.environ.pop("PYOPAL_CUDA_PAIR_K", None); os.environ.pop("PYOPAL_CUDA_PAIR_C", None)
         for mode in (1, 2):
             best = 1e9
             for _ in range(3):
                 t = time.perf_counter(); sub.search(q, 11, 1, M, mode, 3, lengths=sl); best = min(best, time.perf_counter() - t)
             st = sub.stats()
-            print(f"Lq={len(q)} forcedK={k or 'model'} mode={mode} K={st['K']} bands={st['passes']} wall {best*1e3:.2f} ms", flush=True)
+            print(f"Lq={len(q)} forcedK={k or 'model'} mode={mode} K={st['K']} C={st['G']} bands={st['passes']} wall {best*1e3:.2f} ms", flush=True)

@@ -232,14 +232,17 @@ def test_reference_vectors_on_gpu(cuda):
 
 
 @pytest.mark.parametrize("algo", ALGOS)
-@pytest.mark.parametrize("pair_k", ["4", "12", "32"])
+@pytest.mark.parametrize("pair_k", ["4", "12", "32", "4x4", "8x4", "8x1"])
 def test_band_teams_match_oracle(cuda, oracle, monkeypatch, algo, pair_k):
     # pairdp.cu walks a long query as bands of 32 K rows on several warps at once (pass p one chunk of columns
     # behind pass p - 1, results merged by the band that finishes last); the band height is normally picked by a
     # cost model, here it is forced: 700 rows = 6 bands of K = 4, 2 of K = 12, 1 of K = 32.  Homologs give the
     # reverse pass something to cut short, and equal scores in different bands exercise the merge order.
-    monkeypatch.setenv("PYOPAL_CUDA_PAIR_K", pair_k)
-    rng = np.random.Generator(np.random.PCG64(977 + int(pair_k)))
+    # "KxC": C columns per step (the latency-bound shape takes four)
+    k, _, c = pair_k.partition("x")
+    monkeypatch.setenv("PYOPAL_CUDA_PAIR_K", k)
+    monkeypatch.setenv("PYOPAL_CUDA_PAIR_C", c or "1")
+    rng = np.random.Generator(np.random.PCG64(977 + int(k) + 100 * int(c or 1)))
     qarr = synthetic.random_residues(rng, 700)
     query = qarr.tobytes()
     seqs = rand_seqs(978, 60, 5.5, 0.8, 1, 3000)
@@ -260,6 +263,7 @@ def test_band_teams_repeats_tie_across_bands(cuda, oracle, monkeypatch):
     # a periodic query against a periodic target: the same maximum in every band and many columns, so the first one
     # in (column, row) order must win whichever band finishes last
     monkeypatch.setenv("PYOPAL_CUDA_PAIR_K", "4")
+    monkeypatch.setenv("PYOPAL_CUDA_PAIR_C", "4")
     unit = np.array([0, 4, 7, 10, 13, 16, 19, 3], dtype=np.uint8)
     query = np.tile(unit, 64).tobytes()  # 512 rows = 4 bands
     seqs = [np.tile(unit, r).tobytes() for r in (1, 2, 5, 40, 64, 100)] + [np.tile(unit[::-1], 30).tobytes()]
