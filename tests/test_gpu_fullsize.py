@@ -173,3 +173,34 @@ def test_sharded_database_api_single_rank(cuda, oracle):
     assert blk.search_scores(queries[0], GO, GE, M).cpu().tolist() == list(want[0])
     with pytest.raises(ValueError):
         sharding.ShardedDatabase.from_blocks((residues, offsets, lengths), 1000, 2, device=0)
+
+
+@pytest.mark.parametrize("qi,algo", [(2, "sw"), (3, "sw"), (3, "hw"), (2, "ov"), (1, "nw")])
+def test_config4_top_hits_end_and_full(full, oracle, cuda, qi, algo):
+    # BASELINE.json config 4 at full size: score pass over the 570k-protein database, the top hits (which include
+    # the planted 10 000 - 35 213-aa giants: SW scores grow with length) re-aligned in end and full mode, every
+    # score, end cell, start cell and operation string against the oracle.  1000- and 2000-aa queries make
+    # pairdp.cu walk the giants as concurrent bands, four columns a step.
+    residues, offsets, lengths = full["db"]
+    q = full["queries"][qi]
+    sc = gpu_scores(full, q, algo)
+    k = 120
+    top = np.sort(np.argsort(-sc.astype(np.int64), kind="stable")[:k])
+    giants = np.nonzero(lengths >= 30_000)[0][:3]
+    top = np.unique(np.concatenate([top, giants]))
+    sr, so, sl = sharding.pack_shard(residues, offsets, lengths, top)
+    sub = cuda.DeviceStore(sr, so, sl, 24, device=0)
+    flat = (sr.tobytes() + b"\0", array.array("q", so.tolist()), array.array("i", sl.tolist()))
+    for mode, st in (("end", 1), ("full", 2)):
+        got = sub.search(q, GO, GE, full["M"], st, ALGO[algo], lengths=sl)
+        want = oracle.search_flat(q, *flat, full["M"], 24, GO, GE, algo, mode, 8)
+        assert list(got[0]) == want["score"], (algo, mode)
+        assert list(got[0]) == [int(x) for x in sc[top]]
+        assert list(got[1]) == want["query_end"] and list(got[2]) == want["target_end"], (algo, mode)
+        if st == 2:
+            assert list(got[3]) == want["query_start"] and list(got[4]) == want["target_start"], (algo, mode)
+            ops, oo, ol = got[5], got[6], got[7]
+            for j in range(len(top)):
+                assert bytes(ops[oo[j] : oo[j] + ol[j]]) == want["alignment"][j], (algo, mode, j)
+    stats = sub.stats()
+    assert stats["K"] in (4, 8) and stats["passes"] > 1  # the latency-bound shape was chosen
