@@ -204,3 +204,24 @@ def test_config4_top_hits_end_and_full(full, oracle, cuda, qi, algo):
                 assert bytes(ops[oo[j] : oo[j] + ol[j]]) == want["alignment"][j], (algo, mode, j)
     stats = sub.stats()
     assert stats["K"] in (4, 8) and stats["passes"] > 1  # the latency-bound shape was chosen
+
+
+@pytest.mark.parametrize("qi,algo", [(1, "sw"), (3, "sw"), (3, "hw")])
+def test_whole_database_end_mode(full, oracle, qi, algo):
+    # end mode over all 570k proteins (the throughput shape of pairdp.cu: one pass of K = 12 rows per lane for the
+    # 300-aa query, two concurrent bands of K = 32 for the 2000-aa one): scores equal the score-mode search
+    # everywhere, end cells equal the oracle's on a random subsample plus every planted giant.
+    residues, offsets, lengths = full["db"]
+    q = full["queries"][qi]
+    out = full["store"].search(q, GO, GE, full["M"], 1, ALGO[algo], lengths=lengths)
+    got_s, got_q, got_t = (np.frombuffer(x, dtype=np.int32) for x in out[:3])
+    assert np.array_equal(got_s, gpu_scores(full, q, algo))
+    rng = np.random.Generator(np.random.PCG64(1234 + qi))
+    giants = np.nonzero(lengths >= 10_000)[0]
+    idx = np.unique(np.concatenate([rng.choice(len(lengths), 1500, replace=False), giants]))
+    sr, so, sl = sharding.pack_shard(residues, offsets, lengths, idx)
+    want = oracle.search_flat(q, sr.tobytes() + b"\0", array.array("q", so.tolist()), array.array("i", sl.tolist()),
+                              full["M"], 24, GO, GE, algo, "end", 8)
+    assert got_s[idx].tolist() == want["score"]
+    assert got_q[idx].tolist() == want["query_end"]
+    assert got_t[idx].tolist() == want["target_end"]
