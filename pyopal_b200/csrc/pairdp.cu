@@ -193,13 +193,28 @@ __global__ void __launch_bounds__(128) pair_kernel(const __grid_constant__ PairP
                     if (col < need) { h[cc] = __ldcg(bH + 2 * (int64_t)col); f[cc] = __ldcg(bF + 2 * (int64_t)col); }
                 }
             };
+            // the same without waiting: false when the band above has not got that far yet
+            auto try_bnd = [&](int firstgrp, int (&h)[C], int (&f)[C]) -> bool {
+                const int need = min(C * (firstgrp + 32), ncols);
+                if (ld_volatile(prog_prev) < need) return false;
+                __threadfence();
+#pragma unroll
+                for (int cc = 0; cc < C; ++cc) {
+                    const int col = C * firstgrp + lane + 32 * cc;
+                    if (col < need) { h[cc] = __ldcg(bH + 2 * (int64_t)col); f[cc] = __ldcg(bF + 2 * (int64_t)col); }
+                }
+                return true;
+            };
             uint32_t rc_prev = 0, rc_cur = load_res(lane), rc_next = load_res(32 + lane);
             int bh_cur[C], bf_cur[C], bh_next[C], bf_next[C];
 #pragma unroll
             for (int cc = 0; cc < C; ++cc) { bh_cur[cc] = bf_cur[cc] = bh_next[cc] = bf_next[cc] = 0; }
+            // a band follows the one above as closely as the published columns allow: the chunk after the current
+            // one is tried for at every half chunk and waited for only when the current one is used up
+            bool have_next = true;
             if (pass > 0) {
                 load_bnd(0, bh_cur, bf_cur);
-                if (C * 32 < ncols) load_bnd(32, bh_next, bf_next);
+                if (C * 32 < ncols) have_next = try_bnd(32, bh_next, bf_next);
             }
             int2* const wbnd = sbnd + (threadIdx.x & ~31) * C;  // this warp's 32 C boundary columns
 
@@ -213,9 +228,10 @@ __global__ void __launch_bounds__(128) pair_kernel(const __grid_constant__ PairP
                     }
                     rc_prev = rc_cur; rc_cur = rc_next; rc_next = load_res(s0 + 32 + lane);
                     if (pass > 0) {
+                        if (!have_next) load_bnd(s0, bh_next, bf_next);
 #pragma unroll
                         for (int cc = 0; cc < C; ++cc) { bh_cur[cc] = bh_next[cc]; bf_cur[cc] = bf_next[cc]; }
-                        if (C * (s0 + 32) < ncols) load_bnd(s0 + 32, bh_next, bf_next);
+                        have_next = (C * (s0 + 32) < ncols) ? try_bnd(s0 + 32, bh_next, bf_next) : true;
                     }
                     if (multi && !last && lane == 31 && s0 > 31) {  // lane 31 is done with the groups below s0 - 31
                         __threadfence();
@@ -228,8 +244,10 @@ __global__ void __launch_bounds__(128) pair_kernel(const __grid_constant__ PairP
                     for (int cc = 0; cc < C; ++cc) wbnd[lane + 32 * cc] = make_int2(bh_cur[cc], bf_cur[cc]);
                     __syncwarp();
                 }
-                int lim = min(s0 + 32, nsteps);
-                for (int s = s0; s < lim; ++s) {
+                for (int hb = 0; hb < 2; ++hb) {
+                if (hb == 1 && pass > 0 && !have_next) have_next = try_bnd(s0 + 32, bh_next, bf_next);
+                int lim = min(s0 + 16 * (hb + 1), nsteps);
+                for (int s = s0 + 16 * hb; s < lim; ++s) {
                     const int sl = s - s0;
                     int upG[C], upF[C];
 #pragma unroll
@@ -362,6 +380,7 @@ __global__ void __launch_bounds__(128) pair_kernel(const __grid_constant__ PairP
                             }
                         }
                     }
+                }
                 }
             }
             if (multi && !last) {
@@ -546,7 +565,7 @@ typedef void (*pair_kernel_t)(const PairParams);
 // at once, and a lane takes C = 4 columns a step, which spreads the per-step latencies (shuffle round trip,
 // branches, shared-memory loads) over four columns.  Both sides of that trade are modelled in clocks, with
 // constants measured on B200 (scratch/pairk_probe.py): a lone warp takes about 470 + 13 K clocks per step at C = 1
-// and 1090 + 42 K at C = 4, a band starts ~96 steps behind the one above it, a step issues about 8.6 K C + 60
+// and 1090 + 42 K at C = 4, a band follows ~72 steps behind the one above it, a step issues about 8.6 K C + 60
 // (+ 40 at C = 4) instructions and a full SM sustains ~2.2 of them per clock; the two terms add because the long
 // target's warps share their SMs with everybody else's.
 int choose_pair_K(int rows, int64_t njobs, int64_t sum_n, int64_t nmax, int64_t table_jobs, int sm_count, int* C) {
@@ -568,7 +587,7 @@ int choose_pair_K(int rows, int64_t njobs, int64_t sum_n, int64_t nmax, int64_t 
             if (c == 4 && bands > 24) continue;
             const double step = (c == 1) ? 470.0 + 13.0 * k : 1090.0 + 42.0 * k;
             const double instr = 8.6 * k * c + (c == 1 ? 60.0 : 100.0);
-            const double crit = ((double)nmax / c + 96.0 * (double)(bands - 1)) * step;
+            const double crit = ((double)nmax / c + 72.0 * (double)(bands - 1)) * step;
             const double thr = (double)bands * ((double)sum_n / c + 31.0 * (double)njobs) * instr / (2.2 * sm_count);
             const double cost = crit + thr;
             if (cost < best * 0.97) { best = cost; bk = k; *C = c; }
