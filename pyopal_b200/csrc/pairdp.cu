@@ -148,7 +148,8 @@ __global__ void __launch_bounds__(128) pair_kernel(const __grid_constant__ PairP
 #pragma unroll
             for (int r = 0; r < K; ++r) {
                 const int i = i0 + r;
-                qa[r] = 4 * ((r < nv) ? (int)P.query[jb.q0 + jb.qdir * i] * P.A : P.A * P.A);  // byte offset of the row in sS
+                // byte offset of the query letter's row in sS (padding rows: the -inf row)
+                qa[r] = 4 * ((r < nv) ? (int)P.query[jb.q0 + jb.qdir * i] * P.A : P.A * P.A);
                 Gl[r] = border_val(P.left_free, i, go, ge) - go;
                 El[r] = NEGV;
             }
@@ -245,142 +246,143 @@ __global__ void __launch_bounds__(128) pair_kernel(const __grid_constant__ PairP
                     __syncwarp();
                 }
                 for (int hb = 0; hb < 2; ++hb) {
-                if (hb == 1 && pass > 0 && !have_next) have_next = try_bnd(s0 + 32, bh_next, bf_next);
-                int lim = min(s0 + 16 * (hb + 1), nsteps);
-                for (int s = s0 + 16 * hb; s < lim; ++s) {
-                    const int sl = s - s0;
-                    int upG[C], upF[C];
-#pragma unroll
-                    for (int cc = 0; cc < C; ++cc) {
-                        upG[cc] = __shfl_up_sync(FULL, Gout[cc], 1);
-                        upF[cc] = __shfl_up_sync(FULL, Fout[cc], 1);
-                    }
-                    const uint32_t tw = __shfl_sync(FULL, (lane <= sl) ? rc_cur : rc_prev, (sl - lane) & 31);
-                    const int grp = s - lane;
-                    const int c0 = C * grp;
-                    const bool active = (grp >= 0) && (c0 < ncols) && (nv > 0);
-                    int cm = 4 * NEGV;
-                    int Gs[C][K];  // KIND_ALL: the columns of this step, for the rare path
-                    if (active) {
-                        if (lane == 0) {
-                            if (pass == 0) {
-#pragma unroll
-                                for (int cc = 0; cc < C; ++cc) {
-                                    upG[cc] = border_val(P.top_free, c0 + cc, go, ge) - go;
-                                    upF[cc] = upG[cc];  // F of the first row: max(-inf, H above - open)
-                                }
-                            } else {
-#pragma unroll
-                                for (int cc = 0; cc < C; ++cc) {
-                                    const int2 bb = wbnd[C * sl + cc];
-                                    upG[cc] = bb.x;
-                                    upF[cc] = bb.y;
-                                }
-                            }
-                        }
+                    if (hb == 1 && pass > 0 && !have_next) have_next = try_bnd(s0 + 32, bh_next, bf_next);
+                    int lim = min(s0 + 16 * (hb + 1), nsteps);
+                    for (int s = s0 + 16 * hb; s < lim; ++s) {
+                        const int sl = s - s0;
+                        int upG[C], upF[C];
 #pragma unroll
                         for (int cc = 0; cc < C; ++cc) {
-                            const int c = c0 + cc;
-                            const bool colok = (C == 1) || (c < ncols);  // the last group may run past the target
-                            const int tl = (C == 1) ? (int)tw : (int)((tw >> (8 * cc)) & 255u);
-                            int gd = (cc == 0) ? Gd0 : upG[cc > 0 ? cc - 1 : 0];
-                            int gu = upG[cc], f = upF[cc], glast = 0, cmc = 4 * NEGV;
-                            const char* const srow = reinterpret_cast<const char*>(sS) + 4 * tl;
+                            upG[cc] = __shfl_up_sync(FULL, Gout[cc], 1);
+                            upF[cc] = __shfl_up_sync(FULL, Fout[cc], 1);
+                        }
+                        const uint32_t tw = __shfl_sync(FULL, (lane <= sl) ? rc_cur : rc_prev, (sl - lane) & 31);
+                        const int grp = s - lane;
+                        const int c0 = C * grp;
+                        const bool active = (grp >= 0) && (c0 < ncols) && (nv > 0);
+                        int cm = 4 * NEGV;
+                        int Gs[C][K];  // KIND_ALL: the columns of this step, for the rare path
+                        if (active) {
+                            if (lane == 0) {
+                                if (pass == 0) {
 #pragma unroll
-                            for (int r = 0; r < K; ++r) {
-                                const int sc = *reinterpret_cast<const int*>(srow + qa[r]);
-                                const int gl = Gl[r];
-                                const int e = max(El[r] - ge, gl);
-                                const int d = max(gd + sc, floorv);
-                                const int de = max(d, e);
-                                const int deg = de - go;
-                                const int g = max(f - go, deg);  // = max(d, e, F) - open
-                                if (KIND == KIND_ALL) {
-                                    cmc = max(cmc, g);
-                                    Gs[cc][r] = g;
-                                } else if (KIND == KIND_EDGE) {
-                                    if (r == rl) glast = g;
+                                    for (int cc = 0; cc < C; ++cc) {
+                                        upG[cc] = border_val(P.top_free, c0 + cc, go, ge) - go;
+                                        upF[cc] = upG[cc];  // F of the first row: max(-inf, H above - open)
+                                    }
                                 } else {
-                                    const int h = max(de, f);
-                                    const uint32_t src = (h == d) ? 0u : (h == e) ? 1u : 2u;
-                                    const uint32_t b = src | ((e == gl) ? 4u : 0u) | ((f == gu) ? 8u : 0u);
-                                    if ((r & 3) == 0) tbw[r >> 2] = b;
-                                    else tbw[r >> 2] |= b << (8 * (r & 3));
-                                    if (r == rl) glast = g;
-                                }
-                                f = max(f - gmin, deg);
-                                gd = gl;
-                                Gl[r] = g;
-                                El[r] = e;
-                                gu = g;
-                            }
-                            const int hlast = glast + go;
-                            Gout[cc] = gu;
-                            Fout[cc] = f;
-                            if (lane == 31 && !last && colok) {
-                                __stcg(bH + 2 * (int64_t)c, gu);
-                                __stcg(bF + 2 * (int64_t)c, f);
-                            }
-                            if (KIND == KIND_ALL) {
-                                cm = max(cm, colok ? cmc : 4 * NEGV);
-                            } else if (KIND == KIND_EDGE) {
-                                if (own && colok) {
-                                    if (P.endrule == END_CORNER) {
-                                        if (c == n - 1) { lv = hlast; lc = c; }
-                                    } else if (hlast > lv) {
-                                        lv = hlast; lc = c;
+#pragma unroll
+                                    for (int cc = 0; cc < C; ++cc) {
+                                        const int2 bb = wbnd[C * sl + cc];
+                                        upG[cc] = bb.x;
+                                        upF[cc] = bb.y;
                                     }
                                 }
-                                if (P.endrule == END_LASTROW_LASTCOL && c == n - 1) {
-#pragma unroll
-                                    for (int r = 0; r < K; ++r)
-                                        if (r < nv && Gl[r] + go > cv) { cv = Gl[r] + go; ci = i0 + r; }
-                                }
-                            } else {
-                                if (colok) {
-                                    uint32_t* col = reinterpret_cast<uint32_t*>(P.tb + jb.tb_off + (int64_t)c * ((m + 3) & ~3) + i0);
-#pragma unroll
-                                    for (int w = 0; w < K / 4; ++w)
-                                        if (4 * w < nv) col[w] = tbw[w];
-                                }
-                                if (own && c == n - 1) corner = hlast;
                             }
-                        }
-                        Gd0 = upG[C - 1];
-                    }
-                    if (KIND == KIND_ALL) {
-                        // rare (a warp-uniform branch): some lane's group beats both its own best and the warp's
-                        const bool cand = (cm > pvg) && (cm >= thr);
-                        if (__any_sync(FULL, cand)) {
-                            if (cand) {
-                                int rf = -1, rc = 0;  // the first cell in (column, row) order that holds the maximum
 #pragma unroll
-                                for (int cc = C - 1; cc >= 0; --cc)
+                            for (int cc = 0; cc < C; ++cc) {
+                                const int c = c0 + cc;
+                                const bool colok = (C == 1) || (c < ncols);  // the last group may run past the target
+                                const int tl = (C == 1) ? (int)tw : (int)((tw >> (8 * cc)) & 255u);
+                                int gd = (cc == 0) ? Gd0 : upG[cc > 0 ? cc - 1 : 0];
+                                int gu = upG[cc], f = upF[cc], glast = 0, cmc = 4 * NEGV;
+                                const char* const srow = reinterpret_cast<const char*>(sS) + 4 * tl;
 #pragma unroll
-                                    for (int r = K - 1; r >= 0; --r)
-                                        if (r < nv && (C == 1 || c0 + cc < ncols) && Gs[cc][r] == cm) { rf = r; rc = cc; }
-                                if (rf >= 0) { pvg = cm; pc = c0 + rc; pi = i0 + rf; }
-                            }
-                            int w = pvg;
-                            for (int d = 16; d > 0; d >>= 1) w = max(w, __shfl_xor_sync(FULL, w, d));
-                            thr = w;
-                            if (cutting) {
-                                // reverse pass: stop once every lane is past the first column that reached `expect`
-                                const bool hit = (pc >= 0) && (pvg + go == jb.expect);
-                                if (__any_sync(FULL, hit)) {
-                                    int cmn = hit ? pc : INT_MAX;
-                                    for (int d = 16; d > 0; d >>= 1) cmn = min(cmn, __shfl_xor_sync(FULL, cmn, d));
-                                    if (cmn + 1 < ncols) {
-                                        ncols = cmn + 1;
-                                        if (multi && lane == 0) atomicMin(cutp, ncols);
+                                for (int r = 0; r < K; ++r) {
+                                    const int sc = *reinterpret_cast<const int*>(srow + qa[r]);
+                                    const int gl = Gl[r];
+                                    const int e = max(El[r] - ge, gl);
+                                    const int d = max(gd + sc, floorv);
+                                    const int de = max(d, e);
+                                    const int deg = de - go;
+                                    const int g = max(f - go, deg);  // = max(d, e, F) - open
+                                    if (KIND == KIND_ALL) {
+                                        cmc = max(cmc, g);
+                                        Gs[cc][r] = g;
+                                    } else if (KIND == KIND_EDGE) {
+                                        if (r == rl) glast = g;
+                                    } else {
+                                        const int h = max(de, f);
+                                        const uint32_t src = (h == d) ? 0u : (h == e) ? 1u : 2u;
+                                        const uint32_t b = src | ((e == gl) ? 4u : 0u) | ((f == gu) ? 8u : 0u);
+                                        if ((r & 3) == 0) tbw[r >> 2] = b;
+                                        else tbw[r >> 2] |= b << (8 * (r & 3));
+                                        if (r == rl) glast = g;
                                     }
-                                    nsteps = min(nsteps, steps_for(ncols));
-                                    lim = min(lim, nsteps);
+                                    f = max(f - gmin, deg);
+                                    gd = gl;
+                                    Gl[r] = g;
+                                    El[r] = e;
+                                    gu = g;
+                                }
+                                const int hlast = glast + go;
+                                Gout[cc] = gu;
+                                Fout[cc] = f;
+                                if (lane == 31 && !last && colok) {
+                                    __stcg(bH + 2 * (int64_t)c, gu);
+                                    __stcg(bF + 2 * (int64_t)c, f);
+                                }
+                                if (KIND == KIND_ALL) {
+                                    cm = max(cm, colok ? cmc : 4 * NEGV);
+                                } else if (KIND == KIND_EDGE) {
+                                    if (own && colok) {
+                                        if (P.endrule == END_CORNER) {
+                                            if (c == n - 1) { lv = hlast; lc = c; }
+                                        } else if (hlast > lv) {
+                                            lv = hlast; lc = c;
+                                        }
+                                    }
+                                    if (P.endrule == END_LASTROW_LASTCOL && c == n - 1) {
+#pragma unroll
+                                        for (int r = 0; r < K; ++r)
+                                            if (r < nv && Gl[r] + go > cv) { cv = Gl[r] + go; ci = i0 + r; }
+                                    }
+                                } else {
+                                    if (colok) {
+                                        uint8_t* colb = P.tb + jb.tb_off + (int64_t)c * ((m + 3) & ~3) + i0;
+                                        uint32_t* col = reinterpret_cast<uint32_t*>(colb);
+#pragma unroll
+                                        for (int w = 0; w < K / 4; ++w)
+                                            if (4 * w < nv) col[w] = tbw[w];
+                                    }
+                                    if (own && c == n - 1) corner = hlast;
+                                }
+                            }
+                            Gd0 = upG[C - 1];
+                        }
+                        if (KIND == KIND_ALL) {
+                            // rare (a warp-uniform branch): some lane's group beats both its own best and the warp's
+                            const bool cand = (cm > pvg) && (cm >= thr);
+                            if (__any_sync(FULL, cand)) {
+                                if (cand) {
+                                    int rf = -1, rc = 0;  // the first cell in (column, row) order that holds the maximum
+#pragma unroll
+                                    for (int cc = C - 1; cc >= 0; --cc)
+#pragma unroll
+                                        for (int r = K - 1; r >= 0; --r)
+                                            if (r < nv && (C == 1 || c0 + cc < ncols) && Gs[cc][r] == cm) { rf = r; rc = cc; }
+                                    if (rf >= 0) { pvg = cm; pc = c0 + rc; pi = i0 + rf; }
+                                }
+                                int w = pvg;
+                                for (int d = 16; d > 0; d >>= 1) w = max(w, __shfl_xor_sync(FULL, w, d));
+                                thr = w;
+                                if (cutting) {
+                                    // reverse pass: stop once every lane is past the first column that reached `expect`
+                                    const bool hit = (pc >= 0) && (pvg + go == jb.expect);
+                                    if (__any_sync(FULL, hit)) {
+                                        int cmn = hit ? pc : INT_MAX;
+                                        for (int d = 16; d > 0; d >>= 1) cmn = min(cmn, __shfl_xor_sync(FULL, cmn, d));
+                                        if (cmn + 1 < ncols) {
+                                            ncols = cmn + 1;
+                                            if (multi && lane == 0) atomicMin(cutp, ncols);
+                                        }
+                                        nsteps = min(nsteps, steps_for(ncols));
+                                        lim = min(lim, nsteps);
+                                    }
                                 }
                             }
                         }
                     }
-                }
                 }
             }
             if (multi && !last) {
@@ -712,7 +714,8 @@ int pyopal_end_full_search(pyopal_cuda_db* db, const unsigned char* query, int L
         }
         int Cc = 1;
         const int K = choose_pair_K(Lq, nlive, sum_n, nmax, njobs, db->sm_count, &Cc);
-        pair_kernel_t kloc = (cfg_for_mode(mode).endrule == END_ALL) ? pair_kernel_for<KIND_ALL>(K, Cc) : pair_kernel_for<KIND_EDGE>(K, Cc);
+        pair_kernel_t kloc = (cfg_for_mode(mode).endrule == END_ALL) ? pair_kernel_for<KIND_ALL>(K, Cc)
+                                                                      : pair_kernel_for<KIND_EDGE>(K, Cc);
         db->stats[5] = Cc;
         db->stats[6] = K;
         db->stats[7] = (Lq + 32 * K - 1) / (32 * K);
