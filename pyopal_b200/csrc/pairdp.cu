@@ -96,7 +96,7 @@ enum : int { KIND_ALL = 0, KIND_FILL = 1, KIND_EDGE = 2 };
 // needs them by shuffle, so no global load sits on the chain.
 template <int K, int KIND, int C>
 __global__ void __launch_bounds__(128) pair_kernel(const __grid_constant__ PairParams P) {
-    static_assert(K % 4 == 0, "K must be a multiple of 4");
+    static_assert(K % 2 == 0 && (KIND != KIND_FILL || K % 4 == 0), "the fill kernel packs four rows per 32-bit store");
     static_assert(C == 1 || C == 2 || C == 4, "columns per step");
     __shared__ int sS[33 * 32];
     __shared__ int2 sbnd[128 * C];  // per warp: the 32 C boundary columns of the current chunk
@@ -164,7 +164,7 @@ __global__ void __launch_bounds__(128) pair_kernel(const __grid_constant__ PairP
             // a step takes a lane through a group of C consecutive columns; lane l is one group behind lane l - 1
             auto steps_for = [](int cols) { return (cols + C - 1) / C + 31; };
             int nsteps = steps_for(ncols);
-            uint32_t tbw[K / 4];
+            uint32_t tbw[(K + 3) / 4];
 
             // chunked prefetch: chunk k = groups [32k, 32k + 32), this lane holds group 32k + lane (C residues, packed)
             auto load_res = [&](int grp) -> uint32_t {
@@ -570,20 +570,21 @@ typedef void (*pair_kernel_t)(const PairParams);
 // and 1090 + 42 K at C = 4, a band follows ~72 steps behind the one above it, a step issues about 8.6 K C + 60
 // (+ 40 at C = 4) instructions and a full SM sustains ~2.2 of them per clock; the two terms add because the long
 // target's warps share their SMs with everybody else's.
-int choose_pair_K(int rows, int64_t njobs, int64_t sum_n, int64_t nmax, int64_t table_jobs, int sm_count, int* C) {
+int choose_pair_K(int rows, int64_t njobs, int64_t sum_n, int64_t nmax, int64_t table_jobs, int sm_count, int gran, int* C) {
     *C = 1;
-    const int kfit = std::min(32, std::max(4, 4 * ((rows + 127) / 128)));
+    // `gran`: K comes in steps of 2 for the locate kernels, 4 for the fill kernel (four rows per 32-bit store)
+    const int kfit = std::min(32, std::max(4, gran * ((rows + 32 * gran - 1) / (32 * gran))));
     const char* env = getenv("PYOPAL_CUDA_PAIR_K");
     const char* envc = getenv("PYOPAL_CUDA_PAIR_C");
     if (env && atoi(env) >= 4) {
-        const int k = std::min(32, atoi(env) / 4 * 4);
+        const int k = std::min(32, atoi(env) / gran * gran);
         if (envc && atoi(envc) == 4 && k <= 8) *C = 4;
         return k;
     }
     double best = 1e300;
     int bk = kfit;
     for (int c = 1; c <= 4; c += 3) {
-        for (int k = 4; k <= (c == 1 ? kfit : std::min(kfit, 8)); k += 4) {
+        for (int k = 4; k <= (c == 1 ? kfit : std::min(kfit, 8)); k += (c == 1 ? gran : 4)) {
             const int64_t bands = (rows + 32 * k - 1) / (32 * k);
             if (k < kfit && table_jobs * bands > ((int64_t)1 << 25)) continue;  // band bookkeeping: 24 B per task
             if (c == 4 && bands > 24) continue;
@@ -602,6 +603,18 @@ template <int KIND>
 pair_kernel_t pair_kernel_for(int k, int c) {
     if (c == 4 && k == 4) return pair_kernel<4, KIND, 4>;
     if (c == 4 && k == 8) return pair_kernel<8, KIND, 4>;
+    if constexpr (KIND != KIND_FILL) {
+        switch (k) {
+            case 6: return pair_kernel<6, KIND, 1>;
+            case 10: return pair_kernel<10, KIND, 1>;
+            case 14: return pair_kernel<14, KIND, 1>;
+            case 18: return pair_kernel<18, KIND, 1>;
+            case 22: return pair_kernel<22, KIND, 1>;
+            case 26: return pair_kernel<26, KIND, 1>;
+            case 30: return pair_kernel<30, KIND, 1>;
+            default: break;
+        }
+    }
     switch (k) {
         case 4: return pair_kernel<4, KIND, 1>;
         case 8: return pair_kernel<8, KIND, 1>;
@@ -713,7 +726,7 @@ int pyopal_end_full_search(pyopal_cuda_db* db, const unsigned char* query, int L
             sum_n += len; nmax = std::max(nmax, len); nlive += (len > 0);
         }
         int Cc = 1;
-        const int K = choose_pair_K(Lq, nlive, sum_n, nmax, njobs, db->sm_count, &Cc);
+        const int K = choose_pair_K(Lq, nlive, sum_n, nmax, njobs, db->sm_count, 2, &Cc);
         pair_kernel_t kloc = (cfg_for_mode(mode).endrule == END_ALL) ? pair_kernel_for<KIND_ALL>(K, Cc)
                                                                       : pair_kernel_for<KIND_EDGE>(K, Cc);
         db->stats[5] = Cc;
@@ -864,7 +877,7 @@ int pyopal_end_full_search(pyopal_cuda_db* db, const unsigned char* query, int L
         int32_t* d_len = db->pd_i32.p;
         int32_t* d_ctl = d_len + nb;
         int Cc = 1;
-        const int K = choose_pair_K(maxm, nb, sum_tn, max_tn, nb, db->sm_count, &Cc);
+        const int K = choose_pair_K(maxm, nb, sum_tn, max_tn, nb, db->sm_count, 4, &Cc);
         pair_kernel_t kfill = pair_kernel_for<KIND_FILL>(K, Cc);
         if (maxm > 32 * K)
             if (db->bnd32H.reserve((size_t)db->ncols * 2 + 16) || db->bnd32F.reserve((size_t)db->ncols * 2 + 16))

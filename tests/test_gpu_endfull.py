@@ -232,11 +232,12 @@ def test_reference_vectors_on_gpu(cuda):
 
 
 @pytest.mark.parametrize("algo", ALGOS)
-@pytest.mark.parametrize("pair_k", ["4", "12", "32", "4x4", "8x4", "8x1"])
+@pytest.mark.parametrize("pair_k", ["4", "10", "12", "22", "32", "4x4", "8x4", "8x1"])
 def test_band_teams_match_oracle(cuda, oracle, monkeypatch, algo, pair_k):
     # pairdp.cu walks a long query as bands of 32 K rows on several warps at once (pass p one chunk of columns
     # behind pass p - 1, results merged by the band that finishes last); the band height is normally picked by a
-    # cost model, here it is forced: 700 rows = 6 bands of K = 4, 2 of K = 12, 1 of K = 32.  Homologs give the
+    # cost model, here it is forced: 700 rows = 6 bands of K = 4, 3 of K = 10,
+    # 2 of K = 12, 1 of K = 22 or 32.  Homologs give the
     # reverse pass something to cut short, and equal scores in different bands exercise the merge order.
     # "KxC": C columns per step (the latency-bound shape takes four)
     k, _, c = pair_k.partition("x")

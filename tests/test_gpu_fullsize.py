@@ -208,7 +208,7 @@ def test_config4_top_hits_end_and_full(full, oracle, cuda, qi, algo):
 
 @pytest.mark.parametrize("qi,algo", [(1, "sw"), (3, "sw"), (3, "hw")])
 def test_whole_database_end_mode(full, oracle, qi, algo):
-    # end mode over all 570k proteins (the throughput shape of pairdp.cu: one pass of K = 12 rows per lane for the
+    # end mode over all 570k proteins (the throughput shape of pairdp.cu: one pass of K = 10 rows per lane for the
     # 300-aa query, two concurrent bands of K = 32 for the 2000-aa one): scores equal the score-mode search
     # everywhere, end cells equal the oracle's on a random subsample plus every planted giant.
     residues, offsets, lengths = full["db"]
