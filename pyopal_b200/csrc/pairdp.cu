@@ -263,20 +263,21 @@ __global__ void __launch_bounds__(128) pair_kernel(const __grid_constant__ PairP
                         int cm = 4 * NEGV;
                         int Gs[C][K];  // KIND_ALL: the columns of this step, for the rare path
                         if (active) {
-                            if (lane == 0) {
-                                if (pass == 0) {
+                            // lane 0 takes the row above the band: the border (evaluated by every lane, so the warp
+                            // does not diverge in the one-band case) or the last row of the band above
+                            if (pass == 0) {
 #pragma unroll
-                                    for (int cc = 0; cc < C; ++cc) {
-                                        upG[cc] = border_val(P.top_free, c0 + cc, go, ge) - go;
-                                        upF[cc] = upG[cc];  // F of the first row: max(-inf, H above - open)
-                                    }
-                                } else {
+                                for (int cc = 0; cc < C; ++cc) {
+                                    const int bg = border_val(P.top_free, c0 + cc, go, ge) - go;
+                                    upG[cc] = (lane == 0) ? bg : upG[cc];
+                                    upF[cc] = (lane == 0) ? bg : upF[cc];  // F of the first row: max(-inf, H above - open)
+                                }
+                            } else if (lane == 0) {
 #pragma unroll
-                                    for (int cc = 0; cc < C; ++cc) {
-                                        const int2 bb = wbnd[C * sl + cc];
-                                        upG[cc] = bb.x;
-                                        upF[cc] = bb.y;
-                                    }
+                                for (int cc = 0; cc < C; ++cc) {
+                                    const int2 bb = wbnd[C * sl + cc];
+                                    upG[cc] = bb.x;
+                                    upF[cc] = bb.y;
                                 }
                             }
 #pragma unroll
