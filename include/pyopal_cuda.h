@@ -41,6 +41,7 @@ extern "C" {
 #define PYOPAL_CUDA_ERR_NOMEM 17    /* host or device allocation failed -> MemoryError */
 #define PYOPAL_CUDA_ERR_ARGUMENT 18 /* NULL / out-of-range argument */
 #define PYOPAL_CUDA_ERR_INTERNAL 19 /* self-check failed (e.g. traceback score mismatch) */
+#define PYOPAL_CUDA_ERR_NCCL 20     /* NCCL missing or a collective failed; see pyopal_cuda_last_error() */
 
 #define OPAL_MODE_NW 0
 #define OPAL_MODE_HW 1
@@ -83,12 +84,20 @@ int opalSearchDatabase(unsigned char query[], int queryLength, unsigned char* db
                        int dbSeqLengths[], int gapOpen, int gapExt, int* scoreMatrix, int alphabetLength,
                        OpalSearchResult* results[], const int searchType, int mode, int overflowMethod);
 
+/* opal.pxd:56-67: Smith-Waterman SCORE search over `char` sequences (declared by the interface PyOpal binds,
+ * never called by it); same staging as opalSearchDatabase. */
+int opalSearchDatabaseCharSW(char query[], int queryLength, char** db, int dbLength, int dbSeqLengths[],
+                             int gapOpen, int gapExt, int* scoreMatrix, int alphabetLength,
+                             OpalSearchResult* results[]);
+
 /* ---- device-resident store (replaces lib.pxd:95-98 for the search) ------ */
 typedef struct pyopal_cuda_db pyopal_cuda_db;
 
 int pyopal_cuda_device_count(void);
 /* name (<= cap bytes), SM count, total memory of `device`. */
 int pyopal_cuda_device_info(int device, char* name, int cap, int* sm_count, int64_t* total_mem);
+/* PCI bus id ("0000:1b:00.0") of `device`: lets a caller find the same GPU in NVML whatever CUDA_VISIBLE_DEVICES says */
+int pyopal_cuda_device_pci_bus_id(int device, char* out, int cap);
 /* thread-local message of the last failing call on this thread */
 const char* pyopal_cuda_last_error(void);
 
@@ -121,8 +130,10 @@ int pyopal_cuda_search(pyopal_cuda_db* db, const unsigned char* query, int query
 
 /* SCORE-mode search whose result stays on the device: `d_scores` is a DEVICE
  * pointer to (end - start) int32.  `stream` is a cudaStream_t (0 = the legacy
- * default stream); the call returns once the work is enqueued on it.  Used by
- * the multi-GPU driver to feed the NCCL gather without a host round trip. */
+ * default stream); the call returns once the work is enqueued on it.  Every
+ * call takes a workspace from the handle's pool; when a workspace is reused
+ * its next search is ordered (by event) after this one, on whatever stream,
+ * so concurrent calls from several threads or streams are safe. */
 int pyopal_cuda_search_scores_device(pyopal_cuda_db* db, const unsigned char* query, int queryLength,
                                      int gapOpen, int gapExt, const int* scoreMatrix, int alphabetLength,
                                      int mode, int64_t start, int64_t end, int32_t* d_scores, void* stream);
@@ -133,6 +144,12 @@ int pyopal_cuda_search_scores_device(pyopal_cuda_db* db, const unsigned char* qu
 int pyopal_cuda_search_batch(pyopal_cuda_db* db, const unsigned char* queries, const int64_t* q_offsets,
                              const int32_t* q_lengths, int nq, int gapOpen, int gapExt,
                              const int* scoreMatrix, int alphabetLength, int mode, int32_t* scores);
+
+/* The same with a device-side top-k per query (topk.cu): scores / indices are HOST buffers of nq * k entries,
+ * row-major by query, each row sorted by score descending, ties by ascending database index; k <= size. */
+int pyopal_cuda_search_batch_topk(pyopal_cuda_db* db, const unsigned char* queries, const int64_t* q_offsets,
+                                  const int32_t* q_lengths, int nq, int gapOpen, int gapExt, const int* scoreMatrix,
+                                  int alphabetLength, int mode, int k, int32_t* scores, int32_t* indices);
 
 /* The k best hits of a SCORE-mode search, selected on the device (topk.cu): `scores` / `indices` are HOST
  * buffers of k entries, filled with min(k, end - start) hits sorted by score descending, ties by ascending
@@ -158,6 +175,66 @@ int pyopal_cuda_topk_device(pyopal_cuda_db* db, const int32_t* d_scores, int64_t
  * tail kernels) / the 16-bit bulk kernel / the 32-bit rescore kernel of the last search (0 until its stream
  * has completed), [11]=1 if the query profile was held in shared memory. */
 int pyopal_cuda_last_stats(const pyopal_cuda_db* db, int64_t* stats, int n);
+
+/* Host helper for packed databases: offsets[i] = sum of lengths[0..i), *total = sum of all (either may be NULL). */
+void pyopal_host_offsets_from_lengths(const int32_t* lengths, int64_t n, int64_t* offsets, int64_t* total);
+
+/* ---- one database over several GPUs (multi.cu) ---------------------------------------------------------
+ * Replaces the ThreadPool fan-out of src/pyopal/_align.py:145-172: the database is dealt to the GPUs by
+ * cumulative cells (length-sorted, snake order), every GPU searches its shard, the per-shard score arrays are
+ * exchanged with ONE ncclAllGather over NVLink and un-permuted to database order on the device.  NCCL is bound
+ * at run time (dlopen libnccl.so.2; PYOPAL_NCCL_LIB or pyopal_cuda_nccl_load() name another copy). */
+typedef struct pyopal_cuda_mdb pyopal_cuda_mdb;
+
+int pyopal_cuda_nccl_load(const char* path);          /* optional: bind this libnccl instead of the default one */
+int pyopal_cuda_nccl_version(void);                   /* e.g. 22809, 0 if NCCL cannot be loaded */
+int pyopal_cuda_nccl_unique_id(unsigned char id[128]); /* ncclGetUniqueId: rank 0 creates it, the caller distributes it */
+
+/* owner[i] = rank of target i under the cell-balanced snake deal (pure host code). */
+int pyopal_cuda_deal(const int32_t* lengths, int64_t n, int world, int32_t* owner);
+
+/* ONE process driving `ndev` devices (ncclCommInitAll, one host thread per device): what Aligner.align uses. */
+int pyopal_cuda_mdb_create(const int* devices, int ndev, const unsigned char* residues, const int64_t* offsets,
+                           const int32_t* lengths, int64_t n, int alphabetLength, pyopal_cuda_mdb** out);
+/* One process PER GPU (ncclCommInitRank): this process is `rank` of `world` and brings its own shard, whose
+ * targets have the (ascending) database indices `global_index` (NULL with world 1: the identity).  Collective. */
+int pyopal_cuda_mdb_create_rank(int device, int rank, int world, const unsigned char nccl_id[128],
+                                const unsigned char* residues, const int64_t* offsets, const int32_t* lengths,
+                                int64_t n_local, const int32_t* global_index, int64_t n_all, int alphabetLength,
+                                pyopal_cuda_mdb** out);
+/* The same when every rank holds the whole packed database on the host: the deal is computed inside. */
+int pyopal_cuda_mdb_create_rank_dealt(int device, int rank, int world, const unsigned char nccl_id[128],
+                                      const unsigned char* residues, const int64_t* offsets, const int32_t* lengths,
+                                      int64_t n, int alphabetLength, pyopal_cuda_mdb** out);
+void pyopal_cuda_mdb_destroy(pyopal_cuda_mdb* m);
+int64_t pyopal_cuda_mdb_size(const pyopal_cuda_mdb* m);
+int pyopal_cuda_mdb_world(const pyopal_cuda_mdb* m);
+int pyopal_cuda_mdb_local_ranks(const pyopal_cuda_mdb* m);
+int64_t pyopal_cuda_mdb_local_size(const pyopal_cuda_mdb* m, int local_rank);
+int64_t pyopal_cuda_mdb_local_residues(const pyopal_cuda_mdb* m, int local_rank);
+pyopal_cuda_db* pyopal_cuda_mdb_shard(pyopal_cuda_mdb* m, int local_rank); /* borrowed: statistics only */
+
+/* pyopal_cuda_search over all GPUs: host outputs in database order (on the first local rank's process).
+ * SCORE goes through the NCCL gather; END / ALIGNMENT need a single-process handle (per-target results, no
+ * exchange).  In the one-process-per-GPU layout every rank must make the same call. */
+int pyopal_cuda_mdb_search(pyopal_cuda_mdb* m, const unsigned char* query, int queryLength, int gapOpen, int gapExt,
+                           const int* scoreMatrix, int alphabetLength, int searchType, int mode, int overflowMethod,
+                           int64_t start, int64_t end, int32_t* scores, int32_t* endQ, int32_t* endT, int32_t* startQ,
+                           int32_t* startT, unsigned char* ops, const int64_t* ops_offsets, int32_t* ops_len);
+/* Batched SCORE search, two queries in flight per GPU: scores = HOST nq * (end - start) int32 (row-major by query)
+ * or NULL to leave the results on the devices (timing). */
+int pyopal_cuda_mdb_search_batch(pyopal_cuda_mdb* m, const unsigned char* queries, const int64_t* q_offsets,
+                                 const int32_t* q_lengths, int nq, int gapOpen, int gapExt, const int* scoreMatrix,
+                                 int alphabetLength, int mode, int64_t start, int64_t end, int32_t* scores);
+/* The same with a device-side top-k per query over the gathered scores: HOST nq * k (score, index) rows. */
+int pyopal_cuda_mdb_search_batch_topk(pyopal_cuda_mdb* m, const unsigned char* queries, const int64_t* q_offsets,
+                                      const int32_t* q_lengths, int nq, int gapOpen, int gapExt, const int* scoreMatrix,
+                                      int alphabetLength, int mode, int k, int32_t* scores, int32_t* indices);
+/* Device-side clock (CUDA events on the handle's own streams) around a sequence of calls; end() returns the
+ * longest elapsed time over this process's GPUs, in milliseconds. */
+int pyopal_cuda_mdb_time_begin(pyopal_cuda_mdb* m);
+int pyopal_cuda_mdb_time_end(pyopal_cuda_mdb* m, double* ms);
+int64_t pyopal_cuda_mdb_last_launches(const pyopal_cuda_mdb* m); /* kernels + collectives of the last call, this process */
 
 /* Integer-ALU issue microbenchmark used for the cell-update roofline
  * (SURVEY.md 8(d)): runs the six-instruction 16-bit cell mix dependency-free

@@ -14,7 +14,7 @@ from .lib import (
     FullResult,
 )
 from .matrices import ScoringMatrix
-from ._align import align
+from ._align import align, align_batch
 
 __version__ = lib.__version__
 __all__ = [
@@ -27,4 +27,5 @@ __all__ = [
     "FullResult",
     "ScoringMatrix",
     "align",
+    "align_batch",
 ]

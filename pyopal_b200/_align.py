@@ -1,11 +1,18 @@
 """``pyopal.align`` for the B200 backend (reference: /root/reference/src/pyopal/_align.py)."""
 
-import contextlib
-import functools
-import multiprocessing.pool
-
 from .lib import Aligner, BaseDatabase, Database
 from .matrices import ScoringMatrix, as_scoring_matrix
+
+
+def _resolve_matrix(scoring_matrix):
+    if scoring_matrix is None:
+        return Aligner._DEFAULT_SCORING_MATRIX
+    if isinstance(scoring_matrix, str):
+        return ScoringMatrix.from_name(scoring_matrix)
+    if as_scoring_matrix(scoring_matrix) is None:
+        ty = type(scoring_matrix).__name__
+        raise TypeError(f"expected str or ScoringMatrix, got {ty}")
+    return as_scoring_matrix(scoring_matrix)
 
 
 def align(
@@ -24,13 +31,15 @@ def align(
 ):
     """Align the query sequence to every database sequence in parallel.
 
-    Same signature and results as the reference (_align.py:28-172).  The
-    parallelism is the GPU's: ``threads=0`` (the default) issues ONE search
-    over the whole database, which the device spreads over its SMs; a
-    positive ``threads`` keeps the reference behaviour of cutting the
-    database in ``threads`` contiguous chunks dispatched from a thread pool
-    (_align.py:145-172) -- the chunks then serialise on the device, so it only
-    exists for drop-in compatibility.
+    Same signature and results as the reference (_align.py:28-172), whose
+    parallelism is a thread pool over ``threads`` contiguous chunks of equal
+    sequence count.  Here the fan-out happens below the C-ABI: the database
+    store is dealt to every visible GPU by cumulative cell count
+    (csrc/multi.cu; ``PYOPAL_CUDA_DEVICES`` restricts the devices), each GPU
+    scores its shard with one host thread and the shards' results come back in
+    database order.  ``threads`` and ``pool`` are therefore accepted for
+    compatibility and do not change how the search is dispatched, and the
+    hits always arrive in database order (what ``ordered=True`` asks for).
 
     Example:
         >>> targets = ["AACCGCTG", "ATGCGCT", "TTATTACG"]
@@ -41,40 +50,29 @@ def align(
         23 TTATTACG
 
     """
-    if threads == 0:
-        threads = 1
-    if scoring_matrix is None:
-        scoring_matrix = Aligner._DEFAULT_SCORING_MATRIX
-    elif isinstance(scoring_matrix, str):
-        scoring_matrix = ScoringMatrix.from_name(scoring_matrix)
-    elif as_scoring_matrix(scoring_matrix) is None:
-        ty = type(scoring_matrix).__name__
-        raise TypeError(f"expected str or ScoringMatrix, got {ty}")
+    if threads < 0:
+        raise ValueError(f"invalid thread count: {threads!r}")
+    scoring_matrix = _resolve_matrix(scoring_matrix)
     if not isinstance(database, BaseDatabase):
         database = Database(database, scoring_matrix.alphabet)
-
-    # avoid using more threads than necessary
-    if threads > len(database):
-        threads = len(database) or 1
-
     aligner = Aligner(scoring_matrix, gap_open=gap_open, gap_extend=gap_extend)
-    if threads == 1:
-        yield from aligner.align(query, database, mode=mode, overflow=overflow, algorithm=algorithm)
+    yield from aligner.align(query, database, mode=mode, overflow=overflow, algorithm=algorithm)
+
+
+def align_batch(queries, database, scoring_matrix=None, *, gap_open=3, gap_extend=1, algorithm="sw", k=None):
+    """Score several queries against the database in one device-side pipeline (additive).
+
+    The reference's pattern for many queries is a ``ThreadPool`` over `Aligner.align` calls
+    (/root/reference/README.md:116-144); here the queries go down in ONE call, two searches are in flight per
+    GPU at any time and nothing waits on the host in between.  Yields, per query and in order, an ``array('i')``
+    of scores in database order -- or, with ``k``, the list of the ``k`` best `ScoreResult` (selected on the
+    device; score descending, ties by target index).
+    """
+    scoring_matrix = _resolve_matrix(scoring_matrix)
+    if not isinstance(database, BaseDatabase):
+        database = Database(database, scoring_matrix.alphabet)
+    aligner = Aligner(scoring_matrix, gap_open=gap_open, gap_extend=gap_extend)
+    if k is None:
+        yield from aligner.align_batch(list(queries), database, algorithm=algorithm)
     else:
-        if pool is None:
-            pool_context = multiprocessing.pool.ThreadPool(threads)
-        else:
-            pool_context = contextlib.nullcontext(pool)
-        # cut the database in chunks of similar length
-        chunk_length = len(database) // threads
-        with pool_context as pool:
-            _align = functools.partial(
-                aligner.align, query, database, mode=mode, overflow=overflow, algorithm=algorithm
-            )
-            mapper = pool.imap if ordered else pool.imap_unordered
-            chunk_hits = mapper(
-                lambda x: _align(start=x, end=x + chunk_length),
-                range(0, len(database), chunk_length),
-            )
-            for hits in chunk_hits:
-                yield from hits
+        yield from aligner.align_batch_topk(list(queries), database, k, algorithm=algorithm)

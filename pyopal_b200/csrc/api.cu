@@ -73,30 +73,23 @@ int pyopal_cuda_device_info(int device, char* name, int cap, int* sm_count, int6
     return 0;
 }
 
+int pyopal_cuda_device_pci_bus_id(int device, char* out, int cap) {
+    if (!out || cap < 16) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "buffer too small");
+    CU(cudaDeviceGetPCIBusId(out, cap, device));
+    return 0;
+}
+
 void pyopal_cuda_db_destroy(pyopal_cuda_db* db) {
     if (!db) return;
-    cudaSetDevice(db->device);
+    DeviceGuard guard(db->device);
+    cudaDeviceSynchronize();
+    cudaGetLastError();
     cudaFree(db->d_stream);
     cudaFree(db->d_pair_off);
     cudaFree(db->d_pair_len);
     cudaFree(db->d_pair_idx);
     cudaFree(db->d_identity);
-    cudaFree(db->d_matrix);
-    cudaFree(db->d_counts);
-    db->wl16.release(); db->wl32.release(); db->ovf.release(); db->out.release(); db->fixes.release();
-    db->query.release(); db->gprofile.release(); db->wprofile.release();
-    db->bndH.release(); db->bndF.release(); db->bnd32H.release(); db->bnd32F.release();
-    db->pd_i32.release(); db->pd_tb.release(); db->pd_ops.release(); db->pd_bnd.release(); db->pd_jobs.release(); db->pd_team.release();
-    db->tk_ws.release(); db->tk_vals.release(); db->tk_idx.release();
-    if (db->ev_fork) cudaEventDestroy(db->ev_fork);
-    if (db->ev_join) cudaEventDestroy(db->ev_join);
-    if (db->side) cudaStreamDestroy(db->side);
-    if (db->side2) cudaStreamDestroy(db->side2);
-    if (db->ev_join2) cudaEventDestroy(db->ev_join2);
-    for (int i = 0; i < 6; i++) if (db->kev[i]) cudaEventDestroy(db->kev[i]);
-    if (db->ev0) cudaEventDestroy(db->ev0);
-    if (db->ev1) cudaEventDestroy(db->ev1);
-    if (db->stream) cudaStreamDestroy(db->stream);
+    for (auto& ws : db->pool) ws->destroy();
     delete db;
 }
 
@@ -109,35 +102,181 @@ int64_t pyopal_cuda_db_device_bytes(const pyopal_cuda_db* db) {
 
 int pyopal_cuda_last_stats(const pyopal_cuda_db* db, int64_t* stats, int n) {
     if (!db || !stats) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null argument");
-    // resolve the per-kernel events of the last search if they have completed
     pyopal_cuda_db* m = const_cast<pyopal_cuda_db*>(db);
-    for (int k = 0; k < 3; k++) {
-        m->stats[8 + k] = 0;
-        if (m->kev_valid[k] && cudaEventQuery(m->kev[2 * k + 1]) == cudaSuccess) {
-            float ms = 0;
-            if (cudaEventElapsedTime(&ms, m->kev[2 * k], m->kev[2 * k + 1]) == cudaSuccess)
-                m->stats[8 + k] = (int64_t)(ms * 1000.0f + 0.5f);
+    std::lock_guard<std::mutex> lock(m->mu);
+    // resolve the per-kernel events of the last search if they have completed
+    if (Workspace* ws = m->last_ws) {
+        DeviceGuard guard(db->device);
+        for (int k = 0; k < 3; k++) {
+            m->last_stats[8 + k] = 0;
+            if (ws->kev_valid[k] && cudaEventQuery(ws->kev[2 * k + 1]) == cudaSuccess) {
+                float ms = 0;
+                if (cudaEventElapsedTime(&ms, ws->kev[2 * k], ws->kev[2 * k + 1]) == cudaSuccess)
+                    m->last_stats[8 + k] = (int64_t)(ms * 1000.0f + 0.5f);
+            }
         }
+        cudaGetLastError();
     }
-    cudaGetLastError();
-    for (int i = 0; i < n && i < 12; i++) stats[i] = db->stats[i];
+    for (int i = 0; i < n && i < 12; i++) stats[i] = m->last_stats[i];
     return 0;
+}
+
+void pyopal_host_offsets_from_lengths(const int32_t* lengths, int64_t n, int64_t* offsets, int64_t* total) {
+    int64_t t = 0;
+    for (int64_t i = 0; i < n; i++) {
+        if (offsets) offsets[i] = t;
+        t += lengths[i] > 0 ? lengths[i] : 0;
+    }
+    if (total) *total = t;
 }
 
 }  // extern "C"
 
 // ---------------------------------------------------------------------------
-// Store construction: sort by length (descending, ties by index), pair
-// neighbours, interleave each pair's residues into one u16 stream.
-template <typename GetSeq>
-static int db_build(int device, GetSeq get_seq, const int32_t* lengths, int64_t n, int A,
-                    pyopal_cuda_db** out) {
+// Tuning switches, workspaces
+
+void Tuning::load() {
+    if (const char* ov = getenv("PYOPAL_CUDA_PLAN")) {  // "logG,K[,threads]"
+        int lg = 0, k = 0, t = 0;
+        const int got = sscanf(ov, "%d,%d,%d", &lg, &k, &t);
+        if (got >= 2 && lg >= 2 && lg <= 5 && k >= 4 && k <= 40 && k % 4 == 0) {
+            has_plan = true; plan_logG = lg; plan_K = k;
+            if (got == 3 && t >= 32 && t <= 512 && t % 32 == 0) plan_threads = t;
+        }
+    }
+    no_giant = getenv("PYOPAL_CUDA_NO_GIANT") != nullptr;
+    no_tgiant = getenv("PYOPAL_CUDA_NO_TGIANT") != nullptr;
+    no_tail = getenv("PYOPAL_CUDA_NO_TAIL") != nullptr;
+    no_end16 = getenv("PYOPAL_CUDA_NO_END16") != nullptr;
+    no_mid = getenv("PYOPAL_CUDA_NO_MID") != nullptr;
+    debug = getenv("PYOPAL_CUDA_DEBUG") != nullptr;
+    if (const char* ov = getenv("PYOPAL_CUDA_TGIANT")) {  // "warps,K[,split]"
+        int a = 0, b = 0, c = -1;
+        const int got = sscanf(ov, "%d,%d,%d", &a, &b, &c);
+        has_tgiant = true;
+        if (got >= 2 && a >= 1 && a <= 8 && (b == 16 || b == 32)) { tg_warps = a; tg_K = b; }
+        if (got == 3 && c >= 0) tg_split = c;
+    }
+    if (const char* v = getenv("PYOPAL_CUDA_SOLO")) solo = atof(v);
+    if (const char* v = getenv("PYOPAL_CUDA_GMUL")) gmul = atof(v);
+    if (const char* v = getenv("PYOPAL_CUDA_MID")) mid = atof(v);
+    if (const char* v = getenv("PYOPAL_CUDA_PAIR_K")) pair_k = atoi(v);
+    if (const char* v = getenv("PYOPAL_CUDA_PAIR_C")) pair_c = atoi(v);
+}
+
+int Workspace::init(int dev) {
+    device = dev;
+    CU(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    // the side streams carry the longest targets: highest priority so their CTAs are placed first
+    int lo_prio = 0, hi_prio = 0;
+    CU(cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio));
+    CU(cudaStreamCreateWithPriority(&side, cudaStreamNonBlocking, hi_prio));
+    CU(cudaStreamCreateWithPriority(&side2, cudaStreamNonBlocking, hi_prio));
+    CU(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&ev_join2, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&ev_free, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&ev_aux0, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&ev_aux1, cudaEventDisableTiming));
+    CU(cudaEventCreate(&ev0));
+    CU(cudaEventCreate(&ev1));
+    for (int i = 0; i < 6; i++) CU(cudaEventCreate(&kev[i]));
+    for (int i = 0; i < NPARAM; i++) CU(cudaEventCreateWithFlags(&par_done[i], cudaEventDisableTiming));
+    return 0;
+}
+
+void Workspace::destroy() {
+    ovf.release(); out.release(); gprofile.release(); wprofile.release(); end_out.release();
+    bndH.release(); bndF.release(); bnd32H.release(); bnd32F.release();
+    pd_i32.release(); pd_tb.release(); pd_ops.release(); pd_jobs.release(); pd_team.release(); pd_query.release();
+    tk_ws.release(); tk_vals.release(); tk_idx.release();
+    d_par.release();
+    for (int i = 0; i < NPARAM; i++) { h_par[i].release(); if (par_done[i]) cudaEventDestroy(par_done[i]); par_done[i] = nullptr; }
+    for (cudaEvent_t* e : {&ev_fork, &ev_join, &ev_join2, &ev_free, &ev_aux0, &ev_aux1, &ev0, &ev1}) { if (*e) cudaEventDestroy(*e); *e = nullptr; }
+    for (int i = 0; i < 6; i++) { if (kev[i]) cudaEventDestroy(kev[i]); kev[i] = nullptr; }
+    for (cudaStream_t* s : {&side, &side2, &stream}) { if (*s) cudaStreamDestroy(*s); *s = nullptr; }
+}
+
+Workspace* pyopal_cuda_db::acquire() {
+    std::unique_lock<std::mutex> lock(mu);
+    for (;;) {
+        if (!free_ws.empty()) {
+            Workspace* ws = free_ws.back();
+            free_ws.pop_back();
+            return ws;
+        }
+        if ((int)pool.size() < max_ws) {
+            std::unique_ptr<Workspace> ws(new (std::nothrow) Workspace());
+            if (!ws) { fail(PYOPAL_CUDA_ERR_NOMEM, "host allocation failed"); return nullptr; }
+            DeviceGuard guard(device);
+            if (ws->init(device)) { ws->destroy(); return nullptr; }
+            pool.push_back(std::move(ws));
+            return pool.back().get();
+        }
+        cv.wait(lock);
+    }
+}
+
+void pyopal_cuda_db::release(Workspace* ws) {
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        for (int i = 0; i < 12; i++) last_stats[i] = ws->stats[i];
+        last_ws = ws;
+        free_ws.push_back(ws);
+    }
+    cv.notify_one();
+}
+
+// ---------------------------------------------------------------------------
+// Store construction: sort by length (descending, ties by index), pair neighbours, upload the raw residues once
+// and interleave each pair's residues into one u16 stream ON THE DEVICE.
+
+namespace {
+
+// One warp per pair: column c of pair k = a[c] | b[c] << 8 (padding letter A past the end of the shorter target
+// and up to the 16-byte boundary).  Also checks that every residue indexes the profile (< A).
+__global__ void interleave_kernel(const unsigned char* __restrict__ raw, const int64_t* __restrict__ src_off,
+                                  const int64_t* __restrict__ pair_off, const int32_t* __restrict__ pair_len,
+                                  int64_t npairs, int A, uint16_t* __restrict__ stream, int* bad) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    unsigned any_bad = 0;
+    for (int64_t k = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; k < npairs; k += warps) {
+        const int la = pair_len[2 * k], lb = pair_len[2 * k + 1];
+        const unsigned char* a = raw + src_off[2 * k];
+        const unsigned char* b = lb > 0 ? raw + src_off[2 * k + 1] : nullptr;
+        uint16_t* dst = stream + pair_off[k];
+        const int padded = (la + PAD_ALIGN_COLS - 1) / PAD_ALIGN_COLS * PAD_ALIGN_COLS;
+        for (int c = lane; c < padded; c += 32) {
+            unsigned ra = (c < la) ? a[c] : (unsigned)A;
+            unsigned rb = (c < lb) ? b[c] : (unsigned)A;
+            any_bad |= (unsigned)(c < la && ra >= (unsigned)A) | (unsigned)(c < lb && rb >= (unsigned)A);
+            dst[c] = (uint16_t)(ra | (rb << 8));
+        }
+    }
+    if (any_bad) atomicOr(bad, 1);
+}
+
+__global__ void iota_kernel(int32_t* p, int64_t n) {
+    for (int64_t x = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; x < n; x += (int64_t)gridDim.x * blockDim.x) p[x] = (int32_t)x;
+}
+
+}  // namespace
+
+int pyopal::db_build_from(int device, const unsigned char* residues, const int64_t* offsets,
+                          const unsigned char* const* pointers, const int32_t* index, const int32_t* lengths, int64_t n,
+                          int A, pyopal_cuda_db** out) {
     if (!out) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null output handle");
     *out = nullptr;
     if (n < 0 || n > INT32_MAX) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "database size out of range");
     if (A < 1 || A > 32) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "alphabet length must be in 1..32");
     if (pyopal_cuda_device_count() <= 0) return fail(OPAL_ERR_NO_SIMD_SUPPORT, "no CUDA device available");
-    CU(cudaSetDevice(device));
+    DeviceGuard dguard(device);
+    {
+        int cur = -1;
+        CU(cudaGetDevice(&cur));
+        if (cur != device) CU(cudaSetDevice(device));
+    }
     pyopal_cuda_db* db = new (std::nothrow) pyopal_cuda_db();
     if (!db) return fail(PYOPAL_CUDA_ERR_NOMEM, "host allocation failed");
     struct Guard {
@@ -147,120 +286,58 @@ static int db_build(int device, GetSeq get_seq, const int32_t* lengths, int64_t 
     db->device = device;
     db->A = A;
     db->n = n;
+    db->tune.load();
     cudaDeviceProp prop;
     CU(cudaGetDeviceProperties(&prop, device));
     db->sm_count = prop.multiProcessorCount;
+    CU(cudaDeviceGetAttribute(&db->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
 
+    // ---- sort by length, descending, ties by index: counting sort (lengths are small integers) ----
     db->h_lengths.assign(lengths, lengths + n);
-    std::vector<int32_t> order;
-    order.reserve((size_t)n);
+    int32_t maxlen = 0;
+    int64_t m = 0;
     for (int64_t i = 0; i < n; i++) {
         if (lengths[i] < 0) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "negative sequence length");
         db->total_len += lengths[i];
+        maxlen = std::max(maxlen, lengths[i]);
         if (lengths[i] == 0) db->h_zero_idx.push_back((int32_t)i);
-        else order.push_back((int32_t)i);
+        else m++;
     }
-    std::stable_sort(order.begin(), order.end(),
-                     [&](int32_t a, int32_t b) { return lengths[a] > lengths[b]; });
-    const int64_t m = (int64_t)order.size();
+    std::vector<int32_t> order((size_t)m);
+    if ((int64_t)maxlen <= std::max<int64_t>(4 * n, (int64_t)1 << 20)) {
+        std::vector<int64_t> first((size_t)maxlen + 2, 0);
+        for (int64_t i = 0; i < n; i++) first[(size_t)lengths[i]]++;
+        int64_t pos = 0;
+        for (int64_t l = maxlen; l >= 1; l--) { const int64_t c = first[(size_t)l]; first[(size_t)l] = pos; pos += c; }
+        for (int64_t i = 0; i < n; i++)
+            if (lengths[i] > 0) order[(size_t)first[(size_t)lengths[i]]++] = (int32_t)i;
+    } else {
+        int64_t w = 0;
+        for (int64_t i = 0; i < n; i++) if (lengths[i] > 0) order[(size_t)w++] = (int32_t)i;
+        std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) { return lengths[a] > lengths[b]; });
+    }
     const int64_t npairs = (m + 1) / 2;
     db->npairs = npairs;
     db->h_pair_off.resize((size_t)npairs);
     db->h_pair_len.resize((size_t)npairs * 2);
     db->h_pair_idx.resize((size_t)npairs * 2);
+    db->h_where.assign((size_t)n, -1);
     int64_t ncols = 0;
     for (int64_t k = 0; k < npairs; k++) {
-        int32_t a = order[(size_t)(2 * k)];
-        int32_t b = (2 * k + 1 < m) ? order[(size_t)(2 * k + 1)] : -1;
+        const int32_t a = order[(size_t)(2 * k)];
+        const int32_t b = (2 * k + 1 < m) ? order[(size_t)(2 * k + 1)] : -1;
         db->h_pair_off[(size_t)k] = ncols;
         db->h_pair_len[(size_t)(2 * k)] = lengths[a];
         db->h_pair_len[(size_t)(2 * k + 1)] = b >= 0 ? lengths[b] : 0;
         db->h_pair_idx[(size_t)(2 * k)] = a;
         db->h_pair_idx[(size_t)(2 * k + 1)] = b;
+        db->h_where[(size_t)a] = (int32_t)(2 * k);
+        if (b >= 0) db->h_where[(size_t)b] = (int32_t)(2 * k + 1);
         ncols += ((int64_t)lengths[a] + PAD_ALIGN_COLS - 1) / PAD_ALIGN_COLS * PAD_ALIGN_COLS;
     }
     db->ncols = ncols;
     db->mean_cols = npairs ? (double)ncols / (double)npairs : 0.0;
 
-    // interleave on the host into a pinned staging buffer, chunk by chunk
-    if (ncols > 0) {
-        CU(cudaMalloc(&db->d_stream, (size_t)ncols * sizeof(uint16_t)));
-        const size_t CHUNK = (size_t)16 << 20;  // columns per staging chunk
-        uint16_t* stage = nullptr;
-        size_t stage_cols = std::min<size_t>(CHUNK, (size_t)ncols);
-        // a pair never straddles chunks: grow the staging buffer to the longest pair
-        int64_t longest = ((int64_t)db->h_pair_len[0] + PAD_ALIGN_COLS - 1) / PAD_ALIGN_COLS * PAD_ALIGN_COLS;
-        stage_cols = std::max<size_t>(stage_cols, (size_t)longest);
-        CU(cudaMallocHost(&stage, stage_cols * sizeof(uint16_t)));
-        const uint16_t PADPAIR = (uint16_t)(A | (A << 8));
-        int64_t k = 0;
-        int rc = 0;
-        while (k < npairs && rc == 0) {
-            const int64_t base = db->h_pair_off[(size_t)k];
-            int64_t k2 = k;
-            while (k2 < npairs) {
-                int64_t endc = (k2 + 1 < npairs) ? db->h_pair_off[(size_t)(k2 + 1)] : ncols;
-                if ((size_t)(endc - base) > stage_cols) break;
-                k2++;
-            }
-            const int64_t endc = (k2 < npairs) ? db->h_pair_off[(size_t)k2] : ncols;
-            // interleave the pairs of this chunk on several host threads (205 MB of residues for config 2)
-            std::atomic<unsigned> bad_any{0};
-            auto fill = [&](int64_t q0, int64_t q1) {
-                unsigned bad = 0;  // residues must index the profile: < A
-                for (int64_t q = q0; q < q1; q++) {
-                    uint16_t* dst = stage + (db->h_pair_off[(size_t)q] - base);
-                    const int la = db->h_pair_len[(size_t)(2 * q)], lb = db->h_pair_len[(size_t)(2 * q + 1)];
-                    const unsigned char* sa = get_seq(db->h_pair_idx[(size_t)(2 * q)]);
-                    const unsigned char* sb = lb > 0 ? get_seq(db->h_pair_idx[(size_t)(2 * q + 1)]) : nullptr;
-                    int c = 0;
-                    for (; c < lb; c++) {
-                        bad |= (unsigned)(sa[c] >= A) | (unsigned)(sb[c] >= A);
-                        dst[c] = (uint16_t)(sa[c] | (sb[c] << 8));
-                    }
-                    for (; c < la; c++) {
-                        bad |= (unsigned)(sa[c] >= A);
-                        dst[c] = (uint16_t)(sa[c] | (A << 8));
-                    }
-                    const int padded = (la + PAD_ALIGN_COLS - 1) / PAD_ALIGN_COLS * PAD_ALIGN_COLS;
-                    for (; c < padded; c++) dst[c] = PADPAIR;
-                }
-                if (bad) bad_any.store(1);
-            };
-            {
-                const int64_t npq = k2 - k;
-                unsigned nth = std::min<unsigned>(16u, std::max(1u, std::thread::hardware_concurrency()));
-                if ((endc - base) < ((int64_t)1 << 20)) nth = 1;
-                if (nth <= 1) {
-                    fill(k, k2);
-                } else {
-                    // pairs are sorted by length: deal contiguous ranges of about equal column count
-                    std::vector<std::thread> pool;
-                    int64_t q0 = k;
-                    for (unsigned t = 0; t < nth && q0 < k2; t++) {
-                        const int64_t want = base + (endc - base) * (int64_t)(t + 1) / nth;
-                        int64_t q1 = (t + 1 == nth) ? k2
-                                                    : std::upper_bound(db->h_pair_off.begin() + q0, db->h_pair_off.begin() + k2, want) -
-                                                          db->h_pair_off.begin();
-                        q1 = std::max(q1, q0 + (t + 1 == nth ? 0 : 1));
-                        q1 = std::min(q1, k2);
-                        pool.emplace_back(fill, q0, q1);
-                        q0 = q1;
-                    }
-                    if (q0 < k2) fill(q0, k2);
-                    for (auto& th : pool) th.join();
-                }
-                (void)npq;
-            }
-            if (bad_any.load()) rc = fail(PYOPAL_CUDA_ERR_ARGUMENT, "residue code outside the alphabet");
-            cudaError_t e = cudaMemcpy(db->d_stream + base, stage, (size_t)(endc - base) * sizeof(uint16_t),
-                                       cudaMemcpyHostToDevice);
-            if (e != cudaSuccess) rc = fail(PYOPAL_CUDA_ERR_CUDA, std::string("stream upload: ") + cudaGetErrorString(e));
-            k = k2;
-        }
-        cudaFreeHost(stage);
-        if (rc) return rc;
-    }
     if (npairs > 0) {
         CU(cudaMalloc(&db->d_pair_off, (size_t)npairs * sizeof(int64_t)));
         CU(cudaMalloc(&db->d_pair_len, (size_t)npairs * 2 * sizeof(int32_t)));
@@ -269,26 +346,92 @@ static int db_build(int device, GetSeq get_seq, const int32_t* lengths, int64_t 
         CU(cudaMemcpy(db->d_pair_off, db->h_pair_off.data(), (size_t)npairs * sizeof(int64_t), cudaMemcpyHostToDevice));
         CU(cudaMemcpy(db->d_pair_len, db->h_pair_len.data(), (size_t)npairs * 2 * sizeof(int32_t), cudaMemcpyHostToDevice));
         CU(cudaMemcpy(db->d_pair_idx, db->h_pair_idx.data(), (size_t)npairs * 2 * sizeof(int32_t), cudaMemcpyHostToDevice));
-        std::vector<int32_t> ident((size_t)npairs);
-        std::iota(ident.begin(), ident.end(), 0);
-        CU(cudaMemcpy(db->d_identity, ident.data(), (size_t)npairs * sizeof(int32_t), cudaMemcpyHostToDevice));
+        iota_kernel<<<256, 256>>>(db->d_identity, npairs);
+        CU(cudaGetLastError());
     }
-    CU(cudaMalloc(&db->d_matrix, 32 * 32 * sizeof(int32_t)));
-    CU(cudaMalloc(&db->d_counts, 16 * sizeof(int32_t)));
-    CU(cudaStreamCreateWithFlags(&db->stream, cudaStreamNonBlocking));
-    {
-        // the side stream carries the longest targets: highest priority so its CTAs are placed first
-        int lo_prio = 0, hi_prio = 0;
-        CU(cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio));
-        CU(cudaStreamCreateWithPriority(&db->side, cudaStreamNonBlocking, hi_prio));
-        CU(cudaStreamCreateWithPriority(&db->side2, cudaStreamNonBlocking, hi_prio));
+
+    // ---- raw residues to the device (one copy), interleave there ----
+    if (ncols > 0) {
+        CU(cudaMalloc(&db->d_stream, (size_t)ncols * sizeof(uint16_t)));
+        struct Tmp {
+            unsigned char* raw = nullptr;
+            int64_t* off = nullptr;
+            int* bad = nullptr;
+            unsigned char* stage = nullptr;
+            ~Tmp() { cudaFree(raw); cudaFree(off); cudaFree(bad); if (stage) cudaFreeHost(stage); }
+        } tmp;
+        std::vector<int64_t> src((size_t)npairs * 2, 0);
+        int64_t raw_bytes = 0;
+        auto source = [&](int32_t local) -> int64_t { return index ? (int64_t)index[local] : (int64_t)local; };
+        if (pointers == nullptr) {
+            // packed input: upload the byte range that covers this store's sequences as it lies in host memory
+            int64_t lo = INT64_MAX, hi = 0;
+            for (int64_t x = 0; x < 2 * npairs; x++) {
+                const int32_t i = db->h_pair_idx[(size_t)x];
+                if (i < 0) continue;
+                const int64_t o = offsets[source(i)];
+                lo = std::min(lo, o);
+                hi = std::max(hi, o + lengths[i]);
+            }
+            for (int64_t x = 0; x < 2 * npairs; x++) {
+                const int32_t i = db->h_pair_idx[(size_t)x];
+                src[(size_t)x] = i < 0 ? 0 : offsets[source(i)] - lo;
+            }
+            raw_bytes = hi - lo;
+            CU(cudaMalloc(&tmp.raw, (size_t)raw_bytes));
+            CU(cudaMemcpy(tmp.raw, residues + lo, (size_t)raw_bytes, cudaMemcpyHostToDevice));
+        } else {
+            // per-sequence pointers (the reference's own layout, lib.pxd:90-92): gather into pinned chunks in
+            // sorted order on several host threads, copy chunk by chunk
+            int64_t t = 0;
+            for (int64_t x = 0; x < 2 * npairs; x++) {
+                src[(size_t)x] = t;
+                t += db->h_pair_len[(size_t)x];
+            }
+            raw_bytes = t;
+            CU(cudaMalloc(&tmp.raw, (size_t)std::max<int64_t>(raw_bytes, 1)));
+            const int64_t CHUNK = (int64_t)64 << 20;
+            const int64_t stage_bytes = std::max<int64_t>(std::min(CHUNK, raw_bytes), (int64_t)db->h_pair_len[0]);
+            CU(cudaMallocHost(&tmp.stage, (size_t)std::max<int64_t>(stage_bytes, 1)));
+            int64_t x0 = 0;
+            while (x0 < 2 * npairs) {
+                int64_t x1 = x0;
+                const int64_t base = src[(size_t)x0];
+                while (x1 < 2 * npairs && src[(size_t)x1] + db->h_pair_len[(size_t)x1] - base <= stage_bytes) x1++;
+                const int64_t bytes = (x1 < 2 * npairs ? src[(size_t)x1] : raw_bytes) - base;
+                auto fill = [&](int64_t a, int64_t b) {
+                    for (int64_t x = a; x < b; x++) {
+                        const int32_t i = db->h_pair_idx[(size_t)x];
+                        if (i < 0) continue;
+                        memcpy(tmp.stage + (src[(size_t)x] - base), pointers[source(i)], (size_t)db->h_pair_len[(size_t)x]);
+                    }
+                };
+                unsigned nth = std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency()));
+                if (bytes < ((int64_t)4 << 20)) nth = 1;
+                if (nth <= 1) fill(x0, x1);
+                else {
+                    std::vector<std::thread> pool;
+                    for (unsigned t2 = 0; t2 < nth; t2++)
+                        pool.emplace_back(fill, x0 + (x1 - x0) * t2 / nth, x0 + (x1 - x0) * (t2 + 1) / nth);
+                    for (auto& th : pool) th.join();
+                }
+                CU(cudaMemcpy(tmp.raw + base, tmp.stage, (size_t)bytes, cudaMemcpyHostToDevice));
+                x0 = x1;
+            }
+        }
+        CU(cudaMalloc(&tmp.off, (size_t)npairs * 2 * sizeof(int64_t)));
+        CU(cudaMalloc(&tmp.bad, sizeof(int)));
+        CU(cudaMemset(tmp.bad, 0, sizeof(int)));
+        CU(cudaMemcpy(tmp.off, src.data(), (size_t)npairs * 2 * sizeof(int64_t), cudaMemcpyHostToDevice));
+        const int64_t want_blocks = (npairs + 7) / 8;
+        const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>(want_blocks, (int64_t)db->sm_count * 32));
+        interleave_kernel<<<blocks, 256>>>(tmp.raw, tmp.off, db->d_pair_off, db->d_pair_len, npairs, A, db->d_stream, tmp.bad);
+        CU(cudaGetLastError());
+        int bad = 0;
+        CU(cudaMemcpy(&bad, tmp.bad, sizeof(int), cudaMemcpyDeviceToHost));
+        if (bad) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "residue code outside the alphabet");
     }
-    CU(cudaEventCreateWithFlags(&db->ev_fork, cudaEventDisableTiming));
-    CU(cudaEventCreateWithFlags(&db->ev_join, cudaEventDisableTiming));
-    CU(cudaEventCreateWithFlags(&db->ev_join2, cudaEventDisableTiming));
-    CU(cudaEventCreate(&db->ev0));
-    CU(cudaEventCreate(&db->ev1));
-    for (int i = 0; i < 6; i++) CU(cudaEventCreate(&db->kev[i]));
+    CU(cudaDeviceSynchronize());
     guard.d = nullptr;
     *out = db;
     return 0;
@@ -298,14 +441,15 @@ extern "C" int pyopal_cuda_db_create(int device, const unsigned char* residues, 
                                      const int32_t* lengths, int64_t n, int alphabetLength,
                                      pyopal_cuda_db** out) {
     if (n > 0 && (!residues || !offsets || !lengths)) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null argument");
-    return db_build(device, [&](int32_t i) { return residues + offsets[i]; }, lengths, n, alphabetLength, out);
+    return db_build_from(device, residues, offsets, nullptr, nullptr, lengths, n, alphabetLength, out);
 }
 
 extern "C" int pyopal_cuda_db_create_from_pointers(int device, const unsigned char* const* sequences,
                                                    const int32_t* lengths, int64_t n, int alphabetLength,
                                                    pyopal_cuda_db** out) {
     if (n > 0 && (!sequences || !lengths)) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null argument");
-    return db_build(device, [&](int32_t i) { return sequences[i]; }, lengths, n, alphabetLength, out);
+    static const unsigned char none = 0;
+    return db_build_from(device, &none, nullptr, sequences, nullptr, lengths, n, alphabetLength, out);
 }
 
 // ---------------------------------------------------------------------------
@@ -355,52 +499,92 @@ struct GiantPolicy {
     int64_t kg = 0;         // out: pairs [0, kg) go to the giant kernel
 };
 
-Plan make_plan(int Lq, int A, const pyopal_cuda_db* db, size_t smem_limit, GiantPolicy* gp) {
+// Latency tile for the longer targets: a whole warp per pair and as few rows
+// per thread as one pass allows (the per-step critical path is ~12 cycles per
+// row); with several passes, deep tiles amortise the per-step latency better.
+Plan make_tail_plan(int Lq, int A, size_t smem_limit) {
+    Plan p; p.G = 32; p.logG = 5;
+    p.K = std::min(40, std::max(4, (Lq + 127) / 128 * 4));
+    return finish_plan(p, Lq, A, smem_limit);
+}
+
+// first pair (pairs are sorted by length, descending) whose longer target has at most `len` columns
+int64_t first_pair_at_most(const pyopal_cuda_db* db, double len, int64_t from) {
+    int64_t lo = from, hi = db->npairs;
+    while (lo < hi) {
+        const int64_t mid = (lo + hi) / 2;
+        if ((double)db->h_pair_len[(size_t)(2 * mid)] > len) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+// Tiers.  Pairs are sorted by length; the longest [0, kg) go to the giant kernels, the next [kg, kmid) -- too
+// long to be walked by a narrow group within the time the whole search takes -- to the same 16-bit kernel in
+// its 32-lane tile (`mid`), the rest to the throughput tile.  A wide tile costs the same instructions per
+// cell as a narrow one of the same depth; what it loses is the G - 1 fill steps per pass, which only matter
+// for short pairs -- so the split lets small shards (8 GPUs) keep the narrow tile for the bulk of their cells.
+Plan make_plan(int Lq, int A, const pyopal_cuda_db* db, size_t smem_limit, GiantPolicy* gp, bool allow_mid,
+               int64_t* kmid_out) {
     const double C0 = 28.0, C1 = 6.5;
-    const double mean_cols = db->mean_cols;
+    const Tuning& tune = db->tune;
     Plan best;
     double best_cost = 1e300;
-    int64_t best_kg = 0;
+    int64_t best_kg = 0, best_kmid = 0;
+    const Plan tailp = make_tail_plan(Lq, A, smem_limit);
+    auto cols_of = [&](int64_t k0, int64_t k1) {
+        return (double)((k1 < db->npairs ? db->h_pair_off[(size_t)k1] : db->ncols) - (k0 < db->npairs ? db->h_pair_off[(size_t)k0] : db->ncols));
+    };
     for (int logG = 2; logG <= 5; logG++) {
         const int G = 1 << logG;
         // calibrated on 1/2, 1/4 and 1/8 shards of config 2 (scratch/shard_sweep.py): groups of 8+ lanes reach the
         // critical path about 25 % earlier than 448 / G groups per SM suggest; 4-lane groups do not
-        static const double solo_env = getenv("PYOPAL_CUDA_SOLO") ? atof(getenv("PYOPAL_CUDA_SOLO")) : 0.0;
-        const double solo = solo_env > 0 ? solo_env : (G == 4 ? 448.0 : 560.0);
-        const double L_even = (double)db->ncols * G / (solo * db->sm_count);
+        auto l_even = [&](int g) {
+            const double solo = tune.solo > 0 ? tune.solo : (g == 4 ? 448.0 : 560.0);
+            return (double)db->ncols * g / (solo * db->sm_count);
+        };
+        const bool mid = allow_mid && G < 32;
+        // giants: beyond what the widest tile of this launch can walk in time
+        const double L_top = mid ? l_even(32) : l_even(G);
         int64_t kg = 0;
         double giant_cols = 0;
         if (gp && gp->ok) {
-            const double gthr = std::max(1024.0, 0.6 * L_even);
+            const double gthr = std::max(1024.0, 0.6 * L_top);
             while (kg < gp->cap && kg < db->npairs && (double)db->h_pair_len[(size_t)(2 * kg)] > gthr) {
                 giant_cols += (double)db->h_pair_len[(size_t)(2 * kg)] + (double)db->h_pair_len[(size_t)(2 * kg + 1)];
                 kg++;
             }
         }
         // the giants hold whole SMs at a fraction of the bulk kernel's efficiency
-        const double giant_cost = giant_cols * (gp ? gp->col_cost : 0.0) / std::max<double>(1.0, (double)db->npairs);
-        const double longest_bulk = kg < db->npairs ? (double)db->h_pair_len[(size_t)(2 * kg)] : 0.0;
-        const double stretch = std::max(1.0, longest_bulk / std::max(L_even, 1.0));
+        const double giant_cost = giant_cols * (gp ? gp->col_cost : 0.0);
+        const double midf = tune.mid > 0 ? tune.mid : 0.5;
+        const int64_t kmid = mid ? first_pair_at_most(db, std::max(256.0, midf * l_even(G)), kg) : kg;
+        const double cols_mid = cols_of(kg, kmid), n_mid = (double)(kmid - kg);
+        const double cols_bulk = cols_of(kmid, db->npairs), n_bulk = (double)(db->npairs - kmid);
+        const double longest_bulk = kmid < db->npairs ? (double)db->h_pair_len[(size_t)(2 * kmid)] : 0.0;
+        const double stretch = std::max(1.0, longest_bulk / std::max(l_even(G), 1.0));
+        const double mid_cost = (double)tailp.npass * (cols_mid + 31.0 * n_mid) *
+                                (C0 + (tailp.npass > 1 ? 12.0 : 0.0) + C1 * tailp.K) * 32.0;
         for (int K = 4; K <= 40; K += 4) {
             const int T = G * K;
             const int npass = (Lq + T - 1) / T;
             // several passes also pay the boundary round trip through L2 every step
-            const double cost = stretch * (double)npass * (mean_cols + G - 1) * (C0 + (npass > 1 ? 12.0 : 0.0) + C1 * K) * (double)G +
-                                giant_cost;
+            const double cost = stretch * (double)npass * (cols_bulk + (G - 1) * n_bulk) *
+                                    (C0 + (npass > 1 ? 12.0 : 0.0) + C1 * K) * (double)G +
+                                mid_cost + giant_cost;
             if (cost < best_cost - 1e-9) {
                 best_cost = cost;
                 best.G = G; best.logG = logG; best.K = K; best.npass = npass;
-                best_kg = kg;
+                best_kg = kg; best_kmid = kmid;
             }
         }
     }
-    if (const char* ov = getenv("PYOPAL_CUDA_PLAN")) {  // "logG,K[,threads]": tuning override
-        int lg = 0, k = 0;
-        if (sscanf(ov, "%d,%d", &lg, &k) == 2 && lg >= 2 && lg <= 5 && k >= 4 && k <= 40 && k % 4 == 0) {
-            best.G = 1 << lg; best.logG = lg; best.K = k; best.npass = (Lq + best.G * k - 1) / (best.G * k);
-        }
+    if (tune.has_plan) {  // "logG,K[,threads]": tuning override
+        best.G = 1 << tune.plan_logG; best.logG = tune.plan_logG; best.K = tune.plan_K;
+        best.npass = (Lq + best.G * best.K - 1) / (best.G * best.K);
+        best_kmid = best_kg;
     }
     if (gp) gp->kg = best_kg;
+    if (kmid_out) *kmid_out = best_kmid;
     best = finish_plan(best, Lq, A, smem_limit);
     return best;
 }
@@ -411,15 +595,6 @@ Plan make_forced_plan(int Lq) {
     p.psmem = false; p.smem = 0;
     return p;
 }
-// Latency tile for the longest targets: a whole warp per pair and as few rows
-// per thread as one pass allows (the per-step critical path is ~12 cycles per
-// row); with several passes, deep tiles amortise the per-step latency better.
-Plan make_tail_plan(int Lq, int A, size_t smem_limit) {
-    Plan p; p.G = 32; p.logG = 5;
-    p.K = std::min(40, std::max(4, (Lq + 127) / 128 * 4));
-    return finish_plan(p, Lq, A, smem_limit);
-}
-
 struct Rung {
     bool fits8 = false;       // folded scores fit the int8 profile
     bool ok16 = false;        // the 16-bit rung may be used at all
@@ -480,23 +655,28 @@ __global__ void scatter_fixes_kernel(const int32_t* fixes, int nfix, int32_t* ou
     if (i < nfix) out[fixes[2 * i]] = fixes[2 * i + 1];
 }
 
-search_kernel_t pick_kernel(int K, int W, bool local, bool psmem, bool tdadd = true) {
-    if (W == 16) return local ? get_search_kernel_w16_l1(K, psmem, tdadd) : get_search_kernel_w16_l0(K, psmem, tdadd);
+search_kernel_t pick_kernel(int K, int W, bool local, bool psmem, bool tdadd = true, bool endm = false) {
+    if (W == 16) {
+        if (endm) return local ? get_search_kernel_w16_l1_end(K, psmem, tdadd) : get_search_kernel_w16_l0_end(K, psmem, tdadd);
+        return local ? get_search_kernel_w16_l1(K, psmem, tdadd) : get_search_kernel_w16_l0(K, psmem, tdadd);
+    }
     return local ? get_search_kernel_w32_l1(K, psmem) : get_search_kernel_w32_l0(K, psmem);
 }
 
-int launch_search(pyopal_cuda_db* db, search_kernel_t fn, const KParams& P, size_t smem, int threads,
-                  int64_t max_tasks, cudaStream_t st) {
+int launch_search(pyopal_cuda_db* db, Workspace* ws, search_kernel_t fn, const KParams& P, size_t smem, int threads,
+                  int64_t max_tasks, cudaStream_t st, int64_t grid_cap = 0) {
     CU(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, threads, smem));
     if (per_sm < 1) return fail(PYOPAL_CUDA_ERR_INTERNAL, "kernel does not fit on an SM");
     int64_t grid = (int64_t)db->sm_count * per_sm;
     const int64_t need = (max_tasks + (threads / 32) - 1) / (threads / 32);
-    grid = std::max<int64_t>(1, std::min(grid, need));
+    grid = std::min(grid, need);
+    if (grid_cap > 0) grid = std::min(grid, grid_cap);
+    grid = std::max<int64_t>(1, grid);
     fn<<<(unsigned)grid, threads, smem, st>>>(P);
     CU(cudaGetLastError());
-    db->stats[0]++;
+    ws->stats[0]++;
     return 0;
 }
 
@@ -505,7 +685,15 @@ void apply_plan(KParams& P, const Plan& pl) {
     P.krows = pl.K; P.kstride = pl.kstride;
 }
 
-// Enqueue a SCORE search of [start, end) on `st`; scores land in d_out (device).
+// layout of the per-search parameter block (one pinned host copy -> one H2D)
+constexpr size_t PAR_COUNTS = 0;                  // int32[16]: [0..3] list sizes, [4..7] task counters, [8..11] giants
+constexpr size_t PAR_MATRIX = 64;                 // int32[32 * 32]
+constexpr size_t PAR_LISTS = PAR_MATRIX + 4096;   // work lists, fix-ups, query
+
+}  // namespace
+
+// Enqueue a SCORE search of [start, end) on `st`; scores land in d_out (device).  With `endp` the 16-bit
+// launches also locate the end cell (END mode); targets they cannot hold are returned in endp->spill.
 //
 // Launches (all optional but the bulk):
 //   tgiants: targets longer than one slab of tgiant.cu when the query is short enough for it, 32 bit, one CTA
@@ -513,245 +701,273 @@ void apply_plan(KParams& P, const Plan& pl) {
 //   giants : the other "long" pairs chosen with the tile (make_plan), giant.cu, 32 bit, high-priority side stream
 //   wide32 : 32-bit rung for pairs the 16-bit rung cannot hold exactly (NW/HW/OV static bound, or gap costs /
 //            scores outside its range: then every pair), latency tile, side stream
-//   tail   : 16-bit rung for the longest pairs, one warp per pair, only when no giant kernel can take the query
+//   mid    : 16-bit rung in its 32-lane tile for pairs too long for the narrow groups of the bulk tile, side stream
 //   bulk   : 16-bit rung, throughput tile (make_plan), persistent 224/480-thread CTAs, on `st`
 //   rescue : 32-bit rescore of SW targets whose 16-bit running max overflowed; its work list is produced on the
-//            device by bulk/tail.
-int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq, int go, int ge,
-                         const int* M, int A, int mode, int64_t start, int64_t end, int32_t* d_out,
-                         cudaStream_t st) {
-    for (int i = 0; i < 12; i++) db->stats[i] = 0;
-    db->kev_valid[0] = db->kev_valid[1] = db->kev_valid[2] = false;
+//            device by bulk/mid.
+int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const unsigned char* query, int Lq, int go,
+                                    int ge, const int* M, int A, int mode, int64_t start, int64_t end,
+                                    int32_t* d_out, cudaStream_t st, EndPlan* endp) {
+    for (int i = 0; i < 12; i++) ws->stats[i] = 0;
+    ws->kev_valid[0] = ws->kev_valid[1] = ws->kev_valid[2] = false;
     const int64_t nout = end - start;
     if (nout <= 0) return 0;
     const bool local = (mode == MODE_SW);
+    const bool endm = endp != nullptr;
+    const Tuning& tune = db->tune;
+    if (endm) { endp->spill.clear(); endp->d_ovf = nullptr; endp->d_ovf_count = nullptr; endp->packed = false; }
 
-    // host-side fix-ups: zero-length targets, or everything when the query is empty
+    // a workspace is reused across streams: wait for its previous search, mark the end of this one
+    if (ws->used) CU(cudaStreamWaitEvent(st, ws->ev_free, 0));
+    ws->used = true;
+    struct Mark {
+        Workspace* w; cudaStream_t s;
+        ~Mark() { cudaEventRecord(w->ev_free, s); }
+    } mark{ws, st};
+
+    // host-side fix-ups: zero-length targets, or everything when the query is empty (score mode; the end-mode
+    // caller fills these from closed forms on the host)
     std::vector<int32_t> fixes;
-    if (Lq == 0) {
-        for (int64_t i = start; i < end; i++) {
-            fixes.push_back((int32_t)(i - start));
-            fixes.push_back(degenerate_score(mode, 0, db->h_lengths[(size_t)i], go, ge));
-        }
-    } else {
-        for (int32_t z : db->h_zero_idx)
-            if (z >= start && z < end) {
-                fixes.push_back((int32_t)(z - start));
-                fixes.push_back(degenerate_score(mode, Lq, 0, go, ge));
+    if (!endm) {
+        if (Lq == 0) {
+            for (int64_t i = start; i < end; i++) {
+                fixes.push_back((int32_t)(i - start));
+                fixes.push_back(degenerate_score(mode, 0, db->h_lengths[(size_t)i], go, ge));
             }
+        } else {
+            for (int32_t z : db->h_zero_idx)
+                if (z >= start && z < end) {
+                    fixes.push_back((int32_t)(z - start));
+                    fixes.push_back(degenerate_score(mode, Lq, 0, go, ge));
+                }
+        }
     }
-    auto apply_fixes = [&]() -> int {
-        if (fixes.empty()) return 0;
-        const int nfix = (int)(fixes.size() / 2);
-        if (db->fixes.reserve(fixes.size())) return PYOPAL_CUDA_ERR_NOMEM;
-        CU(cudaMemcpyAsync(db->fixes.p, fixes.data(), fixes.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
-        scatter_fixes_kernel<<<(nfix + 255) / 256, 256, 0, st>>>(db->fixes.p, nfix, d_out);
-        CU(cudaGetLastError());
-        return 0;
-    };
-    if (Lq == 0 || db->npairs == 0) return apply_fixes();
+    const bool device_dp = !(Lq == 0 || db->npairs == 0);
 
     // ---- plans -------------------------------------------------------------
     const size_t SMEM_LIMIT = (size_t)200 * 1024;
-    // giants: the longest targets get a team of warps each (giant.cu), 32 bit; needs the int8
-    // profile of the whole query in shared memory
     GiantPolicy gpol;
     int gK = 4, gwarps = 1, gteams = 1, gpitch = 0;
     size_t gsmem = 0;
-    // gap_extend > gap_open: NW's padding rows need the border fix of the 32-bit kernel (kernels.cuh, BFIX); the
-    // giant kernels do not carry it, so everything stays on search_kernel then
-    const bool bfix = (mode == MODE_NW && ge > go);
-    if (make_rung(M, A, go, ge, mode, 0).fits8 && Lq <= 8192 && !bfix && !getenv("PYOPAL_CUDA_NO_GIANT")) {
-        gK = (Lq <= 2048) ? 4 : (Lq <= 4096) ? 8 : 16;            // rows per lane
-        gwarps = ((Lq + gK - 1) / gK + 31) / 32;                  // warps per team (<= 16): the whole query in one pass
-        gteams = (gwarps == 1) ? 16 : std::min(15, 16 / gwarps);  // teams per 512-thread CTA (15 named barriers)
-        gpitch = (gwarps * 32 * (gK + 4) + 15) / 16 * 16;         // gK = 4, 8, 16 words-even: chunks of gK + 4 bytes
-        gsmem = giant_smem_bytes(A, gpitch, gwarps, gteams);
-        gpol.ok = gsmem <= SMEM_LIMIT + 24 * 1024;
-        gpol.cap = (int64_t)db->sm_count * 8;
-        // one SM clock ~ 56 cost units (calibrated on config 2); a team advances one column in about
-        // 36 clocks per row held by a lane, 1.6 x that when the wavefront crosses warps
-        const int teams_now = (gwarps == 1) ? 16 : std::max(1, 16 / gwarps);
-        static const double gmul = getenv("PYOPAL_CUDA_GMUL") ? atof(getenv("PYOPAL_CUDA_GMUL")) : 1.0;
-        gpol.col_cost = gmul * 56.0 * 36.0 * gK * (gwarps > 1 ? 1.6 : 1.0) / teams_now;
-    }
-    const bool old_giants_ok = gpol.ok;
-    // transposed giants (tgiant.cu): the target over the lanes, the query streamed; needs the short F chain
-    bool use_t = false;
+    bool use_t = false, old_giants_ok = false, bfix = false, wide = false, same_plan = true;
     int tK = 32, tNW = 4, tpitch = 0, tsplit_override = -1;
     size_t tsmem = 0;
-    int smem_optin = 0;
-    CU(cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, db->device));
-    if (make_rung(M, A, go, ge, mode, 0).fits8 && ge <= go && !getenv("PYOPAL_CUDA_NO_TGIANT") &&
-        !getenv("PYOPAL_CUDA_NO_GIANT")) {
-        if (const char* ov = getenv("PYOPAL_CUDA_TGIANT")) {  // "warps,K": tuning override
-            int a = 0, b = 0, c = -1;
-            const int got = sscanf(ov, "%d,%d,%d", &a, &b, &c);
-            if (got >= 2 && a >= 1 && a <= 8 && (b == 16 || b == 32)) { tNW = a; tK = b; }
-            if (got == 3 && c >= 0) tsplit_override = c;
+    const int smem_optin = db->smem_optin;
+    Plan bulk, tail;
+    Rung rung;
+    int64_t kmid = 0, kg = 0, n32p = 0, tail_end = 0;
+    std::vector<int32_t> wl32, wl16, wlg, wlt;
+    int64_t ntail = 0, nbulk = 0, n32 = 0, ng = 0, nt = 0;
+    bool whole = false;
+    if (device_dp) {
+        // giants: the longest targets get a team of warps each (giant.cu), 32 bit; needs the int8
+        // profile of the whole query in shared memory.
+        // gap_extend > gap_open: NW's padding rows need the border fix of the 32-bit kernel (kernels.cuh, BFIX); the
+        // giant kernels do not carry it, so everything stays on search_kernel then
+        bfix = (mode == MODE_NW && ge > go);
+        const bool fits8 = make_rung(M, A, go, ge, mode, 0).fits8;
+        if (fits8 && Lq <= 8192 && !bfix && !tune.no_giant && !endm) {
+            gK = (Lq <= 2048) ? 4 : (Lq <= 4096) ? 8 : 16;            // rows per lane
+            gwarps = ((Lq + gK - 1) / gK + 31) / 32;                  // warps per team (<= 16): the whole query in one pass
+            gteams = (gwarps == 1) ? 16 : std::min(15, 16 / gwarps);  // teams per 512-thread CTA (15 named barriers)
+            gpitch = (gwarps * 32 * (gK + 4) + 15) / 16 * 16;         // gK = 4, 8, 16 words-even: chunks of gK + 4 bytes
+            gsmem = giant_smem_bytes(A, gpitch, gwarps, gteams);
+            gpol.ok = gsmem <= SMEM_LIMIT + 24 * 1024;
+            gpol.cap = (int64_t)db->sm_count * 8;
+            // one SM clock ~ 56 cost units (calibrated on config 2); a team advances one column in about
+            // 36 clocks per row held by a lane, 1.6 x that when the wavefront crosses warps
+            const int teams_now = (gwarps == 1) ? 16 : std::max(1, 16 / gwarps);
+            gpol.col_cost = tune.gmul * 56.0 * 36.0 * gK * (gwarps > 1 ? 1.6 : 1.0) / teams_now;
         }
-        tpitch = tNW * 32 * (tK + 4);
-        tsmem = tgiant_smem_bytes(A, tpitch, tNW, Lq);
-        // one warp per scheduler issues a 32-row step in ~820 clocks: faster than giant.cu up to ~1500 rows
-        use_t = tsmem + 1024 <= (size_t)smem_optin && (Lq <= 1536 || getenv("PYOPAL_CUDA_TGIANT"));
-        if (use_t && !old_giants_ok) {
+        old_giants_ok = gpol.ok;
+        // transposed giants (tgiant.cu): the target over the lanes, the query streamed; needs the short F chain
+        if (fits8 && ge <= go && !tune.no_tgiant && !tune.no_giant && !endm) {
+            if (tune.has_tgiant) { tNW = tune.tg_warps; tK = tune.tg_K; tsplit_override = tune.tg_split; }
+            tpitch = tNW * 32 * (tK + 4);
+            tsmem = tgiant_smem_bytes(A, tpitch, tNW, Lq);
+            // one warp per scheduler issues a 32-row step in ~820 clocks: faster than giant.cu up to ~1500 rows
+            use_t = tsmem + 1024 <= (size_t)smem_optin && (Lq <= 1536 || tune.has_tgiant);
+            if (use_t && !old_giants_ok) {
+                gpol.ok = true;
+                gpol.cap = (int64_t)db->sm_count * 8;
+                // a revolution of Lq + 32 * warps - 1 steps covers 32 * warps * K target columns; a step costs
+                // about 25 clocks per row held by a lane (measured); 56 cost units per SM clock
+                const double step_clk = 25.0 * tK + 20.0;
+                gpol.col_cost = 56.0 * step_clk * (double)(Lq + tNW * 32 - 1) / (double)(tNW * 32 * tK);
+            }
+        }
+        if (endm && fits8 && !tune.no_giant) {
+            // end mode: the "giants" are walked by pairdp.cu's band teams; it takes what the 32-lane tile cannot
             gpol.ok = true;
             gpol.cap = (int64_t)db->sm_count * 8;
-            // a revolution of Lq + 32 * warps - 1 steps covers 32 * warps * K target columns; a step costs
-            // about 25 clocks per row held by a lane (measured); 56 cost units per SM clock
-            const double step_clk = 25.0 * tK + 20.0;
-            gpol.col_cost = 56.0 * step_clk * (double)(Lq + tNW * 32 - 1) / (double)(tNW * 32 * tK);
+            gpol.col_cost = 56.0 * 40.0 * (double)std::max(1, (Lq + 127) / 128);
         }
-    }
-    Plan bulk = make_plan(Lq, A, db, SMEM_LIMIT, &gpol);
-    Plan tail = make_tail_plan(Lq, A, SMEM_LIMIT);
-    int smax = INT_MIN, smin = INT_MAX;
-    for (int i = 0; i < A * A; i++) { smax = std::max(smax, M[i]); smin = std::min(smin, M[i]); }
-    const int Lp = std::max(bulk.npass * bulk.G * bulk.K, tail.npass * tail.G * tail.K);
-    Rung rung = make_rung(M, A, go, ge, mode, Lp);
-    const bool wide = !rung.fits8;
-    if (wide || bfix || !bulk.psmem || !tail.psmem) {
-        // profile in global memory: one tile shape (32 x 32) for every launch
-        bulk = make_forced_plan(Lq);
-        tail = bulk;
-    }
-    {
-        // 32-bit overflow cannot happen below this bound (scores are exact otherwise)
-        int64_t mag = std::max<int64_t>({(int64_t)go, (int64_t)ge, 1, std::llabs((long long)smax), std::llabs((long long)smin)});
-        const int64_t longest = db->h_pair_len[0];
-        if (mag * ((int64_t)Lp + longest + 8) >= (1LL << 29))
-            return fail(OPAL_ERR_OVERFLOW, "scores may exceed the 32-bit range");
-    }
-    const bool same_plan = (bulk.G == tail.G && bulk.K == tail.K && bulk.npass == tail.npass) ||
-                           getenv("PYOPAL_CUDA_NO_TAIL") != nullptr;
-    if (getenv("PYOPAL_CUDA_NO_TAIL")) tail = bulk;
+        const bool allow_mid = !tune.no_mid && !tune.no_tail && !tune.has_plan;
+        bulk = make_plan(Lq, A, db, SMEM_LIMIT, &gpol, allow_mid, &kmid);
+        tail = make_tail_plan(Lq, A, SMEM_LIMIT);
+        int smax = INT_MIN, smin = INT_MAX;
+        for (int i = 0; i < A * A; i++) { smax = std::max(smax, M[i]); smin = std::min(smin, M[i]); }
+        const int Lp = std::max(bulk.npass * bulk.G * bulk.K, tail.npass * tail.G * tail.K);
+        rung = make_rung(M, A, go, ge, mode, Lp);
+        wide = !rung.fits8;
+        if (wide || bfix || !bulk.psmem || !tail.psmem) {
+            // profile in global memory: one tile shape (32 x 32) for every launch
+            bulk = make_forced_plan(Lq);
+            tail = bulk;
+        }
+        {
+            // 32-bit overflow cannot happen below this bound (scores are exact otherwise)
+            int64_t mag = std::max<int64_t>({(int64_t)go, (int64_t)ge, 1, std::llabs((long long)smax), std::llabs((long long)smin)});
+            const int64_t longest = db->h_pair_len[0];
+            if (mag * ((int64_t)Lp + longest + 8) >= (1LL << 29))
+                return fail(OPAL_ERR_OVERFLOW, "scores may exceed the 32-bit range");
+        }
+        same_plan = (bulk.G == tail.G && bulk.K == tail.K && bulk.npass == tail.npass) || tune.no_tail;
+        if (tune.no_tail) tail = bulk;
 
-    // ---- split the (length-sorted) pairs ------------------------------------
-    // [0, n32p): 32-bit static; [n32p, n32p + ntailp): 16-bit tail; rest: 16-bit bulk
-    int64_t n32p = 0;
-    if (!rung.ok16) n32p = db->npairs;
-    else if (!local) {
-        int64_t lo = 0, hi = db->npairs;
-        while (lo < hi) {
-            int64_t mid = (lo + hi) / 2;
-            if (db->h_pair_len[(size_t)(2 * mid)] > rung.max_cols16) lo = mid + 1; else hi = mid;
+        // ---- split the (length-sorted) pairs ------------------------------------
+        // [0, kg): giants; [kg, n32p): 32-bit static; [n32p, tail_end): 16-bit mid tier; rest: 16-bit bulk
+        if (!rung.ok16) n32p = db->npairs;
+        else if (!local) n32p = first_pair_at_most(db, (double)rung.max_cols16, 0);
+        const bool giants_ok = gpol.ok && bulk.psmem && !wide;
+        kg = giants_ok ? gpol.kg : 0;
+        n32p = std::max(n32p, kg);
+        tail_end = n32p;
+        if (!same_plan) {
+            if (giants_ok) {
+                tail_end = std::max(n32p, kmid);
+            } else {
+                // no giant kernel for this query: a pair leaves the bulk kernel when walking it alone in the bulk tile
+                // would take more than a quarter of the whole search at full machine throughput
+                const double C0 = 28.0, C1 = 6.5;
+                const double total_instr = (double)db->ncols * bulk.npass * bulk.G * (C0 + C1 * bulk.K);
+                const double ideal_cycles = total_instr / ((double)db->sm_count * 64.0);
+                const double step_latency = 12.0 * bulk.K + 80.0;
+                const double thr = std::max(256.0, ideal_cycles / 4.0 / (bulk.npass * step_latency));
+                tail_end = first_pair_at_most(db, thr, n32p);
+            }
         }
-        n32p = lo;
-    }
-    int64_t tail_end = n32p;
-    // a pair leaves the bulk kernel when walking it alone in the bulk tile would
-    // take more than a quarter of the whole search at full machine throughput
-    double thr = 256.0;
-    {
-        const double C0 = 28.0, C1 = 6.5;
-        const double total_instr = (double)db->ncols * bulk.npass * bulk.G * (C0 + C1 * bulk.K);
-        const double ideal_cycles = total_instr / ((double)db->sm_count * 64.0);
-        const double step_latency = 12.0 * bulk.K + 80.0;
-        thr = std::max(256.0, ideal_cycles / 4.0 / (bulk.npass * step_latency));
-    }
-    // ---- giants: pairs [0, kg), chosen with the tile (make_plan) ----
-    const bool giants_ok = gpol.ok && bulk.psmem && !wide;
-    const int64_t kg = giants_ok ? gpol.kg : 0;
-    n32p = std::max(n32p, kg);
-    tail_end = n32p;
-    // the one-warp-per-pair tail kernel only remains for queries the giant kernel cannot take
-    if (!same_plan && !giants_ok) {
-        int64_t lo = n32p, hi = db->npairs;
-        while (lo < hi) {
-            int64_t mid = (lo + hi) / 2;
-            if ((double)db->h_pair_len[(size_t)(2 * mid)] > thr) lo = mid + 1; else hi = mid;
+        whole = (start == 0 && end >= db->n);
+        auto in_range = [&](int32_t idx) { return idx >= start && idx < end; };
+        auto pair_in_range = [&](int64_t k) {
+            return in_range(db->h_pair_idx[(size_t)(2 * k)]) ||
+                   (db->h_pair_idx[(size_t)(2 * k + 1)] >= 0 && in_range(db->h_pair_idx[(size_t)(2 * k + 1)]));
+        };
+        // giants longer than one slab of the transposed kernel go to tgiant.cu, the others to giant.cu
+        const int tsplit = !use_t ? INT32_MAX : tsplit_override >= 0 ? tsplit_override : tNW * 32 * tK;
+        for (int64_t k = 0; k < kg; k++) {
+            for (int h = 0; h < 2; h++) {
+                const int32_t ix = db->h_pair_idx[(size_t)(2 * k + h)];
+                if (ix < 0 || !in_range(ix)) continue;
+                const int32_t e = (int32_t)((k << 1) | h);
+                if (endm) endp->spill.push_back(e);
+                else if (db->h_pair_len[(size_t)(2 * k + h)] > tsplit || !old_giants_ok) wlt.push_back(e);
+                else wlg.push_back(e);
+            }
         }
-        tail_end = lo;
-    }
-    const bool whole = (start == 0 && end >= db->n);
-    auto in_range = [&](int32_t idx) { return idx >= start && idx < end; };
-    auto pair_in_range = [&](int64_t k) {
-        return in_range(db->h_pair_idx[(size_t)(2 * k)]) ||
-               (db->h_pair_idx[(size_t)(2 * k + 1)] >= 0 && in_range(db->h_pair_idx[(size_t)(2 * k + 1)]));
-    };
-    std::vector<int32_t> wl32, wl16, wlg, wlt;
-    // giants longer than one slab of the transposed kernel go to tgiant.cu, the others to giant.cu
-    const int tsplit = !use_t ? INT32_MAX : tsplit_override >= 0 ? tsplit_override : tNW * 32 * tK;
-    for (int64_t k = 0; k < kg; k++) {
-        for (int h = 0; h < 2; h++) {
-            const int32_t ix = db->h_pair_idx[(size_t)(2 * k + h)];
-            if (ix < 0 || !in_range(ix)) continue;
-            const int32_t e = (int32_t)((k << 1) | h);
-            if (db->h_pair_len[(size_t)(2 * k + h)] > tsplit || !old_giants_ok) wlt.push_back(e);
-            else wlg.push_back(e);
+        for (int64_t k = kg; k < n32p; k++) {
+            for (int h = 0; h < 2; h++) {
+                const int32_t ix = db->h_pair_idx[(size_t)(2 * k + h)];
+                if (ix < 0 || !in_range(ix)) continue;
+                if (endm) endp->spill.push_back((int32_t)((k << 1) | h));
+                else wl32.push_back((int32_t)((k << 1) | h));
+            }
         }
+        if (!whole) {
+            for (int64_t k = n32p; k < tail_end; k++) if (pair_in_range(k)) wl16.push_back((int32_t)k);
+            ntail = (int64_t)wl16.size();
+            for (int64_t k = tail_end; k < db->npairs; k++) if (pair_in_range(k)) wl16.push_back((int32_t)k);
+            nbulk = (int64_t)wl16.size() - ntail;
+        } else {
+            ntail = tail_end - n32p;
+            nbulk = db->npairs - tail_end;
+        }
+        n32 = (int64_t)wl32.size();
+        ng = (int64_t)wlg.size();
+        nt = (int64_t)wlt.size();
+        wl32.insert(wl32.end(), wlg.begin(), wlg.end());  // one list: [static 32-bit | giants | transposed giants]
+        wl32.insert(wl32.end(), wlt.begin(), wlt.end());
     }
-    for (int64_t k = kg; k < n32p; k++) {
-        if (in_range(db->h_pair_idx[(size_t)(2 * k)])) wl32.push_back((int32_t)(k << 1));
-        if (db->h_pair_idx[(size_t)(2 * k + 1)] >= 0 && in_range(db->h_pair_idx[(size_t)(2 * k + 1)]))
-            wl32.push_back((int32_t)((k << 1) | 1));
-    }
-    const int32_t* d_wl_tail = nullptr;
-    const int32_t* d_wl_bulk = nullptr;
-    int64_t ntail = 0, nbulk = 0;
-    if (whole) {
-        d_wl_tail = db->d_identity + n32p; ntail = tail_end - n32p;
-        d_wl_bulk = db->d_identity + tail_end; nbulk = db->npairs - tail_end;
-    } else {
-        for (int64_t k = n32p; k < tail_end; k++) if (pair_in_range(k)) wl16.push_back((int32_t)k);
-        ntail = (int64_t)wl16.size();
-        for (int64_t k = tail_end; k < db->npairs; k++) if (pair_in_range(k)) wl16.push_back((int32_t)k);
-        nbulk = (int64_t)wl16.size() - ntail;
-        if (db->wl16.reserve(wl16.size() + 1)) return PYOPAL_CUDA_ERR_NOMEM;
-        if (!wl16.empty())
-            CU(cudaMemcpyAsync(db->wl16.p, wl16.data(), wl16.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
-        d_wl_tail = db->wl16.p; d_wl_bulk = db->wl16.p + ntail;
-    }
-    const int64_t n32 = (int64_t)wl32.size();
-    const int64_t ng = (int64_t)wlg.size(), nt = (int64_t)wlt.size();
-    wl32.insert(wl32.end(), wlg.begin(), wlg.end());  // one upload: [static 32-bit | giants | transposed giants]
-    wl32.insert(wl32.end(), wlt.begin(), wlt.end());
-    if (db->wl32.reserve(wl32.size() + 1)) return PYOPAL_CUDA_ERR_NOMEM;
-    if (!wl32.empty()) CU(cudaMemcpyAsync(db->wl32.p, wl32.data(), wl32.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
     const int64_t n16 = ntail + nbulk;
-    if (same_plan) { d_wl_bulk = d_wl_tail; nbulk = n16; ntail = 0; }
-    if (local && n16 && db->ovf.reserve((size_t)(2 * n16))) return PYOPAL_CUDA_ERR_NOMEM;
+    if (same_plan) { nbulk = n16; ntail = 0; }
 
-    // ---- query, matrix, counters, buffers ------------------------------------
-    if (db->query.reserve((size_t)Lq)) return PYOPAL_CUDA_ERR_NOMEM;
-    CU(cudaMemcpyAsync(db->query.p, query, (size_t)Lq, cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(db->d_matrix, M, (size_t)A * A * sizeof(int32_t), cudaMemcpyHostToDevice, st));
-    int32_t counts[16] = {0};
-    counts[0] = (int32_t)nbulk; counts[1] = (int32_t)n32; counts[2] = 0; counts[3] = (int32_t)ntail;
-    counts[8] = (int32_t)ng; counts[10] = (int32_t)nt;
-    CU(cudaMemcpyAsync(db->d_counts, counts, sizeof(counts), cudaMemcpyHostToDevice, st));
+    // ---- the parameter block: counters, matrix, lists, fix-ups, query: one pinned copy, one H2D ------------
+    const size_t off_wl32 = PAR_LISTS;
+    const size_t off_wl16 = off_wl32 + ((wl32.size() * 4 + 15) & ~(size_t)15);
+    const size_t off_fix = off_wl16 + ((wl16.size() * 4 + 15) & ~(size_t)15);
+    const size_t off_query = off_fix + ((fixes.size() * 4 + 15) & ~(size_t)15);
+    const size_t par_bytes = off_query + (((size_t)Lq + 15) & ~(size_t)15) + 16;
+    const int slot = ws->par_next;
+    ws->par_next = (slot + 1) % Workspace::NPARAM;
+    if (ws->par_used[slot]) CU(cudaEventSynchronize(ws->par_done[slot]));
+    if (ws->h_par[slot].reserve(par_bytes) || ws->d_par.reserve(par_bytes)) return PYOPAL_CUDA_ERR_NOMEM;
+    unsigned char* hp = ws->h_par[slot].p;
+    unsigned char* dp = ws->d_par.p;
+    {
+        int32_t* counts = reinterpret_cast<int32_t*>(hp + PAR_COUNTS);
+        memset(counts, 0, 64);
+        counts[0] = (int32_t)nbulk; counts[1] = (int32_t)n32; counts[2] = 0; counts[3] = (int32_t)ntail;
+        counts[8] = (int32_t)ng; counts[10] = (int32_t)nt;
+        memcpy(hp + PAR_MATRIX, M, (size_t)A * A * sizeof(int32_t));
+        if (!wl32.empty()) memcpy(hp + off_wl32, wl32.data(), wl32.size() * 4);
+        if (!wl16.empty()) memcpy(hp + off_wl16, wl16.data(), wl16.size() * 4);
+        if (!fixes.empty()) memcpy(hp + off_fix, fixes.data(), fixes.size() * 4);
+        if (Lq > 0) memcpy(hp + off_query, query, (size_t)Lq);
+    }
+    CU(cudaMemcpyAsync(dp, hp, par_bytes, cudaMemcpyHostToDevice, st));
+    CU(cudaEventRecord(ws->par_done[slot], st));
+    ws->par_used[slot] = true;
+    int32_t* d_counts = reinterpret_cast<int32_t*>(dp + PAR_COUNTS);
+    const int32_t* d_wl32 = reinterpret_cast<const int32_t*>(dp + off_wl32);
+    const int32_t* d_wl16 = reinterpret_cast<const int32_t*>(dp + off_wl16);
+
+    auto apply_fixes = [&]() -> int {
+        if (fixes.empty()) return 0;
+        const int nfix = (int)(fixes.size() / 2);
+        scatter_fixes_kernel<<<(nfix + 255) / 256, 256, 0, st>>>(reinterpret_cast<const int32_t*>(dp + off_fix), nfix, d_out);
+        CU(cudaGetLastError());
+        return 0;
+    };
+    if (!device_dp) return apply_fixes();
+
+    const int32_t* d_wl_tail = whole ? db->d_identity + n32p : d_wl16;
+    const int32_t* d_wl_bulk = whole ? db->d_identity + tail_end : d_wl16 + (same_plan ? 0 : ntail);
+    if (same_plan) d_wl_bulk = d_wl_tail;
+    if (local && n16 && ws->ovf.reserve((size_t)(2 * n16))) return PYOPAL_CUDA_ERR_NOMEM;
     if (bulk.npass > 1 || tail.npass > 1) {
-        if (db->bndH.reserve((size_t)db->ncols + 16) || db->bndF.reserve((size_t)db->ncols + 16)) return PYOPAL_CUDA_ERR_NOMEM;
-        if (n32 > 0 || local)
-            if (db->bnd32H.reserve((size_t)db->ncols * 2 + 16) || db->bnd32F.reserve((size_t)db->ncols * 2 + 16))
+        if (ws->bndH.reserve((size_t)db->ncols + 16) || ws->bndF.reserve((size_t)db->ncols + 16)) return PYOPAL_CUDA_ERR_NOMEM;
+        if (!endm && (n32 > 0 || local))
+            if (ws->bnd32H.reserve((size_t)db->ncols * 2 + 16) || ws->bnd32F.reserve((size_t)db->ncols * 2 + 16))
                 return PYOPAL_CUDA_ERR_NOMEM;
     }
 
     KParams P;
     memset(&P, 0, sizeof(P));
     P.stream = db->d_stream; P.pair_off = db->d_pair_off; P.pair_len = db->d_pair_len; P.pair_idx = db->d_pair_idx;
-    P.query = db->query.p; P.matrix = db->d_matrix;
+    P.query = dp + off_query; P.matrix = reinterpret_cast<const int32_t*>(dp + PAR_MATRIX);
     P.Lq = Lq; P.A = A; P.go = go; P.ge = ge;
     P.mode = mode; P.pad_score = rung.pad_score; P.ovf_thresh = rung.ovf_thresh;
     P.one = 1u; P.bias = 0;
     P.out = d_out; P.out_start = start; P.out_end = end;
-    P.ovf_list = db->ovf.p; P.ovf_count = db->d_counts + 2;
-    P.bndH = db->bndH.p; P.bndF = db->bndF.p;
+    if (endm) { P.out_q = endp->d_endq; P.out_t = endp->d_endt; }
+    P.ovf_list = ws->ovf.p; P.ovf_count = d_counts + 2;
+    P.bndH = ws->bndH.p; P.bndF = ws->bndF.p;
+    if (endm) { endp->d_ovf = ws->ovf.p; endp->d_ovf_count = d_counts + 2; endp->packed = n16 > 0; }
 
     search_kernel_t k32 = nullptr;
     if (wide) {
         apply_plan(P, tail);
-        if (db->wprofile.reserve((size_t)(A + 1) * tail.pitch)) return PYOPAL_CUDA_ERR_NOMEM;
-        P.wprofile = db->wprofile.p;
-        build_profile_kernel<<<64, 256, 0, st>>>(P, nullptr, db->wprofile.p);
+        if (ws->wprofile.reserve((size_t)(A + 1) * tail.pitch)) return PYOPAL_CUDA_ERR_NOMEM;
+        P.wprofile = ws->wprofile.p;
+        build_profile_kernel<<<64, 256, 0, st>>>(P, nullptr, ws->wprofile.p);
         CU(cudaGetLastError());
         k32 = bfix ? get_search_kernel_bfix(true) : get_search_kernel_wide(local);
     } else {
         if (!tail.psmem) {
             apply_plan(P, tail);
-            if (db->gprofile.reserve((size_t)(A + 1) * tail.pitch)) return PYOPAL_CUDA_ERR_NOMEM;
-            P.gprofile = db->gprofile.p;
-            build_profile_kernel<<<64, 256, 0, st>>>(P, db->gprofile.p, nullptr);
+            if (ws->gprofile.reserve((size_t)(A + 1) * tail.pitch)) return PYOPAL_CUDA_ERR_NOMEM;
+            P.gprofile = ws->gprofile.p;
+            build_profile_kernel<<<64, 256, 0, st>>>(P, ws->gprofile.p, nullptr);
             CU(cudaGetLastError());
         }
         k32 = bfix ? get_search_kernel_bfix(false) : pick_kernel(tail.K, 32, local, tail.psmem);
@@ -759,12 +975,13 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
     if (!k32) return fail(PYOPAL_CUDA_ERR_INTERNAL, "no 32-bit kernel for this tile");
 
     // ---- side stream: longest targets first, concurrently with the bulk -------
-    const bool side_work = (ng > 0) || (nt > 0) || (n32 > 0) || (ntail > 0 && !same_plan);
-    cudaStream_t side = db->side;
+    const bool mid_work = ntail > 0 && !same_plan;
+    const bool side_work = (ng > 0) || (nt > 0) || (n32 > 0) || mid_work;
+    cudaStream_t side = ws->side;
     if (side_work) {
-        CU(cudaEventRecord(db->ev_fork, st));
-        CU(cudaStreamWaitEvent(side, db->ev_fork, 0));
-        CU(cudaEventRecord(db->kev[0], side));
+        CU(cudaEventRecord(ws->ev_fork, st));
+        CU(cudaStreamWaitEvent(side, ws->ev_fork, 0));
+        CU(cudaEventRecord(ws->kev[0], side));
     }
     if (nt > 0) {
         search_kernel_t kt = get_tgiant_kernel(tK, local);
@@ -774,17 +991,17 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
         Q.krows = tK; Q.kstride = tK + 4;
         // padding rows above target position 0 reproduce the border H[i][-1] (kernels.cuh, profile_entry)
         Q.pad_score = ((mode == MODE_NW || mode == MODE_HW) ? -std::max(go, ge) : 0) + go;
-        Q.worklist = db->wl32.p + n32 + ng; Q.nwork = db->d_counts + 10; Q.counter = db->d_counts + 11;
+        Q.worklist = d_wl32 + n32 + ng; Q.nwork = d_counts + 10; Q.counter = d_counts + 11;
         Q.neg = -(1 << 29);
         // the whole SM's shared memory: no throughput CTA shares the SM with a giant (giant.cu)
         const size_t smem_all = std::max<size_t>(tsmem, (size_t)smem_optin - 1024);
         CU(cudaFuncSetAttribute(kt, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_all));
         // its own stream: the few longest targets start at once, beside giant.cu's medium ones
-        CU(cudaStreamWaitEvent(db->side2, db->ev_fork, 0));
-        kt<<<(unsigned)std::min<int64_t>(nt, db->sm_count), tNW * 32, smem_all, db->side2>>>(Q);
+        CU(cudaStreamWaitEvent(ws->side2, ws->ev_fork, 0));
+        kt<<<(unsigned)std::min<int64_t>(nt, db->sm_count), tNW * 32, smem_all, ws->side2>>>(Q);
         CU(cudaGetLastError());
-        CU(cudaEventRecord(db->ev_join2, db->side2));
-        db->stats[0]++;
+        CU(cudaEventRecord(ws->ev_join2, ws->side2));
+        ws->stats[0]++;
     }
     if (ng > 0) {
         search_kernel_t kgiant = get_giant_kernel(gK, local);
@@ -794,7 +1011,7 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
         const int teams = (int)std::max<int64_t>(1, std::min<int64_t>(gteams, (ng + 7) / 8));
         Q.G = gwarps; Q.logG = 0; Q.npass = teams; Q.pitch = gpitch; Q.padtop = gwarps * 32 * gK - Lq;
         Q.krows = gK; Q.kstride = (gK == 4) ? 4 : gK + 4;
-        Q.worklist = db->wl32.p + n32; Q.nwork = db->d_counts + 8; Q.counter = db->d_counts + 9;
+        Q.worklist = d_wl32 + n32; Q.nwork = d_counts + 8; Q.counter = d_counts + 9;
         Q.neg = -(1 << 29);
         // ask for the whole SM's shared memory: no throughput CTA may share the SM with the giants (giant.cu)
         const size_t gsmem_all = std::max<size_t>(gsmem, (size_t)smem_optin - 1024);
@@ -804,86 +1021,93 @@ int enqueue_score_search(pyopal_cuda_db* db, const unsigned char* query, int Lq,
         const int64_t gcap = use_t ? std::max<int64_t>(8, db->sm_count / 4) : db->sm_count;
         kgiant<<<(unsigned)std::min<int64_t>((ng + teams - 1) / teams, gcap), 512, gsmem_all, side>>>(Q);
         CU(cudaGetLastError());
-        db->stats[0]++;
+        ws->stats[0]++;
     }
     if (n32 > 0) {
         KParams Q = P;
         apply_plan(Q, tail);
-        Q.worklist = db->wl32.p; Q.nwork = db->d_counts + 1; Q.counter = db->d_counts + 5;
+        Q.worklist = d_wl32; Q.nwork = d_counts + 1; Q.counter = d_counts + 5;
         Q.neg = -(1 << 29);
-        Q.bndH = db->bnd32H.p; Q.bndF = db->bnd32F.p;
-        int rc = launch_search(db, k32, Q, tail.smem, 32, n32, side);
+        Q.bndH = ws->bnd32H.p; Q.bndF = ws->bnd32F.p;
+        int rc = launch_search(db, ws, k32, Q, tail.smem, 32, n32, side);
         if (rc) return rc;
     }
-    if (ntail > 0 && !same_plan) {
-        search_kernel_t kt = pick_kernel(tail.K, 16, local, tail.psmem, rung.tdadd);
-        if (!kt) return fail(PYOPAL_CUDA_ERR_INTERNAL, "no 16-bit kernel for the tail tile");
+    if (mid_work) {
+        search_kernel_t kt = pick_kernel(tail.K, 16, local, tail.psmem, rung.tdadd, endm);
+        if (!kt) return fail(PYOPAL_CUDA_ERR_INTERNAL, "no 16-bit kernel for the mid tile");
         KParams Q = P;
         apply_plan(Q, tail);
-        Q.worklist = d_wl_tail; Q.nwork = db->d_counts + 3; Q.counter = db->d_counts + 7;
+        Q.worklist = d_wl_tail; Q.nwork = d_counts + 3; Q.counter = d_counts + 7;
         Q.neg = rung.neg16; Q.bias = rung.bias16;
-        int rc = launch_search(db, kt, Q, tail.smem, 32, ntail, side);
+        // CTAs of four warps share one copy of the profile; as many of them as the mid tier's share of the
+        // columns is of the machine's resident warps, so that both tiers finish together
+        const double share = (double)((tail_end < db->npairs ? db->h_pair_off[(size_t)tail_end] : db->ncols) -
+                                      (n32p < db->npairs ? db->h_pair_off[(size_t)n32p] : db->ncols)) /
+                             std::max<double>(1.0, (double)db->ncols);
+        const int mthreads = ntail >= 4 * (int64_t)db->sm_count ? 128 : 32;
+        const int64_t cap = std::max<int64_t>(db->sm_count / 4,
+                                              (int64_t)(1.15 * share * db->sm_count * 14.0 / (mthreads / 32) + 0.999));
+        int rc = launch_search(db, ws, kt, Q, tail.smem, mthreads, ntail, side, cap);
         if (rc) return rc;
     }
     if (side_work) {
-        if (nt > 0) CU(cudaStreamWaitEvent(side, db->ev_join2, 0));  // joins only after everything is launched
-        CU(cudaEventRecord(db->kev[1], side));
-        db->kev_valid[0] = true;
-        CU(cudaEventRecord(db->ev_join, side));
+        if (nt > 0) CU(cudaStreamWaitEvent(side, ws->ev_join2, 0));  // joins only after everything is launched
+        CU(cudaEventRecord(ws->kev[1], side));
+        ws->kev_valid[0] = true;
+        CU(cudaEventRecord(ws->ev_join, side));
     }
 
     // ---- bulk -------------------------------------------------------------------
-    {
-        const int32_t* wl = d_wl_bulk;
-        const int64_t nw = nbulk;
-        if (nw > 0) {
-            search_kernel_t kb = pick_kernel(bulk.K, 16, local, bulk.psmem, rung.tdadd);
-            if (!kb) return fail(PYOPAL_CUDA_ERR_INTERNAL, "no 16-bit kernel for this tile");
-            KParams Q = P;
-            apply_plan(Q, bulk);
-            Q.worklist = wl; Q.nwork = db->d_counts + 0; Q.counter = db->d_counts + 4;
-            Q.neg = rung.neg16; Q.bias = rung.bias16;
-            const int gpw = 32 >> bulk.logG;
-            // one CTA per SM when the profile is large: use the whole register file with 16 warps
-            // (with side-stream CTAs resident, 7-warp CTAs leave them registers: 2 x 224 x 128 < 64K)
-            int threads = (bulk.smem > (size_t)110 * 1024) ? (side_work ? 480 : 512) : (side_work ? 224 : 256);
-            if (const char* ov = getenv("PYOPAL_CUDA_PLAN")) {
-                int lg = 0, k = 0, t = 0;
-                if (sscanf(ov, "%d,%d,%d", &lg, &k, &t) == 3 && t >= 32 && t <= 512 && t % 32 == 0) threads = t;
-            }
-            CU(cudaEventRecord(db->kev[2], st));
-            if (getenv("PYOPAL_CUDA_DEBUG"))
-                fprintf(stderr, "[pyopal_cuda] Lq=%d bulk: G=%d K=%d npass=%d pairs=%lld | giants=%lld tgiants=%lld static32=%lld threads=%d smem=%zu\n",
-                        Lq, bulk.G, bulk.K, bulk.npass, (long long)nw, (long long)ng, (long long)nt, (long long)n32, threads,
-                        bulk.smem);
-            int rc = launch_search(db, kb, Q, bulk.smem, threads, (nw + gpw - 1) / gpw, st);
-            if (rc) return rc;
-            CU(cudaEventRecord(db->kev[3], st));
-            db->kev_valid[1] = true;
-        }
+    if (nbulk > 0) {
+        search_kernel_t kb = pick_kernel(bulk.K, 16, local, bulk.psmem, rung.tdadd, endm);
+        if (!kb) return fail(PYOPAL_CUDA_ERR_INTERNAL, "no 16-bit kernel for this tile");
+        KParams Q = P;
+        apply_plan(Q, bulk);
+        Q.worklist = d_wl_bulk; Q.nwork = d_counts + 0; Q.counter = d_counts + 4;
+        Q.neg = rung.neg16; Q.bias = rung.bias16;
+        const int gpw = 32 >> bulk.logG;
+        // one CTA per SM when the profile is large: use the whole register file with 16 warps
+        // (with side-stream CTAs resident, 7-warp CTAs leave them registers: 2 x 224 x 128 < 64K)
+        int threads = (bulk.smem > (size_t)110 * 1024) ? (side_work ? 480 : 512) : (side_work ? 224 : 256);
+        if (tune.plan_threads) threads = tune.plan_threads;
+        CU(cudaEventRecord(ws->kev[2], st));
+        if (tune.debug)
+            fprintf(stderr, "[pyopal_cuda] Lq=%d %s bulk: G=%d K=%d npass=%d pairs=%lld | mid=%lld (K=%d npass=%d) giants=%lld tgiants=%lld static32=%lld spill=%lld threads=%d smem=%zu\n",
+                    Lq, endm ? "END" : "score", bulk.G, bulk.K, bulk.npass, (long long)nbulk, (long long)(mid_work ? ntail : 0), tail.K,
+                    tail.npass, (long long)ng, (long long)nt, (long long)n32, (long long)(endm ? endp->spill.size() : 0), threads, bulk.smem);
+        int rc = launch_search(db, ws, kb, Q, bulk.smem, threads, (nbulk + gpw - 1) / gpw, st);
+        if (rc) return rc;
+        CU(cudaEventRecord(ws->kev[3], st));
+        ws->kev_valid[1] = true;
     }
-    if (side_work) CU(cudaStreamWaitEvent(st, db->ev_join, 0));
+    if (side_work) CU(cudaStreamWaitEvent(st, ws->ev_join, 0));
 
     // ---- rescue: 32-bit rescore of what overflowed (list and size live on the device)
-    if (local && n16 > 0) {
+    if (local && n16 > 0 && !endm) {
         KParams R = P;
         apply_plan(R, tail);
-        R.worklist = db->ovf.p; R.nwork = db->d_counts + 2; R.counter = db->d_counts + 6;
+        R.worklist = ws->ovf.p; R.nwork = d_counts + 2; R.counter = d_counts + 6;
         R.neg = -(1 << 29);
-        R.bndH = db->bnd32H.p; R.bndF = db->bnd32F.p;
-        CU(cudaEventRecord(db->kev[4], st));
-        int rc = launch_search(db, k32, R, tail.smem, 32, std::min<int64_t>(2 * n16, (int64_t)db->sm_count * 4), st);
+        R.bndH = ws->bnd32H.p; R.bndF = ws->bnd32F.p;
+        CU(cudaEventRecord(ws->kev[4], st));
+        int rc = launch_search(db, ws, k32, R, tail.smem, 32, std::min<int64_t>(2 * n16, (int64_t)db->sm_count * 4), st);
         if (rc) return rc;
-        CU(cudaEventRecord(db->kev[5], st));
-        db->kev_valid[2] = true;
+        CU(cudaEventRecord(ws->kev[5], st));
+        ws->kev_valid[2] = true;
     }
-    db->stats[1] = n16 * 2; db->stats[2] = n32 + ng + nt;
-    db->stats[5] = bulk.G; db->stats[6] = bulk.K; db->stats[7] = bulk.npass; db->stats[11] = bulk.psmem ? 1 : 0;
+    ws->stats[1] = n16 * 2; ws->stats[2] = n32 + ng + nt;
+    ws->stats[5] = bulk.G; ws->stats[6] = bulk.K; ws->stats[7] = bulk.npass; ws->stats[11] = bulk.psmem ? 1 : 0;
     return apply_fixes();
 }
 
-int check_search_args(pyopal_cuda_db* db, const unsigned char* query, int Lq, int go, int ge, const int* M,
-                      int A, int mode, int64_t* start, int64_t* end) {
+int pyopal::enqueue_score_search(pyopal_cuda_db* db, Workspace* ws, const unsigned char* query, int Lq, int go, int ge,
+                                 const int* M, int A, int mode, int64_t start, int64_t end, int32_t* d_out,
+                                 cudaStream_t st) {
+    return enqueue_score_search_ex(db, ws, query, Lq, go, ge, M, A, mode, start, end, d_out, st, nullptr);
+}
+
+int pyopal::check_search_args(pyopal_cuda_db* db, const unsigned char* query, int Lq, int go, int ge, const int* M,
+                              int A, int mode, int64_t* start, int64_t* end) {
     if (!db || !M || (Lq > 0 && !query)) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null argument");
     if (mode < MODE_NW || mode > MODE_SW) return fail(OPAL_ERR_INVALID_MODE, "invalid alignment mode");
     if (A != db->A) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "alphabet length differs from the store's");
@@ -897,7 +1121,6 @@ int check_search_args(pyopal_cuda_db* db, const unsigned char* query, int Lq, in
     return 0;
 }
 
-}  // namespace
 
 // ---------------------------------------------------------------------------
 // Public search entry points
@@ -909,10 +1132,13 @@ extern "C" int pyopal_cuda_search_scores_device(pyopal_cuda_db* db, const unsign
     int rc = check_search_args(db, query, queryLength, gapOpen, gapExt, scoreMatrix, alphabetLength, mode, &start, &end);
     if (rc) return rc;
     if (end > start && !d_scores) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null output");
-    std::lock_guard<std::mutex> lock(db->mu);
-    CU(cudaSetDevice(db->device));
-    return enqueue_score_search(db, query, queryLength, gapOpen, gapExt, scoreMatrix, alphabetLength, mode, start,
-                                end, d_scores, (cudaStream_t)stream);
+    DeviceGuard guard(db->device);
+    Lease lease(db);
+    if (!lease.ws) return PYOPAL_CUDA_ERR_NOMEM;
+    // the workspace goes back to the pool when this returns; its `ev_free` event orders the next search that
+    // picks it up (on whatever stream) after this one
+    return enqueue_score_search(db, lease.ws, query, queryLength, gapOpen, gapExt, scoreMatrix, alphabetLength, mode,
+                                start, end, d_scores, (cudaStream_t)stream);
 }
 
 extern "C" int pyopal_cuda_search(pyopal_cuda_db* db, const unsigned char* query, int queryLength, int gapOpen,
@@ -929,90 +1155,156 @@ extern "C" int pyopal_cuda_search(pyopal_cuda_db* db, const unsigned char* query
     const int64_t nout = end - start;
     if (nout <= 0) return 0;
     if (!scores) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null output");
-    std::lock_guard<std::mutex> lock(db->mu);
-    CU(cudaSetDevice(db->device));
+    DeviceGuard guard(db->device);
+    Lease lease(db);
+    Workspace* ws = lease.ws;
+    if (!ws) return PYOPAL_CUDA_ERR_NOMEM;
     if (searchType != OPAL_SEARCH_SCORE)
-        return pyopal_end_full_search(db, query, queryLength, gapOpen, gapExt, scoreMatrix, alphabetLength,
+        return pyopal_end_full_search(db, ws, query, queryLength, gapOpen, gapExt, scoreMatrix, alphabetLength,
                                       searchType, mode, start, end, scores, endQ, endT, startQ, startT, ops,
                                       ops_offsets, ops_len);
-    if (db->out.reserve((size_t)nout)) return PYOPAL_CUDA_ERR_NOMEM;
-    CU(cudaEventRecord(db->ev0, db->stream));
-    rc = enqueue_score_search(db, query, queryLength, gapOpen, gapExt, scoreMatrix, alphabetLength, mode, start, end,
-                              db->out.p, db->stream);
+    if (ws->out.reserve((size_t)nout)) return PYOPAL_CUDA_ERR_NOMEM;
+    CU(cudaEventRecord(ws->ev0, ws->stream));
+    rc = enqueue_score_search(db, ws, query, queryLength, gapOpen, gapExt, scoreMatrix, alphabetLength, mode, start, end,
+                              ws->out.p, ws->stream);
     if (rc) return rc;
-    CU(cudaMemcpyAsync(scores, db->out.p, (size_t)nout * sizeof(int32_t), cudaMemcpyDeviceToHost, db->stream));
-    CU(cudaEventRecord(db->ev1, db->stream));
-    CU(cudaStreamSynchronize(db->stream));
+    CU(cudaMemcpyAsync(scores, ws->out.p, (size_t)nout * sizeof(int32_t), cudaMemcpyDeviceToHost, ws->stream));
+    CU(cudaEventRecord(ws->ev1, ws->stream));
+    CU(cudaStreamSynchronize(ws->stream));
     float ms = 0;
-    CU(cudaEventElapsedTime(&ms, db->ev0, db->ev1));
-    db->stats[4] = (int64_t)(ms * 1000.0f);
-    int32_t novf = 0;
-    CU(cudaMemcpy(&novf, db->d_counts + 2, sizeof(int32_t), cudaMemcpyDeviceToHost));
-    db->stats[3] = novf;
+    CU(cudaEventElapsedTime(&ms, ws->ev0, ws->ev1));
+    ws->stats[4] = (int64_t)(ms * 1000.0f);
+    return 0;
+}
+
+// opal.pxd:56-67: Smith-Waterman SCORE search over `char` sequences (declared by the interface PyOpal binds,
+// never called by it).  Same staging as opalSearchDatabase.
+extern "C" int opalSearchDatabaseCharSW(char query[], int queryLength, char** db, int dbLength, int dbSeqLengths[],
+                                        int gapOpen, int gapExt, int* scoreMatrix, int alphabetLength,
+                                        OpalSearchResult* results[]) {
+    return opalSearchDatabase(reinterpret_cast<unsigned char*>(query), queryLength,
+                              reinterpret_cast<unsigned char**>(db), dbLength, dbSeqLengths, gapOpen, gapExt,
+                              scoreMatrix, alphabetLength, results, OPAL_SEARCH_SCORE, OPAL_MODE_SW,
+                              OPAL_OVERFLOW_BUCKETS);
+}
+
+// Batched SCORE search, stream-ordered: query i runs on workspace i mod 2, so the kernels of query i + 1 are
+// already queued behind those of query i (its persistent CTAs take over the SMs as the previous search's drain),
+// score rows are copied out on the workspace's own stream, and the host only waits once, at the end.  With
+// `k` > 0 only the k best hits of every query leave the device (topk.cu).
+static int search_batch_impl(pyopal_cuda_db* db, const unsigned char* queries, const int64_t* q_offsets,
+                             const int32_t* q_lengths, int nq, int go, int ge, const int* M, int A, int mode,
+                             int32_t* scores, int k, int32_t* top_scores, int32_t* top_idx) {
+    if (!db || nq < 0 || (nq > 0 && (!queries || !q_offsets || !q_lengths)))
+        return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null argument");
+    const int64_t n = db->n;
+    if (n == 0 || nq == 0) return 0;
+    DeviceGuard guard(db->device);
+    const int NB = 2;
+    Lease l0(db), l1(db);
+    Workspace* wsv[NB] = {l0.ws, l1.ws};
+    if (!wsv[0] || !wsv[1]) return PYOPAL_CUDA_ERR_NOMEM;
+    const int kk = (int)std::min<int64_t>(k, n);
+    std::vector<int32_t> tv, ti;
+    if (kk > 0) { tv.resize((size_t)nq * kk); ti.resize((size_t)nq * kk); }
+    for (int b = 0; b < NB; b++) {
+        if (wsv[b]->out.reserve((size_t)n)) return PYOPAL_CUDA_ERR_NOMEM;
+        if (kk > 0 && (wsv[b]->tk_ws.reserve(topk_workspace_words()) || wsv[b]->tk_vals.reserve((size_t)kk) ||
+                       wsv[b]->tk_idx.reserve((size_t)kk)))
+            return PYOPAL_CUDA_ERR_NOMEM;
+    }
+    int rc = 0;
+    int64_t launches = 0;
+    // results of query i are copied out AFTER query i + 1 has been enqueued: a copy into pageable host memory
+    // blocks the host until the search before it is done, and by then the next one is already queued on the device
+    auto copy_out = [&](int i) -> int {
+        Workspace* ws = wsv[i % NB];
+        if (kk > 0) {
+            CU(cudaMemcpyAsync(tv.data() + (size_t)i * kk, ws->tk_vals.p, (size_t)kk * 4, cudaMemcpyDeviceToHost, ws->stream));
+            CU(cudaMemcpyAsync(ti.data() + (size_t)i * kk, ws->tk_idx.p, (size_t)kk * 4, cudaMemcpyDeviceToHost, ws->stream));
+        } else if (scores) {
+            CU(cudaMemcpyAsync(scores + (size_t)i * (size_t)n, ws->out.p, (size_t)n * sizeof(int32_t),
+                               cudaMemcpyDeviceToHost, ws->stream));
+        }
+        CU(cudaEventRecord(ws->ev_free, ws->stream));
+        return 0;
+    };
+    for (int i = 0; i < nq && rc == 0; i++) {
+        Workspace* ws = wsv[i % NB];
+        int64_t s = 0, e = n;
+        const unsigned char* q = queries + q_offsets[i];
+        rc = check_search_args(db, q, q_lengths[i], go, ge, M, A, mode, &s, &e);
+        if (rc) break;
+        // this workspace's row buffer is overwritten: its previous copy-out ran on the same stream
+        rc = enqueue_score_search(db, ws, q, q_lengths[i], go, ge, M, A, mode, 0, n, ws->out.p, ws->stream);
+        if (rc) break;
+        launches += ws->stats[0];
+        if (kk > 0) {
+            rc = topk_device(ws->out.p, n, kk, ws->tk_vals.p, ws->tk_idx.p, ws->tk_ws.p, db->sm_count, ws->stream);
+            if (rc) break;
+            launches += 9;
+        }
+        if (i > 0) rc = copy_out(i - 1);
+    }
+    if (rc == 0) rc = copy_out(nq - 1);
+    for (int b = 0; b < NB; b++) {
+        cudaError_t e = cudaStreamSynchronize(wsv[b]->stream);
+        if (e != cudaSuccess && rc == 0) rc = fail(PYOPAL_CUDA_ERR_CUDA, std::string("batch: ") + cudaGetErrorString(e));
+    }
+    wsv[0]->stats[0] = launches;
+    wsv[1]->stats[0] = launches;
+    if (rc) return rc;
+    if (kk > 0) {
+        // order the k hits of every query: score descending, ties by ascending database index
+        std::vector<int32_t> order((size_t)kk);
+        for (int i = 0; i < nq; i++) {
+            const int32_t* v = tv.data() + (size_t)i * kk;
+            const int32_t* ix = ti.data() + (size_t)i * kk;
+            std::iota(order.begin(), order.end(), 0);
+            std::sort(order.begin(), order.end(), [&](int32_t a, int32_t b) { return v[a] != v[b] ? v[a] > v[b] : ix[a] < ix[b]; });
+            for (int j = 0; j < kk; j++) {
+                top_scores[(size_t)i * k + j] = v[order[(size_t)j]];
+                top_idx[(size_t)i * k + j] = ix[order[(size_t)j]];
+            }
+        }
+    }
     return 0;
 }
 
 extern "C" int pyopal_cuda_search_batch(pyopal_cuda_db* db, const unsigned char* queries, const int64_t* q_offsets,
                                         const int32_t* q_lengths, int nq, int gapOpen, int gapExt,
                                         const int* scoreMatrix, int alphabetLength, int mode, int32_t* scores) {
-    if (!db || nq < 0 || (nq > 0 && (!queries || !q_offsets || !q_lengths || !scores)))
-        return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null argument");
-    const int64_t n = db->n;
-    if (n == 0) return 0;
-    std::lock_guard<std::mutex> lock(db->mu);
-    CU(cudaSetDevice(db->device));
-    // double-buffer the score rows so the D2H of query i overlaps the kernels of query i+1
-    int32_t* d_rows[2] = {nullptr, nullptr};
-    cudaStream_t copy_stream = nullptr;
-    cudaEvent_t done[2] = {nullptr, nullptr}, copied[2] = {nullptr, nullptr};
-    int rc = 0;
-    auto cleanup = [&]() {
-        for (int b = 0; b < 2; b++) {
-            if (d_rows[b]) cudaFree(d_rows[b]);
-            if (done[b]) cudaEventDestroy(done[b]);
-            if (copied[b]) cudaEventDestroy(copied[b]);
-        }
-        if (copy_stream) cudaStreamDestroy(copy_stream);
-    };
-#define CUB(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { cleanup(); return fail(PYOPAL_CUDA_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } } while (0)
-    CUB(cudaStreamCreateWithFlags(&copy_stream, cudaStreamNonBlocking));
-    for (int b = 0; b < 2; b++) {
-        CUB(cudaMalloc(&d_rows[b], (size_t)n * sizeof(int32_t)));
-        CUB(cudaEventCreateWithFlags(&done[b], cudaEventDisableTiming));
-        CUB(cudaEventCreateWithFlags(&copied[b], cudaEventDisableTiming));
-    }
-    for (int i = 0; i < nq && rc == 0; i++) {
-        const int b = i & 1;
-        int64_t s = 0, e = n;
-        const unsigned char* q = queries + q_offsets[i];
-        rc = check_search_args(db, q, q_lengths[i], gapOpen, gapExt, scoreMatrix, alphabetLength, mode, &s, &e);
-        if (rc) break;
-        if (i >= 2) CUB(cudaStreamWaitEvent(db->stream, copied[b], 0));
-        rc = enqueue_score_search(db, q, q_lengths[i], gapOpen, gapExt, scoreMatrix, alphabetLength, mode, 0, n,
-                                  d_rows[b], db->stream);
-        if (rc) break;
-        CUB(cudaEventRecord(done[b], db->stream));
-        CUB(cudaStreamWaitEvent(copy_stream, done[b], 0));
-        CUB(cudaMemcpyAsync(scores + (size_t)i * (size_t)n, d_rows[b], (size_t)n * sizeof(int32_t),
-                            cudaMemcpyDeviceToHost, copy_stream));
-        CUB(cudaEventRecord(copied[b], copy_stream));
-        // the per-search workspace (query, counters, lists) is reused by the next query
-        CUB(cudaStreamSynchronize(db->stream));
-    }
-    if (rc == 0) CUB(cudaStreamSynchronize(copy_stream));
-#undef CUB
-    cleanup();
-    return rc;
+    if (nq > 0 && db && db->n > 0 && !scores) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null output");
+    return search_batch_impl(db, queries, q_offsets, q_lengths, nq, gapOpen, gapExt, scoreMatrix, alphabetLength, mode,
+                             scores, 0, nullptr, nullptr);
+}
+
+extern "C" int pyopal_cuda_search_batch_topk(pyopal_cuda_db* db, const unsigned char* queries, const int64_t* q_offsets,
+                                             const int32_t* q_lengths, int nq, int gapOpen, int gapExt,
+                                             const int* scoreMatrix, int alphabetLength, int mode, int k,
+                                             int32_t* scores, int32_t* indices) {
+    if (k <= 0) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "k must be positive");
+    if (nq > 0 && (!scores || !indices)) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null output");
+    if (db && k > db->n) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "k exceeds the database size");
+    return search_batch_impl(db, queries, q_offsets, q_lengths, nq, gapOpen, gapExt, scoreMatrix, alphabetLength, mode,
+                             nullptr, k, scores, indices);
 }
 
 extern "C" int pyopal_cuda_topk_device(pyopal_cuda_db* db, const int32_t* d_scores, int64_t n, int k,
                                        int32_t* d_scores_out, int32_t* d_indices_out, void* stream) {
     if (!db || (n > 0 && k > 0 && (!d_scores || !d_scores_out || !d_indices_out))) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null argument");
     if (k < 0 || n < 0 || k > n || n > INT32_MAX) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "top-k needs 0 <= k <= n < 2^31");
-    std::lock_guard<std::mutex> lock(db->mu);
-    CU(cudaSetDevice(db->device));
-    if (db->tk_ws.reserve(topk_workspace_words())) return PYOPAL_CUDA_ERR_NOMEM;
-    return topk_device(d_scores, n, k, d_scores_out, d_indices_out, db->tk_ws.p, db->sm_count, (cudaStream_t)stream);
+    DeviceGuard guard(db->device);
+    Lease lease(db);
+    Workspace* ws = lease.ws;
+    if (!ws) return PYOPAL_CUDA_ERR_NOMEM;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (ws->tk_ws.reserve(topk_workspace_words())) return PYOPAL_CUDA_ERR_NOMEM;
+    if (ws->used) CU(cudaStreamWaitEvent(st, ws->ev_free, 0));
+    ws->used = true;
+    int rc = topk_device(d_scores, n, k, d_scores_out, d_indices_out, ws->tk_ws.p, db->sm_count, st);
+    CU(cudaEventRecord(ws->ev_free, st));
+    return rc;
 }
 
 extern "C" int pyopal_cuda_search_topk(pyopal_cuda_db* db, const unsigned char* query, int queryLength, int gapOpen,
@@ -1026,26 +1318,29 @@ extern "C" int pyopal_cuda_search_topk(pyopal_cuda_db* db, const unsigned char* 
     if (n_hits) *n_hits = kk > 0 ? kk : 0;
     if (kk <= 0) return 0;
     if (!scores || !indices) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null output");
-    std::lock_guard<std::mutex> lock(db->mu);
-    CU(cudaSetDevice(db->device));
-    if (db->out.reserve((size_t)nout) || db->tk_ws.reserve(topk_workspace_words()) || db->tk_vals.reserve((size_t)kk) ||
-        db->tk_idx.reserve((size_t)kk))
+    DeviceGuard guard(db->device);
+    Lease lease(db);
+    Workspace* ws = lease.ws;
+    if (!ws) return PYOPAL_CUDA_ERR_NOMEM;
+    if (ws->out.reserve((size_t)nout) || ws->tk_ws.reserve(topk_workspace_words()) || ws->tk_vals.reserve((size_t)kk) ||
+        ws->tk_idx.reserve((size_t)kk))
         return PYOPAL_CUDA_ERR_NOMEM;
-    CU(cudaEventRecord(db->ev0, db->stream));
-    rc = enqueue_score_search(db, query, queryLength, gapOpen, gapExt, scoreMatrix, alphabetLength, mode, start, end,
-                              db->out.p, db->stream);
+    CU(cudaEventRecord(ws->ev0, ws->stream));
+    rc = enqueue_score_search(db, ws, query, queryLength, gapOpen, gapExt, scoreMatrix, alphabetLength, mode, start, end,
+                              ws->out.p, ws->stream);
     if (rc) return rc;
-    rc = topk_device(db->out.p, nout, kk, db->tk_vals.p, db->tk_idx.p, db->tk_ws.p, db->sm_count, db->stream);
+    rc = topk_device(ws->out.p, nout, kk, ws->tk_vals.p, ws->tk_idx.p, ws->tk_ws.p, db->sm_count, ws->stream);
     if (rc) return rc;
-    db->stats[0] += 9;
+    ws->stats[0] += 9;
     std::vector<int32_t> v((size_t)kk), ix((size_t)kk);
-    CU(cudaMemcpyAsync(v.data(), db->tk_vals.p, (size_t)kk * sizeof(int32_t), cudaMemcpyDeviceToHost, db->stream));
-    CU(cudaMemcpyAsync(ix.data(), db->tk_idx.p, (size_t)kk * sizeof(int32_t), cudaMemcpyDeviceToHost, db->stream));
-    CU(cudaEventRecord(db->ev1, db->stream));
-    CU(cudaStreamSynchronize(db->stream));
+    CU(cudaMemcpyAsync(v.data(), ws->tk_vals.p, (size_t)kk * sizeof(int32_t), cudaMemcpyDeviceToHost, ws->stream));
+    CU(cudaMemcpyAsync(ix.data(), ws->tk_idx.p, (size_t)kk * sizeof(int32_t), cudaMemcpyDeviceToHost, ws->stream));
+    CU(cudaEventRecord(ws->ev1, ws->stream));
+    CU(cudaEventRecord(ws->ev_free, ws->stream));
+    CU(cudaStreamSynchronize(ws->stream));
     float ms = 0;
-    CU(cudaEventElapsedTime(&ms, db->ev0, db->ev1));
-    db->stats[4] = (int64_t)(ms * 1000.0f);
+    CU(cudaEventElapsedTime(&ms, ws->ev0, ws->ev1));
+    ws->stats[4] = (int64_t)(ms * 1000.0f);
     // the k hits: score descending, ties by ascending database index
     std::vector<int32_t> order((size_t)kk);
     std::iota(order.begin(), order.end(), 0);
@@ -1070,6 +1365,8 @@ extern "C" int opalSearchDatabase(unsigned char query[], int queryLength, unsign
     if (!db || !dbSeqLengths || !results) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null argument");
     int device = 0;
     if (pyopal_cuda_device_count() <= 0) return fail(OPAL_ERR_NO_SIMD_SUPPORT, "no CUDA device available");
+    // the calling thread's current device, like any CUDA library entered without a handle; the Python layer selects
+    // its default device (PYOPAL_CUDA_DEVICE / LOCAL_RANK) before this call
     cudaGetDevice(&device);
     pyopal_cuda_db* h = nullptr;
     int rc = pyopal_cuda_db_create_from_pointers(device, (const unsigned char* const*)db, dbSeqLengths, dbLength,

@@ -69,6 +69,8 @@ struct KParams {
     int ovf_thresh;           // 16-bit rung, SW: running max >= this => rescore at 32 bit
     // results
     int32_t* out;             // scores in database order, entry (index - out_start)
+    int32_t* out_q;           // END kernels: end cell (query row, target column), same indexing
+    int32_t* out_t;
     int64_t out_start, out_end;
     int32_t* ovf_list;        // (pair << 1) | half of overflowed targets
     int32_t* ovf_count;
@@ -185,6 +187,49 @@ template <int W> struct CellConsts {
     }
 };
 
+// END mode (score + end cell) in the 16-bit rung, local alignment.  The end cell of Smith-Waterman is the FIRST
+// maximum in (target column, query row) order (oracle/opal_oracle.c dp_end: `h > best`, columns outer).  A thread
+// sees the columns of its K-row strip in ascending order, so it keeps one candidate per target (value, column,
+// row) and replaces it when its strip's column maximum `cm` beats it -- or, in a later pass, ties it at an earlier
+// column.  The row is looked up among the K registers only in that case: a divergent, rare path.  To keep it rare
+// `thr` carries the best value any lane of the group has seen for the target (one butterfly shuffle per step):
+// a strip maximum below it cannot be the target's maximum and is not even looked at.  The group's candidates are
+// merged (value desc, column asc, row asc) when the target is done.
+struct EndTrack {
+    uint32_t thr;            // packed: best value known for the two targets (biased), >= bias + 1
+    int bv0, bc0, bi0;       // candidate of the low-half target: biased value, column, tile row
+    int bv1, bc1, bi1;       // high half
+};
+
+template <int K>
+__device__ __forceinline__ void end_event(const uint32_t (&Gl)[K], uint32_t cm, EndTrack& T, int j, int rowbase, int go,
+                                          bool c0, bool c1) {
+    // between the sweeps Gl[r] holds M(r) - open in each half
+    if (c0) {
+        const int v = (int)(cm & 0xffffu);
+        if (v > T.bv0 || (v == T.bv0 && j < T.bc0)) {
+            const unsigned want = (unsigned)(v - go);
+            int row = 0;
+#pragma unroll
+            for (int r = K - 1; r >= 0; --r)
+                if ((Gl[r] & 0xffffu) == want) row = r;
+            T.bv0 = v; T.bc0 = j; T.bi0 = rowbase + row;
+        }
+    }
+    if (c1) {
+        const int v = (int)(cm >> 16);
+        if (v > T.bv1 || (v == T.bv1 && j < T.bc1)) {
+            const unsigned want = (unsigned)(v - go);
+            int row = 0;
+#pragma unroll
+            for (int r = K - 1; r >= 0; --r)
+                if ((Gl[r] >> 16) == want) row = r;
+            T.bv1 = v; T.bc1 = j; T.bi1 = rowbase + row;
+        }
+    }
+    T.thr = __vmaxu2(T.thr, cm);
+}
+
 // One column of K rows held by one thread.  In: E, Gl = (E, H - open) of the
 // previous column, upGprev = H - open of the row above in the previous column,
 // F / Gup = (F, H - open) of the row above in this column.  Out: E, Gl of this
@@ -194,14 +239,18 @@ template <int W> struct CellConsts {
 // penalised top border (re-opening a gap is then cheaper than extending it, so their E path beats the border
 // value); the thread that holds the LAST padding row (register `fixrow`) overwrites its output with the border
 // H[-1][j] - open (`fixG`) and an empty F, which is exactly what the first query row must see.
-template <int K, int W, bool LOCAL, bool PSMEM, bool WIDE, bool TDADD, bool SHORTF_ = (W == 16), bool BFIX = false>
+template <int K, int W, bool LOCAL, bool PSMEM, bool WIDE, bool TDADD, bool SHORTF_ = (W == 16), bool BFIX = false,
+          bool END = false>
 __device__ __forceinline__ void column_update(const KParams& P, const int8_t* prof, unsigned t0, unsigned t1, int pslot,
                                               const CellConsts<W>& C, typename Val<W>::T (&E)[K],
                                               typename Val<W>::T (&Gl)[K], typename Val<W>::T upGprev,
                                               typename Val<W>::T& F, typename Val<W>::T& Gup,
                                               typename Val<W>::T& best, int fixrow = -1,
-                                              typename Val<W>::T fixG = 0) {
+                                              typename Val<W>::T fixG = 0, EndTrack* track = nullptr, int col = 0,
+                                              int rowbase = 0) {
     static_assert(!BFIX || !SHORTF_, "the border fix lives in the long F chain");
+    static_assert(!END || (W == 16 && SHORTF_ && LOCAL), "end-cell tracking: 16-bit rung, local alignment");
+    typename Val<W>::T cm = C.FLOOR;  // END: maximum of this column over the thread's rows
     typedef Val<W> V;
     typedef typename V::T val_t;
     constexpr bool ADDPATH = TDADD || (W == 32);
@@ -244,12 +293,19 @@ __device__ __forceinline__ void column_update(const KParams& P, const int8_t* pr
             }
             if (SHORTF) {
                 // F never sets a new maximum, so the running best only looks at M
-                if (LOCAL) best = V::max2(best, M);
+                if (END) cm = V::max2(cm, M);
+                else if (LOCAL) best = V::max2(best, M);
                 Gl[r] = V::add(M, NEGOPEN, one);         // M - open
             } else {
                 Gl[r] = M;
             }
         }
+    }
+    if constexpr (END) {
+        // rare: this strip's column maximum reaches the best known for one of the two targets
+        const uint32_t x = __vmaxu2((uint32_t)cm, track->thr) ^ (uint32_t)cm;  // half == 0 <=> cm >= thr there
+        const bool c0 = (x & 0xffffu) == 0u, c1 = (x >> 16) == 0u;
+        if (c0 || c1) end_event<K>(Gl, (uint32_t)cm, *track, col, rowbase, P.go, c0, c1);
     }
     // ---- sweep 2, top-down: the F chain, H, G = H - open
     if (SHORTF) {
@@ -279,9 +335,10 @@ __device__ __forceinline__ void column_update(const KParams& P, const int8_t* pr
 // TDADD: every profile entry (S + open, padding included) is >= 0, so the
 // 16-bit rung may form Hdiag + S with a 32-bit IMAD; otherwise that add stays
 // in the packed adder of VIADDMNMX.  (Ignored by the 32-bit rung.)
-template <int K, int W, bool LOCAL, bool PSMEM, bool WIDE = false, bool TDADD = true, bool BFIX = false>
+template <int K, int W, bool LOCAL, bool PSMEM, bool WIDE = false, bool TDADD = true, bool BFIX = false, bool END = false>
 __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KParams P) {
     static_assert(!BFIX || (W == 32 && !LOCAL), "border fix: 32-bit rung, NW");
+    static_assert(!END || W == 16, "end-cell tracking lives in the 16-bit rung");
     static_assert(K % 4 == 0, "K must be a multiple of 4");
     static_assert(!WIDE || (W == 32 && !PSMEM), "wide profile: 32-bit rung, global memory only");
     typedef Val<W> V;
@@ -343,6 +400,12 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
 
         val_t best = FLOOR;                   // SW: running max of H
         int res0 = INT_MIN, res1 = INT_MIN;   // NW/HW/OV (true values)
+        // END mode: SW candidates (EndTrack); HW/OV: column of the last-row maximum, best of the last column
+        EndTrack track;
+        track.thr = (uint32_t)V::splat(B + 1);
+        track.bv0 = track.bv1 = B; track.bc0 = track.bc1 = -1; track.bi0 = track.bi1 = 0;
+        int lc0 = -1, lc1 = -1, cv0 = INT_MIN, cv1 = INT_MIN, ci0 = -1, ci1 = -1;
+        int sh_d = 1;                          // rotating butterfly distance for sharing track.thr
 
         for (int pass = 0; pass < P.npass; ++pass) {
             const int rowbase = pass * T + p * K;  // tile row of register 0
@@ -375,6 +438,11 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
             for (int s = 0; s < nsteps; ++s) {
                 val_t upG = __shfl_up_sync(FULL, Gout, 1, G);
                 val_t upF = __shfl_up_sync(FULL, Fout, 1, G);
+                if (END && LOCAL) {
+                    track.thr = __vmaxu2(track.thr, __shfl_xor_sync(FULL, track.thr, sh_d));
+                    sh_d <<= 1;
+                    if (sh_d >= G) sh_d = 1;
+                }
                 const int j = s - p;
                 const bool active = (j >= 0) && (j < ncol);
                 const unsigned code = code_nx;
@@ -410,7 +478,8 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
                             P, prof, t0, t1, (pass * G + p) * P.kstride, C, E, Gl, upGprev, F, Gup, best, mine ? fr : -1,
                             V::splat(-(P.go + j * P.ge) - P.go + B));
                     } else {
-                        column_update<K, W, LOCAL, PSMEM, WIDE, TDADD>(P, prof, t0, t1, (pass * G + p) * P.kstride, C, E, Gl, upGprev, F, Gup, best);
+                        column_update<K, W, LOCAL, PSMEM, WIDE, TDADD, (W == 16), false, (END && LOCAL)>(
+                            P, prof, t0, t1, (pass * G + p) * P.kstride, C, E, Gl, upGprev, F, Gup, best, -1, 0, &track, j, rowbase);
                     }
                     Gout = Gup;
                     Fout = F;
@@ -426,6 +495,10 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
                             if (P.mode == MODE_NW) {
                                 if (j == len0 - 1) res0 = h0;
                                 if (j == len1 - 1) res1 = h1;
+                            } else if (END) {
+                                // first maximum of the last row (oracle: `H[m - 1] > best`, columns ascending)
+                                if (j < len0 && h0 > res0) { res0 = h0; lc0 = j; }
+                                if (j < len1 && h1 > res1) { res1 = h1; lc1 = j; }
                             } else {
                                 if (j < len0) res0 = max(res0, h0);
                                 if (j < len1) res1 = max(res1, h1);
@@ -437,8 +510,15 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
 #pragma unroll
                         for (int r = 0; r < K; ++r) {
                             if (rowbase + r >= P.padtop) {
-                                if (j == len0 - 1) res0 = max(res0, V::lo(Gl[r]) + P.go - B);
-                                if (W == 16 && j == len1 - 1) res1 = max(res1, V::hi(Gl[r]) + P.go - B);
+                                if (END) {
+                                    // lowest row of the last-column maximum (rows ascend within a thread)
+                                    const int v0 = V::lo(Gl[r]) + P.go - B, v1 = V::hi(Gl[r]) + P.go - B;
+                                    if (j == len0 - 1 && v0 > cv0) { cv0 = v0; ci0 = rowbase + r - P.padtop; }
+                                    if (W == 16 && j == len1 - 1 && v1 > cv1) { cv1 = v1; ci1 = rowbase + r - P.padtop; }
+                                } else {
+                                    if (j == len0 - 1) res0 = max(res0, V::lo(Gl[r]) + P.go - B);
+                                    if (W == 16 && j == len1 - 1) res1 = max(res1, V::hi(Gl[r]) + P.go - B);
+                                }
                             }
                         }
                     }
@@ -449,11 +529,49 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
 
         // reduce over the group, lane p == 0 publishes
         int r0, r1;
-        if (LOCAL) { r0 = V::lo(best) - B; r1 = V::hi(best) - B; }
-        else { r0 = res0; r1 = res1; }
-        for (int d = 1; d < G; d <<= 1) {
-            r0 = max(r0, __shfl_xor_sync(FULL, r0, d));
-            r1 = max(r1, __shfl_xor_sync(FULL, r1, d));
+        int eq0 = -1, et0 = -1, eq1 = -1, et1 = -1;   // END: end cell (query row, target column)
+        if (END && LOCAL) {
+            for (int d = 1; d < G; d <<= 1) {
+                const int ov0 = __shfl_xor_sync(FULL, track.bv0, d), oc0 = __shfl_xor_sync(FULL, track.bc0, d),
+                          oi0 = __shfl_xor_sync(FULL, track.bi0, d);
+                if (ov0 > track.bv0 || (ov0 == track.bv0 && (oc0 < track.bc0 || (oc0 == track.bc0 && oi0 < track.bi0)))) {
+                    track.bv0 = ov0; track.bc0 = oc0; track.bi0 = oi0;
+                }
+                const int ov1 = __shfl_xor_sync(FULL, track.bv1, d), oc1 = __shfl_xor_sync(FULL, track.bc1, d),
+                          oi1 = __shfl_xor_sync(FULL, track.bi1, d);
+                if (ov1 > track.bv1 || (ov1 == track.bv1 && (oc1 < track.bc1 || (oc1 == track.bc1 && oi1 < track.bi1)))) {
+                    track.bv1 = ov1; track.bc1 = oc1; track.bi1 = oi1;
+                }
+            }
+            r0 = track.bv0 - B; r1 = track.bv1 - B;
+            if (track.bc0 >= 0) { eq0 = track.bi0 - P.padtop; et0 = track.bc0; }   // score 0: no alignment, (-1, -1)
+            if (track.bc1 >= 0) { eq1 = track.bi1 - P.padtop; et1 = track.bc1; }
+        } else if (END) {
+            // NW: the corner.  HW: first last-row maximum (held by the group's last lane).  OV: the last row,
+            // then the last column where it is strictly better (oracle/opal_oracle.c dp_end).
+            const int lv0 = __shfl_sync(FULL, res0, G - 1, G), lv1 = __shfl_sync(FULL, res1, G - 1, G);
+            const int lcol0 = __shfl_sync(FULL, lc0, G - 1, G), lcol1 = __shfl_sync(FULL, lc1, G - 1, G);
+            r0 = lv0; r1 = lv1;
+            eq0 = eq1 = P.Lq - 1;
+            if (P.mode == MODE_NW) { et0 = len0 - 1; et1 = len1 - 1; }
+            else { et0 = lcol0; et1 = lcol1; }
+            if (P.mode == MODE_OV) {
+                for (int d = 1; d < G; d <<= 1) {
+                    const int ov0 = __shfl_xor_sync(FULL, cv0, d), oi0 = __shfl_xor_sync(FULL, ci0, d);
+                    if (ov0 > cv0 || (ov0 == cv0 && oi0 < ci0)) { cv0 = ov0; ci0 = oi0; }
+                    const int ov1 = __shfl_xor_sync(FULL, cv1, d), oi1 = __shfl_xor_sync(FULL, ci1, d);
+                    if (ov1 > cv1 || (ov1 == cv1 && oi1 < ci1)) { cv1 = ov1; ci1 = oi1; }
+                }
+                if (cv0 > r0) { r0 = cv0; eq0 = ci0; et0 = len0 - 1; }
+                if (cv1 > r1) { r1 = cv1; eq1 = ci1; et1 = len1 - 1; }
+            }
+        } else {
+            if (LOCAL) { r0 = V::lo(best) - B; r1 = V::hi(best) - B; }
+            else { r0 = res0; r1 = res1; }
+            for (int d = 1; d < G; d <<= 1) {
+                r0 = max(r0, __shfl_xor_sync(FULL, r0, d));
+                r1 = max(r1, __shfl_xor_sync(FULL, r1, d));
+            }
         }
         if (have && p == 0) {
             if (W == 16) {
@@ -466,11 +584,17 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
                 const bool ovb = LOCAL && (r1 >= P.ovf_thresh || ova);
                 if (ina) {
                     if (ova) P.ovf_list[atomicAdd(P.ovf_count, 1)] = pair << 1;
-                    else P.out[ia - P.out_start] = r0;
+                    else {
+                        P.out[ia - P.out_start] = r0;
+                        if (END) { P.out_q[ia - P.out_start] = eq0; P.out_t[ia - P.out_start] = et0; }
+                    }
                 }
                 if (inb) {
                     if (ovb) P.ovf_list[atomicAdd(P.ovf_count, 1)] = (pair << 1) | 1;
-                    else P.out[ib - P.out_start] = r1;
+                    else {
+                        P.out[ib - P.out_start] = r1;
+                        if (END) { P.out_q[ib - P.out_start] = eq1; P.out_t[ib - P.out_start] = et1; }
+                    }
                 }
             } else {
                 const int ix = P.pair_idx[2 * pair + half];
@@ -489,6 +613,9 @@ typedef void (*search_kernel_t)(const KParams);
 // defined in kernels_w*_l*.cu; nullptr when the combination is not built
 search_kernel_t get_search_kernel_w16_l1(int K, bool psmem, bool tdadd);
 search_kernel_t get_search_kernel_w16_l0(int K, bool psmem, bool tdadd);
+// the same with end-cell tracking (END mode): kernels_w16_l*_end.cu
+search_kernel_t get_search_kernel_w16_l1_end(int K, bool psmem, bool tdadd);
+search_kernel_t get_search_kernel_w16_l0_end(int K, bool psmem, bool tdadd);
 search_kernel_t get_search_kernel_w32_l1(int K, bool psmem);
 search_kernel_t get_search_kernel_w32_l0(int K, bool psmem);
 search_kernel_t get_search_kernel_wide(bool local);  // K = 32, W = 32

@@ -571,15 +571,13 @@ typedef void (*pair_kernel_t)(const PairParams);
 // and 1090 + 42 K at C = 4, a band follows ~72 steps behind the one above it, a step issues about 8.6 K C + 60
 // (+ 40 at C = 4) instructions and a full SM sustains ~2.2 of them per clock; the two terms add because the long
 // target's warps share their SMs with everybody else's.
-int choose_pair_K(int rows, int64_t njobs, int64_t sum_n, int64_t nmax, int64_t table_jobs, int sm_count, int gran, int* C) {
+int choose_pair_K(const Tuning& tune, int rows, int64_t njobs, int64_t sum_n, int64_t nmax, int64_t table_jobs, int sm_count, int gran, int* C) {
     *C = 1;
     // `gran`: K comes in steps of 2 for the locate kernels, 4 for the fill kernel (four rows per 32-bit store)
     const int kfit = std::min(32, std::max(4, gran * ((rows + 32 * gran - 1) / (32 * gran))));
-    const char* env = getenv("PYOPAL_CUDA_PAIR_K");
-    const char* envc = getenv("PYOPAL_CUDA_PAIR_C");
-    if (env && atoi(env) >= 4) {
-        const int k = std::min(32, atoi(env) / gran * gran);
-        if (envc && atoi(envc) == 4 && k <= 8) *C = 4;
+    if (tune.pair_k >= 4) {
+        const int k = std::min(32, tune.pair_k / gran * gran);
+        if (tune.pair_c == 4 && k <= 8) *C = 4;
         return k;
     }
     double best = 1e300;
@@ -629,15 +627,15 @@ pair_kernel_t pair_kernel_for(int k, int c) {
 }
 
 // Reset the band bookkeeping for `P.njobs` jobs of at most `rows` query rows and launch.
-int launch_pair(pyopal_cuda_db* db, pair_kernel_t fn, PairParams P, int rows, int K, cudaStream_t st) {
+int launch_pair(pyopal_cuda_db* db, Workspace* ws, pair_kernel_t fn, PairParams P, int rows, int K, cudaStream_t st) {
     if (P.njobs <= 0) return 0;
     P.maxpass = std::max(1, (rows + 32 * K - 1) / (32 * K));
     const int64_t ntasks = (int64_t)P.njobs * P.maxpass;
     if (ntasks >= ((int64_t)1 << 31) - 1024) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "too many target x band tasks");
     P.prog = P.done = P.cut = P.slots = nullptr;
     if (P.maxpass > 1) {
-        if (db->pd_team.reserve((size_t)(6 * ntasks + 2 * (int64_t)P.njobs + 16))) return PYOPAL_CUDA_ERR_NOMEM;
-        P.prog = db->pd_team.p;
+        if (ws->pd_team.reserve((size_t)(6 * ntasks + 2 * (int64_t)P.njobs + 16))) return PYOPAL_CUDA_ERR_NOMEM;
+        P.prog = ws->pd_team.p;
         P.done = P.prog + ntasks;
         P.cut = P.done + P.njobs;
         P.slots = P.cut + P.njobs;
@@ -652,7 +650,7 @@ int launch_pair(pyopal_cuda_db* db, pair_kernel_t fn, PairParams P, int rows, in
     int64_t grid = std::min<int64_t>((int64_t)db->sm_count * per_sm, (ntasks + 3) / 4);
     fn<<<(unsigned)std::max<int64_t>(grid, 1), 128, 0, st>>>(P);
     CU(cudaGetLastError());
-    db->stats[0]++;
+    ws->stats[0]++;
     return 0;
 }
 
@@ -682,8 +680,29 @@ void degenerate_end(int mode, int m, int n, int go, int ge, int* score, int* eq,
 
 }  // namespace
 
-int pyopal_end_full_search(pyopal_cuda_db* db, const unsigned char* query, int Lq, int go, int ge, const int* M,
-                           int A, int searchType, int mode, int64_t start, int64_t end, int32_t* scores,
+// host-built forward jobs for the sorted positions in `pos` (targets the packed kernel leaves to this file)
+static void host_forward_jobs(const pyopal_cuda_db* db, const int32_t* pos, size_t count, bool packed_entries, int Lq,
+                              int64_t start, std::vector<PairJob>& out) {
+    out.clear();
+    out.reserve(count);
+    for (size_t i = 0; i < count; i++) {
+        const int32_t x = pos[i];  // 2 * pair + half either way
+        (void)packed_entries;
+        PairJob jb;
+        jb.tbase = db->h_pair_off[(size_t)(x >> 1)];
+        jb.tb_off = 0;
+        jb.half = x & 1;
+        jb.q0 = 0; jb.qdir = 1; jb.m = Lq;
+        jb.t0 = 0; jb.tdir = 1; jb.n = db->h_pair_len[(size_t)x];
+        jb.expect = 0;
+        jb.slot = (int32_t)(db->h_pair_idx[(size_t)x] - start);
+        jb.ops_end = 0;
+        out.push_back(jb);
+    }
+}
+
+int pyopal_end_full_search(pyopal_cuda_db* db, Workspace* ws, const unsigned char* query, int Lq, int go, int ge,
+                           const int* M, int A, int searchType, int mode, int64_t start, int64_t end, int32_t* scores,
                            int32_t* endQ, int32_t* endT, int32_t* startQ, int32_t* startT, unsigned char* ops,
                            const int64_t* ops_offsets, int32_t* ops_len) {
     const int64_t nout = end - start;
@@ -692,9 +711,15 @@ int pyopal_end_full_search(pyopal_cuda_db* db, const unsigned char* query, int L
     if (!endQ || !endT) return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null end-location output");
     if (full && (!startQ || !startT || !ops || !ops_offsets || !ops_len))
         return fail(PYOPAL_CUDA_ERR_ARGUMENT, "null alignment output");
-    for (int i = 0; i < 12; i++) db->stats[i] = 0;
-    cudaStream_t st = db->stream;
-    CU(cudaEventRecord(db->ev0, st));
+    for (int i = 0; i < 12; i++) ws->stats[i] = 0;
+    cudaStream_t st = ws->stream;
+    if (ws->used) CU(cudaStreamWaitEvent(st, ws->ev_free, 0));
+    ws->used = true;
+    struct Mark {
+        Workspace* w; cudaStream_t s;
+        ~Mark() { cudaEventRecord(w->ev_free, s); }
+    } mark{ws, st};
+    CU(cudaEventRecord(ws->ev0, st));
 
     // 32-bit overflow cannot happen below this bound (values stay exact otherwise)
     {
@@ -716,52 +741,135 @@ int pyopal_end_full_search(pyopal_cuda_db* db, const unsigned char* query, int L
     memset(&P, 0, sizeof(P));
 
     if (device_work) {
-        if (db->pd_i32.reserve((size_t)nout * 6 + 16)) return PYOPAL_CUDA_ERR_NOMEM;
-        if (db->pd_jobs.reserve((size_t)njobs * sizeof(PairJob))) return PYOPAL_CUDA_ERR_NOMEM;
-        if (db->query.reserve((size_t)Lq)) return PYOPAL_CUDA_ERR_NOMEM;
-        d_res = db->pd_i32.p;
-        d_jobs = reinterpret_cast<PairJob*>(db->pd_jobs.p);
-        int64_t sum_n = 0, nmax = 0, nlive = 0;
-        for (int64_t k = 0; k < nout; k++) {
-            const int64_t len = db->h_lengths[(size_t)(start + k)];
-            sum_n += len; nmax = std::max(nmax, len); nlive += (len > 0);
-        }
-        int Cc = 1;
-        const int K = choose_pair_K(Lq, nlive, sum_n, nmax, njobs, db->sm_count, 2, &Cc);
-        pair_kernel_t kloc = (cfg_for_mode(mode).endrule == END_ALL) ? pair_kernel_for<KIND_ALL>(K, Cc)
-                                                                      : pair_kernel_for<KIND_EDGE>(K, Cc);
-        db->stats[5] = Cc;
-        db->stats[6] = K;
-        db->stats[7] = (Lq + 32 * K - 1) / (32 * K);
-        if (Lq > 32 * K) {
-            if (db->bnd32H.reserve((size_t)db->ncols * 2 + 16) || db->bnd32F.reserve((size_t)db->ncols * 2 + 16))
-                return PYOPAL_CUDA_ERR_NOMEM;
-        }
-        CU(cudaMemcpyAsync(db->query.p, query, (size_t)Lq, cudaMemcpyHostToDevice, st));
-        CU(cudaMemcpyAsync(db->d_matrix, M, (size_t)A * A * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+        if (ws->pd_i32.reserve((size_t)nout * 6 + 64)) return PYOPAL_CUDA_ERR_NOMEM;
+        if (ws->pd_query.reserve((size_t)Lq + 32 * 32 * 4 + 16)) return PYOPAL_CUDA_ERR_NOMEM;
+        d_res = ws->pd_i32.p;
+        int32_t* d_matrix = reinterpret_cast<int32_t*>(ws->pd_query.p);
+        uint8_t* d_query = ws->pd_query.p + 32 * 32 * 4;
+        CU(cudaMemcpyAsync(d_query, query, (size_t)Lq, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(d_matrix, M, (size_t)A * A * sizeof(int32_t), cudaMemcpyHostToDevice, st));
         int32_t* d_ctl = d_res + (size_t)nout * 6;
-        CU(cudaMemsetAsync(d_ctl, 0, 16 * sizeof(int32_t), st));
+        CU(cudaMemsetAsync(d_ctl, 0, 32 * sizeof(int32_t), st));
         fill_i32<<<256, 256, 0, st>>>(d_res, nout * 6, -1);
-        const int tpb = 256;
-        make_forward_jobs<<<(njobs + tpb - 1) / tpb, tpb, 0, st>>>(d_jobs, njobs, db->d_pair_off, db->d_pair_len,
-                                                                  db->d_pair_idx, Lq, start, end);
         CU(cudaGetLastError());
-        P.stream = db->d_stream; P.query = db->query.p; P.matrix = db->d_matrix;
+        P.stream = db->d_stream; P.query = d_query; P.matrix = d_matrix;
         P.A = A; P.go = go; P.ge = ge;
-        P.jobs = d_jobs; P.njobs = njobs; P.counter = d_ctl; P.err = d_ctl + 1;
-        P.bndH = reinterpret_cast<int32_t*>(db->bnd32H.p); P.bndF = reinterpret_cast<int32_t*>(db->bnd32F.p);
+        P.err = d_ctl + 1;
         const ModeCfg c = cfg_for_mode(mode);
         P.top_free = c.top_free; P.left_free = c.left_free; P.floor0 = c.floor0; P.endrule = c.endrule; P.anchored = 0;
         P.out_score = d_res; P.out_q = d_res + nout; P.out_t = d_res + 2 * nout;
-        int rc = launch_pair(db, kloc, P, Lq, K, st);
-        if (rc) return rc;
+        const int tpb = 256;
+
+        // locate launch over a host-built job list (the 32-bit kernels of this file)
+        std::vector<PairJob> hjobs0;
+        auto locate = [&](const std::vector<PairJob>& jobs, size_t job_off_bytes, int32_t* counter, cudaStream_t s2) -> int {
+            if (jobs.empty()) return 0;
+            int64_t sum_n = 0, nmax = 0;
+            for (const PairJob& jb : jobs) { sum_n += jb.n; nmax = std::max<int64_t>(nmax, jb.n); }
+            int Cc = 1;
+            const int K = choose_pair_K(db->tune, Lq, (int64_t)jobs.size(), sum_n, nmax, (int64_t)jobs.size(), db->sm_count, 2, &Cc);
+            pair_kernel_t kloc = (c.endrule == END_ALL) ? pair_kernel_for<KIND_ALL>(K, Cc) : pair_kernel_for<KIND_EDGE>(K, Cc);
+            ws->stats[5] = Cc; ws->stats[6] = K; ws->stats[7] = (Lq + 32 * K - 1) / (32 * K);
+            if (Lq > 32 * K)
+                if (ws->bnd32H.reserve((size_t)db->ncols * 2 + 16) || ws->bnd32F.reserve((size_t)db->ncols * 2 + 16))
+                    return PYOPAL_CUDA_ERR_NOMEM;
+            PairJob* dj = reinterpret_cast<PairJob*>(ws->pd_jobs.p + job_off_bytes);
+            CU(cudaMemcpyAsync(dj, jobs.data(), jobs.size() * sizeof(PairJob), cudaMemcpyHostToDevice, s2));
+            PairParams Q = P;
+            Q.jobs = dj; Q.njobs = (int)jobs.size(); Q.counter = counter;
+            Q.bndH = reinterpret_cast<int32_t*>(ws->bnd32H.p); Q.bndF = reinterpret_cast<int32_t*>(ws->bnd32F.p);
+            return launch_pair(db, ws, kloc, Q, Lq, K, s2);
+        };
+
+        bool packed_done = false;
+        if (!db->tune.no_end16) {
+            // ---- forward pass in the packed 16-bit kernels (kernels.cuh, END): score + end cell at score-mode
+            // cost; what they cannot hold (the longest targets, the static 32-bit rung, 16-bit overflows) is
+            // located by this file's 32-bit kernel, concurrently on a high-priority stream
+            EndPlan ep;
+            ep.d_endq = d_res + nout; ep.d_endt = d_res + 2 * nout;
+            // reserve the job area first: [all-target jobs (full mode) | spill jobs | overflow jobs]
+            if (ws->pd_jobs.reserve((size_t)njobs * sizeof(PairJob) * 2 + 4096)) return PYOPAL_CUDA_ERR_NOMEM;
+            CU(cudaEventRecord(ws->ev_aux0, st));
+            int rc = enqueue_score_search_ex(db, ws, query, Lq, go, ge, M, A, mode, start, end, d_res, st, &ep);
+            if (rc) return rc;
+            packed_done = true;
+            if (!ep.spill.empty()) {
+                host_forward_jobs(db, ep.spill.data(), ep.spill.size(), false, Lq, start, hjobs0);
+                CU(cudaStreamWaitEvent(ws->side2, ws->ev_aux0, 0));
+                rc = locate(hjobs0, (size_t)njobs * sizeof(PairJob), d_ctl, ws->side2);
+                if (rc) return rc;
+                CU(cudaEventRecord(ws->ev_aux1, ws->side2));
+                CU(cudaStreamWaitEvent(st, ws->ev_aux1, 0));
+            }
+            if (ep.packed && mode == MODE_SW) {
+                // 16-bit overflows: the list was produced on the device; fetch it and locate those at 32 bit
+                int32_t novf = 0;
+                CU(cudaMemcpyAsync(&novf, ep.d_ovf_count, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+                CU(cudaStreamSynchronize(st));
+                ws->stats[3] = novf;
+                if (novf > 0) {
+                    std::vector<int32_t> ovf((size_t)novf);
+                    CU(cudaMemcpy(ovf.data(), ep.d_ovf, (size_t)novf * sizeof(int32_t), cudaMemcpyDeviceToHost));
+                    std::vector<PairJob> hj;
+                    host_forward_jobs(db, ovf.data(), ovf.size(), true, Lq, start, hj);
+                    rc = locate(hj, (size_t)njobs * sizeof(PairJob) + hjobs0.size() * sizeof(PairJob), d_ctl + 8, st);
+                    if (rc) return rc;
+                }
+            }
+            d_jobs = reinterpret_cast<PairJob*>(ws->pd_jobs.p);
+            if (full && mode != MODE_NW) {
+                make_forward_jobs<<<(njobs + tpb - 1) / tpb, tpb, 0, st>>>(d_jobs, njobs, db->d_pair_off, db->d_pair_len,
+                                                                          db->d_pair_idx, Lq, start, end);
+                CU(cudaGetLastError());
+            }
+        }
+        if (!packed_done) {
+            if (ws->pd_jobs.reserve((size_t)njobs * sizeof(PairJob))) return PYOPAL_CUDA_ERR_NOMEM;
+            d_jobs = reinterpret_cast<PairJob*>(ws->pd_jobs.p);
+            int64_t sum_n = 0, nmax = 0, nlive = 0;
+            for (int64_t k = 0; k < nout; k++) {
+                const int64_t len = db->h_lengths[(size_t)(start + k)];
+                sum_n += len; nmax = std::max(nmax, len); nlive += (len > 0);
+            }
+            int Cc = 1;
+            const int K = choose_pair_K(db->tune, Lq, nlive, sum_n, nmax, njobs, db->sm_count, 2, &Cc);
+            pair_kernel_t kloc = (c.endrule == END_ALL) ? pair_kernel_for<KIND_ALL>(K, Cc) : pair_kernel_for<KIND_EDGE>(K, Cc);
+            ws->stats[5] = Cc; ws->stats[6] = K; ws->stats[7] = (Lq + 32 * K - 1) / (32 * K);
+            if (Lq > 32 * K)
+                if (ws->bnd32H.reserve((size_t)db->ncols * 2 + 16) || ws->bnd32F.reserve((size_t)db->ncols * 2 + 16))
+                    return PYOPAL_CUDA_ERR_NOMEM;
+            make_forward_jobs<<<(njobs + tpb - 1) / tpb, tpb, 0, st>>>(d_jobs, njobs, db->d_pair_off, db->d_pair_len,
+                                                                      db->d_pair_idx, Lq, start, end);
+            CU(cudaGetLastError());
+            PairParams Q = P;
+            Q.jobs = d_jobs; Q.njobs = njobs; Q.counter = d_ctl;
+            Q.bndH = reinterpret_cast<int32_t*>(ws->bnd32H.p); Q.bndF = reinterpret_cast<int32_t*>(ws->bnd32F.p);
+            int rc = launch_pair(db, ws, kloc, Q, Lq, K, st);
+            if (rc) return rc;
+        }
         if (full && mode != MODE_NW) {
+            // reverse pass over every target, anchored at its end cell (the band-team kernel of this file)
+            int64_t sum_n = 0, nmax = 0, nlive = 0;
+            for (int64_t k = 0; k < nout; k++) {
+                const int64_t len = db->h_lengths[(size_t)(start + k)];
+                sum_n += len; nmax = std::max(nmax, len); nlive += (len > 0);
+            }
+            int Cc = 1;
+            const int K = choose_pair_K(db->tune, Lq, nlive, sum_n, nmax, njobs, db->sm_count, 2, &Cc);
+            pair_kernel_t kloc = (c.endrule == END_ALL) ? pair_kernel_for<KIND_ALL>(K, Cc) : pair_kernel_for<KIND_EDGE>(K, Cc);
+            ws->stats[5] = Cc; ws->stats[6] = K; ws->stats[7] = (Lq + 32 * K - 1) / (32 * K);
+            if (Lq > 32 * K)
+                if (ws->bnd32H.reserve((size_t)db->ncols * 2 + 16) || ws->bnd32F.reserve((size_t)db->ncols * 2 + 16))
+                    return PYOPAL_CUDA_ERR_NOMEM;
             make_reverse_jobs<<<(njobs + tpb - 1) / tpb, tpb, 0, st>>>(d_jobs, njobs, d_res, d_res + nout, d_res + 2 * nout);
             CU(cudaGetLastError());
             PairParams R = P;
+            R.jobs = d_jobs; R.njobs = njobs; R.counter = d_ctl + 16;
+            R.bndH = reinterpret_cast<int32_t*>(ws->bnd32H.p); R.bndF = reinterpret_cast<int32_t*>(ws->bnd32F.p);
             R.top_free = 0; R.left_free = 0; R.floor0 = 0; R.anchored = 1;
             R.out_score = d_res + 3 * nout; R.out_q = d_res + 4 * nout; R.out_t = d_res + 5 * nout;
-            rc = launch_pair(db, kloc, R, Lq, K, st);
+            int rc = launch_pair(db, ws, kloc, R, Lq, K, st);
             if (rc) return rc;
         }
         CU(cudaMemcpyAsync(h_sc.data(), d_res, (size_t)nout * 4, cudaMemcpyDeviceToHost, st));
@@ -789,11 +897,11 @@ int pyopal_end_full_search(pyopal_cuda_db* db, const unsigned char* query, int L
         endT[k] = h_et[(size_t)k];
     }
     if (!full) {
-        CU(cudaEventRecord(db->ev1, st));
-        CU(cudaEventSynchronize(db->ev1));
+        CU(cudaEventRecord(ws->ev1, st));
+        CU(cudaEventSynchronize(ws->ev1));
         float ms = 0;
-        CU(cudaEventElapsedTime(&ms, db->ev0, db->ev1));
-        db->stats[4] = (int64_t)(ms * 1000.0f);
+        CU(cudaEventElapsedTime(&ms, ws->ev0, ws->ev1));
+        ws->stats[4] = (int64_t)(ms * 1000.0f);
         return 0;
     }
 
@@ -828,10 +936,7 @@ int pyopal_end_full_search(pyopal_cuda_db* db, const unsigned char* query, int L
     size_t free_b = 0, total_b = 0;
     CU(cudaMemGetInfo(&free_b, &total_b));
     const int64_t budget = std::max<int64_t>((int64_t)1 << 28, std::min<int64_t>((int64_t)(free_b / 2), (int64_t)8 << 30));
-    std::vector<int32_t> where;  // database index -> sorted position, built lazily
-    where.assign((size_t)db->n, -1);
-    for (size_t x = 0; x < db->h_pair_idx.size(); x++)
-        if (db->h_pair_idx[x] >= 0) where[(size_t)db->h_pair_idx[x]] = (int32_t)x;
+    const std::vector<int32_t>& where = db->h_where;  // database index -> sorted position
     // big rectangles first so that the dynamic scheduler starts them early
     std::stable_sort(todo.begin(), todo.end(), [](const Todo& a, const Todo& b) {
         return (int64_t)a.m * a.n > (int64_t)b.m * b.n;
@@ -871,38 +976,38 @@ int pyopal_end_full_search(pyopal_cuda_db* db, const unsigned char* query, int L
             p2++;
         }
         const int nb = (int)hjobs.size();
-        if (db->pd_jobs.reserve((size_t)nb * sizeof(PairJob)) || db->pd_tb.reserve((size_t)tb_bytes + 16) ||
-            db->pd_ops.reserve((size_t)ops_bytes + 16) || db->pd_i32.reserve((size_t)nb + 16))
+        if (ws->pd_jobs.reserve((size_t)nb * sizeof(PairJob)) || ws->pd_tb.reserve((size_t)tb_bytes + 16) ||
+            ws->pd_ops.reserve((size_t)ops_bytes + 16) || ws->pd_i32.reserve((size_t)nb + 16))
             return PYOPAL_CUDA_ERR_NOMEM;
-        d_jobs = reinterpret_cast<PairJob*>(db->pd_jobs.p);
-        int32_t* d_len = db->pd_i32.p;
+        d_jobs = reinterpret_cast<PairJob*>(ws->pd_jobs.p);
+        int32_t* d_len = ws->pd_i32.p;
         int32_t* d_ctl = d_len + nb;
         int Cc = 1;
-        const int K = choose_pair_K(maxm, nb, sum_tn, max_tn, nb, db->sm_count, 4, &Cc);
+        const int K = choose_pair_K(db->tune, maxm, nb, sum_tn, max_tn, nb, db->sm_count, 4, &Cc);
         pair_kernel_t kfill = pair_kernel_for<KIND_FILL>(K, Cc);
         if (maxm > 32 * K)
-            if (db->bnd32H.reserve((size_t)db->ncols * 2 + 16) || db->bnd32F.reserve((size_t)db->ncols * 2 + 16))
+            if (ws->bnd32H.reserve((size_t)db->ncols * 2 + 16) || ws->bnd32F.reserve((size_t)db->ncols * 2 + 16))
                 return PYOPAL_CUDA_ERR_NOMEM;
         CU(cudaMemcpyAsync(d_jobs, hjobs.data(), (size_t)nb * sizeof(PairJob), cudaMemcpyHostToDevice, st));
         CU(cudaMemsetAsync(d_ctl, 0, 16 * sizeof(int32_t), st));
         PairParams F = P;
-        F.stream = db->d_stream; F.query = db->query.p; F.matrix = db->d_matrix;
+        F.stream = db->d_stream; F.query = P.query; F.matrix = P.matrix;
         F.A = A; F.go = go; F.ge = ge;
         F.jobs = d_jobs; F.njobs = nb; F.counter = d_ctl; F.err = d_ctl + 1;
-        F.bndH = reinterpret_cast<int32_t*>(db->bnd32H.p); F.bndF = reinterpret_cast<int32_t*>(db->bnd32F.p);
+        F.bndH = reinterpret_cast<int32_t*>(ws->bnd32H.p); F.bndF = reinterpret_cast<int32_t*>(ws->bnd32F.p);
         F.top_free = 0; F.left_free = 0; F.floor0 = 0; F.endrule = END_CORNER; F.anchored = 0;
-        F.tb = db->pd_tb.p;
-        int rc = launch_pair(db, kfill, F, maxm, K, st);
+        F.tb = ws->pd_tb.p;
+        int rc = launch_pair(db, ws, kfill, F, maxm, K, st);
         if (rc) return rc;
-        walk_kernel<<<(nb + 63) / 64, 64, 0, st>>>(F, db->pd_ops.p, d_len);
+        walk_kernel<<<(nb + 63) / 64, 64, 0, st>>>(F, ws->pd_ops.p, d_len);
         CU(cudaGetLastError());
-        db->stats[0]++;
+        ws->stats[0]++;
         hlen.resize((size_t)nb + 2);
         hops.resize((size_t)ops_bytes + 1);
         CU(cudaMemcpyAsync(hlen.data(), d_len, (size_t)nb * 4, cudaMemcpyDeviceToHost, st));
         int32_t herr[2] = {0, 0};
         CU(cudaMemcpyAsync(herr, d_ctl, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-        CU(cudaMemcpyAsync(hops.data(), db->pd_ops.p, (size_t)ops_bytes, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(hops.data(), ws->pd_ops.p, (size_t)ops_bytes, cudaMemcpyDeviceToHost, st));
         CU(cudaStreamSynchronize(st));
         if (herr[1] != 0) return fail(PYOPAL_CUDA_ERR_INTERNAL, "traceback does not reproduce the forward score");
         for (int b = 0; b < nb; b++) {
@@ -913,10 +1018,10 @@ int pyopal_end_full_search(pyopal_cuda_db* db, const unsigned char* query, int L
         }
         pos = p2;
     }
-    CU(cudaEventRecord(db->ev1, st));
-    CU(cudaEventSynchronize(db->ev1));
+    CU(cudaEventRecord(ws->ev1, st));
+    CU(cudaEventSynchronize(ws->ev1));
     float ms = 0;
-    CU(cudaEventElapsedTime(&ms, db->ev0, db->ev1));
-    db->stats[4] = (int64_t)(ms * 1000.0f);
+    CU(cudaEventElapsedTime(&ms, ws->ev0, ws->ev1));
+    ws->stats[4] = (int64_t)(ms * 1000.0f);
     return 0;
 }

@@ -335,19 +335,53 @@ class BaseDatabase:
             i += 1
 
 
+class _PackedSequences:
+    """Read-only sequence view over a packed residue buffer (what `get_sequences` returns for a packed database)."""
+
+    __slots__ = ("buffer", "offsets", "lengths")
+
+    def __init__(self, buffer, offsets, lengths):
+        self.buffer, self.offsets, self.lengths = buffer, offsets, lengths
+
+    def __len__(self):
+        return len(self.lengths)
+
+    def __getitem__(self, index):
+        if isinstance(index, slice):
+            return [self[i] for i in range(*index.indices(len(self)))]
+        i = operator.index(index)
+        if i < 0:
+            i += len(self.lengths)
+        o = self.offsets[i]
+        return bytes(self.buffer[o : o + self.lengths[i]])
+
+    def __iter__(self):
+        return (self[i] for i in range(len(self.lengths)))
+
+
 class Database(BaseDatabase):
     """A database of target sequences, stored encoded (lib.pyx:469-778).
 
-    The host keeps one encoded `bytes` per sequence (shared between views
-    made by `mask` / `extract`, like the reference's ``shared_ptr`` buffers);
-    the first search uploads a length-sorted, pair-interleaved copy to the
-    GPU, which every mutator invalidates under the write lock.
+    Host store, two forms.  A database built one sequence at a time
+    (`append` / `extend` / the constructor, lib.pyx:596-636) keeps one encoded
+    `bytes` per sequence, shared between the views made by `mask` / `extract`
+    like the reference's ``shared_ptr`` buffers.  A database built in bulk
+    (`from_packed`, `from_fasta`, `load`) keeps ONE packed residue buffer plus
+    ``int64`` offsets and ``int32`` lengths -- zero-copy over the caller's buffer
+    or an ``mmap`` -- and is handed to the device as it lies; the first
+    per-sequence mutation turns it into the list form.
+
+    The first search uploads the residues once and builds the length-sorted,
+    pair-interleaved store on the GPU(s); every mutator invalidates it under
+    the write lock.
     """
 
     def __new__(cls, *args, **kwargs):
         self = super().__new__(cls)
         self._sequences = []
         self._lengths = []
+        self._packed = None      # (buffer, offsets array('q'), lengths array('i')) or None
+        self._keepalive = None   # e.g. the mmap behind a loaded database
         self._version = 0
         self._store = None
         self._store_version = -1
@@ -365,13 +399,31 @@ class Database(BaseDatabase):
     # --- Database interface ---
 
     def get_sequences(self):
+        if self._packed is not None:
+            return _PackedSequences(*self._packed)
         return self._sequences
 
     def get_lengths(self):
-        return self._lengths
+        return self._packed[2] if self._packed is not None else self._lengths
 
     def get_size(self):
-        return len(self._sequences)
+        return len(self._packed[2]) if self._packed is not None else len(self._sequences)
+
+    @property
+    def total_length(self):
+        with self.lock.read:
+            if self._packed is not None:
+                return _cuda.offsets_from_lengths(self._packed[2])[1]
+            return sum(self._lengths)
+
+    def _unpack(self):
+        """Packed form -> list form (call under the write lock, before a per-sequence mutation)."""
+        if self._packed is not None:
+            seqs = _PackedSequences(*self._packed)
+            self._sequences = [seqs[i] for i in range(len(seqs))]
+            self._lengths = list(self._packed[2])
+            self._packed = None
+            self._keepalive = None
 
     # --- Device mirror ---
 
@@ -379,12 +431,29 @@ class Database(BaseDatabase):
         self._version += 1
 
     def _device_store(self):
-        """The device-resident store for the current contents (call under the read lock)."""
+        """The device-resident store for the current contents (call under the read lock).
+
+        Every visible GPU is used (``PYOPAL_CUDA_DEVICES`` restricts them; under a one-process-per-GPU launcher
+        the process keeps to its own device): the thread fan-out of the reference's ``pyopal.align``
+        (_align.py:145-172) becomes a cell-balanced deal over the devices inside the library.
+        """
         with self._store_lock:
             if self._store is None or self._store_version != self._version:
                 if self._store is not None:
                     self._store.close()
-                self._store = _cuda.DeviceStore.from_sequences(self._sequences, self.alphabet.length)
+                devices = _cuda.default_devices()
+                if self._packed is not None:
+                    buf, offsets, lengths = self._packed
+                    total = (offsets[-1] + lengths[-1]) if len(lengths) else 0
+                else:
+                    buf, offsets, lengths = None, None, self._lengths
+                    total = sum(lengths)
+                if len(devices) > 1 and total < _cuda.MULTI_GPU_MIN_RESIDUES and not _cuda.devices_forced():
+                    devices = devices[:1]  # a small database: one GPU answers before eight have been fed
+                if self._packed is not None:
+                    self._store = _cuda.make_store(buf, offsets, lengths, self.alphabet.length, devices)
+                else:
+                    self._store = _cuda.make_store_from_sequences(self._sequences, self.alphabet.length, devices)
                 self._store_version = self._version
             return self._store
 
@@ -398,32 +467,32 @@ class Database(BaseDatabase):
     # The reference appends one sequence at a time: a Python call, an encode
     # and a heap allocation each (lib.pyx:596-636), and pickling re-appends the
     # decoded strings one by one (lib.pyx:496-497).  These constructors take
-    # whole buffers instead.
+    # whole buffers instead and never loop over the sequences in Python.
 
-    _MAGIC = b"PYOPALDB1\n"
+    _MAGIC = b"PYOPALDB2\n"
+    _ALIGN = 64
 
     @classmethod
-    def from_packed(cls, residues, lengths, alphabet=None, encoded=True):
-        """Build a database from one packed buffer and the sequence lengths.
+    def from_packed(cls, residues, lengths, alphabet=None, encoded=True, validate=True):
+        """Build a database from one packed buffer and the sequence lengths, without copying it.
 
-        ``residues`` holds the sequences back to back: alphabet indices when
-        ``encoded`` is true, ASCII letters otherwise (translated in one call).
+        ``residues`` holds the sequences back to back (any C-contiguous
+        bytes-like object: `bytes`, ``numpy.uint8``, an ``mmap`` ...): alphabet
+        indices when ``encoded`` is true, ASCII letters otherwise (translated in
+        one call).  ``lengths``: any buffer or iterable of `int`.
         """
         self = cls((), alphabet)
-        data = bytes(residues) if encoded else self.alphabet.encode(bytes(residues))
-        lens = [operator.index(n) for n in lengths]
-        if any(n < 0 for n in lens) or sum(lens) != len(data):
+        data = memoryview(residues).cast("B") if encoded else memoryview(self.alphabet.encode(bytes(residues)))
+        lens = _cuda.as_int32_array(lengths)
+        offsets, total = _cuda.offsets_from_lengths(lens)
+        if (len(lens) and min(lens) < 0) or total != data.nbytes:
             raise ValueError("lengths do not add up to the size of the residue buffer")
-        if encoded and data and max(data) >= self.alphabet.length:
+        if encoded and validate and data.nbytes and _cuda.has_byte_ge(data, self.alphabet.length):
             raise ValueError("residue code outside the alphabet")
-        seqs = []
-        pos = 0
-        for n in lens:
-            seqs.append(data[pos : pos + n])
-            pos += n
         with self.lock.write:
-            self._sequences = seqs
-            self._lengths = lens
+            self._packed = (data, offsets, lens)
+            self._keepalive = residues
+            self._sequences, self._lengths = [], []
             self._touch()
         return self
 
@@ -447,42 +516,69 @@ class Database(BaseDatabase):
             lengths.append(len(seq))
         return cls.from_packed(b"".join(chunks), lengths, alphabet, encoded=False), names
 
+    def _packed_view(self):
+        """(buffer, offsets, lengths) of the current contents (packing the list form if needed)."""
+        if self._packed is not None:
+            return self._packed
+        lens = array.array("i", self._lengths)
+        offsets, _ = _cuda.offsets_from_lengths(lens)
+        return memoryview(b"".join(self._sequences)), offsets, lens
+
     def dump(self, file):
-        """Write the encoded database in a packed binary form (`load` reads it back without re-encoding)."""
+        """Write the encoded database in a packed binary form that `load` maps back without copying.
+
+        Layout (little endian, sections aligned to 64 bytes so that an ``mmap`` of the file can be handed to
+        the device as it lies): magic, alphabet, sequence count, residue count, ``int32`` lengths, residues.
+        The length sort / pairing / interleaving of the device store is not persisted: it is rebuilt ON the
+        GPU from these residues in milliseconds, and the raw residues are half the bytes of the interleaved
+        stream to push over PCIe.
+        """
         with self.lock.read:
+            buf, _, lens = self._packed_view()
             letters = self.alphabet.letters.encode("ascii")
-            lens = array.array("i", self._lengths)
-            payload = [self._MAGIC, len(letters).to_bytes(4, "little"), letters, len(lens).to_bytes(8, "little"),
-                       lens.tobytes(), b"".join(self._sequences)]
-        if hasattr(file, "write"):
-            for part in payload:
-                file.write(part)
-        else:
-            with open(file, "wb") as handle:
+            head = self._MAGIC + len(letters).to_bytes(4, "little") + letters
+            head += b"\0" * (-len(head) % 8)
+            head += len(lens).to_bytes(8, "little") + buf.nbytes.to_bytes(8, "little")
+            head += b"\0" * (-len(head) % self._ALIGN)
+            lens_b = memoryview(lens).cast("B")
+            payload = [head, lens_b, b"\0" * (-lens_b.nbytes % self._ALIGN), buf]
+            if hasattr(file, "write"):
                 for part in payload:
-                    handle.write(part)
+                    file.write(part)
+            else:
+                with open(file, "wb") as handle:
+                    for part in payload:
+                        handle.write(part)
 
     @classmethod
     def load(cls, file):
-        """Read a database written by `dump`."""
+        """Read a database written by `dump`: a path is memory-mapped (no copy, no per-sequence work)."""
+        keep = None
         if hasattr(file, "read"):
-            blob = file.read()
+            view = memoryview(file.read())
         else:
+            import mmap
+
             with open(file, "rb") as handle:
-                blob = handle.read()
-        view = memoryview(blob)
+                keep = mmap.mmap(handle.fileno(), 0, access=mmap.ACCESS_READ)
+            view = memoryview(keep)
         m = len(cls._MAGIC)
         if bytes(view[:m]) != cls._MAGIC:
             raise ValueError("not a packed pyopal database")
         nl = int.from_bytes(view[m : m + 4], "little")
         letters = bytes(view[m + 4 : m + 4 + nl]).decode("ascii")
         pos = m + 4 + nl
+        pos += -pos % 8
         n = int.from_bytes(view[pos : pos + 8], "little")
-        pos += 8
-        lens = array.array("i")
-        lens.frombytes(view[pos : pos + 4 * n])
+        total = int.from_bytes(view[pos + 8 : pos + 16], "little")
+        pos += 16
+        pos += -pos % cls._ALIGN
+        lens = view[pos : pos + 4 * n].cast("i")
         pos += 4 * n
-        return cls.from_packed(view[pos:], lens, Alphabet(letters), encoded=True)
+        pos += -pos % cls._ALIGN
+        self = cls.from_packed(view[pos : pos + total], lens, Alphabet(letters), encoded=True, validate=False)
+        self._keepalive = (keep, view)
+        return self
 
     # --- Sequence interface ---
 
@@ -496,6 +592,7 @@ class Database(BaseDatabase):
         index_ = operator.index(index)
         encoded = self._encode(sequence)
         with self.lock.write:
+            self._unpack()
             size = len(self._sequences)
             if index_ < 0:
                 index_ += size
@@ -508,6 +605,7 @@ class Database(BaseDatabase):
     def __delitem__(self, index):
         index_ = operator.index(index)
         with self.lock.write:
+            self._unpack()
             size = len(self._sequences)
             if index_ < 0:
                 index_ += size
@@ -520,8 +618,10 @@ class Database(BaseDatabase):
     def clear(self):
         """Remove all sequences from the database."""
         with self.lock.write:
-            self._sequences.clear()
-            self._lengths.clear()
+            self._packed = None
+            self._keepalive = None
+            self._sequences = []
+            self._lengths = []
             self._touch()
 
     def extend(self, sequences):
@@ -549,6 +649,7 @@ class Database(BaseDatabase):
         """
         encoded = self._encode(sequence)
         with self.lock.write:
+            self._unpack()
             self._sequences.append(encoded)
             self._lengths.append(len(encoded))
             self._touch()
@@ -564,6 +665,7 @@ class Database(BaseDatabase):
 
         """
         with self.lock.write:
+            self._unpack()
             self._sequences.reverse()
             self._lengths.reverse()
             self._touch()
@@ -585,6 +687,7 @@ class Database(BaseDatabase):
         index_ = operator.index(index)
         encoded = self._encode(sequence)
         with self.lock.write:
+            self._unpack()
             size = len(self._sequences)
             if index_ < 0:
                 index_ += size
@@ -601,8 +704,9 @@ class Database(BaseDatabase):
     def _subset(self, positions):
         subdb = Database.__new__(Database)
         subdb.alphabet = self.alphabet
-        subdb._sequences = [self._sequences[i] for i in positions]
-        subdb._lengths = [self._lengths[i] for i in positions]
+        sequences, lengths = self.get_sequences(), self.get_lengths()
+        subdb._sequences = [sequences[i] for i in positions]
+        subdb._lengths = [lengths[i] for i in positions]
         return subdb
 
     def mask(self, bitmask):
@@ -995,6 +1099,29 @@ class Aligner:
                 start, end,
             )
 
+    @staticmethod
+    def _slice(database, start, end):
+        """``[start, end)`` checked exactly as `align` does (lib.pyx:1365-1370; call under the read lock)."""
+        start = operator.index(start)
+        end = operator.index(end)
+        if start < 0 or end < 0 or start > UINT32_MAX or end > UINT32_MAX:
+            raise OverflowError("can't convert value to uint32_t")
+        size = database.get_size()
+        if end < start:
+            raise IndexError("database slice end is lower than start")
+        end = min(end, size)
+        if start > end:
+            raise IndexError("database slice start is past the end")
+        return start, end
+
+    def _bulk_args(self, database, algorithm):
+        if not isinstance(database, Database):
+            raise TypeError("this call needs a pyopal Database (device-resident store)")
+        _, _, _algo = self._validate("score", "buckets", algorithm)
+        if database.alphabet != self.alphabet:
+            raise ValueError("database and score matrix have different alphabets")
+        return _algo
+
     def align_scores(self, query, database, *, algorithm="sw", start=0, end=UINT32_MAX):
         """Score-mode search returning a flat ``array('i')`` instead of result objects.
 
@@ -1002,19 +1129,10 @@ class Aligner:
         database the per-target Python objects built at pyx.in:65-72 cost far
         more than the search itself once the DP runs on the GPU.
         """
-        if not isinstance(database, Database):
-            raise TypeError("align_scores needs a pyopal Database (device-resident store)")
-        _, _, _algo = self._validate("score", "buckets", algorithm)
-        if database.alphabet != self.alphabet:
-            raise ValueError("database and score matrix have different alphabets")
+        _algo = self._bulk_args(database, algorithm)
         encoded = database.alphabet.encode(query)
         with database.lock.read:
-            size = database.get_size()
-            if end < start:
-                raise IndexError("database slice end is lower than start")
-            end = min(end, size)
-            if start > end:
-                raise IndexError("database slice start is past the end")
+            start, end = self._slice(database, start, end)
             if end == start:
                 return array.array("i")
             store = database._device_store()
@@ -1030,21 +1148,12 @@ class Aligner:
         (docs/examples/abc.ipynb); here the selection runs on the device (csrc/topk.cu) and only ``k``
         (score, index) pairs come back.
         """
-        if not isinstance(database, Database):
-            raise TypeError("align_topk needs a pyopal Database (device-resident store)")
+        _algo = self._bulk_args(database, algorithm)
         if k < 0:
             raise ValueError("k must be non-negative")
-        _, _, _algo = self._validate("score", "buckets", algorithm)
-        if database.alphabet != self.alphabet:
-            raise ValueError("database and score matrix have different alphabets")
         encoded = database.alphabet.encode(query)
         with database.lock.read:
-            size = database.get_size()
-            if end < start:
-                raise IndexError("database slice end is lower than start")
-            end = min(end, size)
-            if start > end:
-                raise IndexError("database slice start is past the end")
+            start, end = self._slice(database, start, end)
             if end == start or k == 0:
                 return []
             store = database._device_store()
@@ -1057,11 +1166,7 @@ class Aligner:
 
         Returns a list of ``array('i')``, one per query.
         """
-        if not isinstance(database, Database):
-            raise TypeError("align_batch needs a pyopal Database (device-resident store)")
-        _, _, _algo = self._validate("score", "buckets", algorithm)
-        if database.alphabet != self.alphabet:
-            raise ValueError("database and score matrix have different alphabets")
+        _algo = self._bulk_args(database, algorithm)
         encoded = [database.alphabet.encode(q) for q in queries]
         with database.lock.read:
             size = database.get_size()
@@ -1070,3 +1175,18 @@ class Aligner:
             store = database._device_store()
             flat = store.search_batch(encoded, self.gap_open, self.gap_extend, self._int_matrix, _algo)
             return [flat[i * size : (i + 1) * size] for i in range(len(encoded))]
+
+    def align_batch_topk(self, queries, database, k, *, algorithm="sw"):
+        """The ``k`` best `ScoreResult` of every query (device-side selection, only the hits leave the GPU)."""
+        _algo = self._bulk_args(database, algorithm)
+        if k < 0:
+            raise ValueError("k must be non-negative")
+        encoded = [database.alphabet.encode(q) for q in queries]
+        with database.lock.read:
+            size = database.get_size()
+            k = min(int(k), size)
+            if size == 0 or not encoded or k == 0:
+                return [[] for _ in encoded]
+            store = database._device_store()
+            vals, idx = store.search_batch_topk(encoded, self.gap_open, self.gap_extend, self._int_matrix, _algo, k)
+        return [[ScoreResult(int(idx[q * k + j]), int(vals[q * k + j])) for j in range(k)] for q in range(len(encoded))]

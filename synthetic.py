@@ -97,6 +97,21 @@ def config2_queries(db, lengths=(100, 300, 1000, 2000, 5000)):
     return out
 
 
+def pack_subset(db, idx):
+    """Packed (residues, offsets, lengths) of the targets ``idx`` of a packed database."""
+    residues, offsets, lengths = db[:3]
+    idx = np.asarray(idx, dtype=np.int64)
+    sl = np.ascontiguousarray(np.asarray(lengths)[idx]).astype(np.int32)
+    so = np.zeros(len(idx), dtype=np.int64)
+    if len(idx) > 1:
+        np.cumsum(sl[:-1], out=so[1:])
+    total = int(sl.sum())
+    if total == 0:
+        return np.zeros(0, dtype=np.uint8), so, sl
+    src = np.repeat(np.asarray(offsets, dtype=np.int64)[idx] - so, sl) + np.arange(total, dtype=np.int64)
+    return np.ascontiguousarray(np.asarray(residues)[src]), so, sl
+
+
 def as_sequences(db):
     """List of encoded `bytes`, one per target."""
     residues, offsets, lengths = db

@@ -15,6 +15,7 @@ import pytest
 import pyopal_b200 as pyopal
 import synthetic
 from pyopal_b200 import sharding
+from pyopal_b200.platform import cuda as _cuda_mod
 
 pytestmark = pytest.mark.gpu
 
@@ -38,20 +39,23 @@ def gpu_scores(full, q, algo, **kw):
 
 def oracle_subset(oracle, full, q, algo, idx):
     residues, offsets, lengths = full["db"]
-    sr, so, sl = sharding.pack_shard(residues, offsets, lengths, np.asarray(idx))
+    sr, so, sl = synthetic.pack_subset(full["db"], np.asarray(idx))
     out = oracle.search_flat(q, sr.tobytes() + b"\0", array.array("q", so.tolist()), array.array("i", sl.tolist()),
                              full["M"], 24, GO, GE, algo, "score", 8)
     return np.asarray(out["score"], dtype=np.int32)
 
 
-@pytest.mark.parametrize("algo", ["sw", "nw", "hw", "ov"])
-def test_subsample_and_giants_match_oracle(full, oracle, algo):
-    # a random subsample + all planted giants, query 300 aa (a mutated database entry)
+@pytest.mark.parametrize("qi,algo", [(0, "sw"), (1, "sw"), (2, "sw"), (3, "sw"), (4, "sw"), (1, "nw"), (1, "hw"), (1, "ov"),
+                                     (4, "nw"), (4, "hw"), (4, "ov")])
+def test_subsample_and_giants_match_oracle(full, oracle, qi, algo):
+    # a random subsample + all planted giants for EVERY query of the benchmark step (SW: the
+    # one-pass tiles of the 100 / 300-aa queries and the 7 / 14 / 35-pass bulk plans of the 1000 / 2000 / 5000-aa
+    # ones, whose random targets never touch the giant kernels) and the 300- and 5000-aa queries for NW / HW / OV
     _, _, lengths = full["db"]
-    rng = np.random.Generator(np.random.PCG64(99))
+    rng = np.random.Generator(np.random.PCG64(99 + qi))
     giants = np.nonzero(lengths >= 10_000)[0]
-    idx = np.unique(np.concatenate([rng.choice(len(lengths), 3000, replace=False), giants]))
-    q = full["queries"][1]
+    idx = np.unique(np.concatenate([rng.choice(len(lengths), 3000 if qi < 3 else 1200, replace=False), giants]))
+    q = full["queries"][qi]
     got = gpu_scores(full, q, algo)
     assert len(got) == len(lengths)
     want = oracle_subset(oracle, full, q, algo, idx)
@@ -111,8 +115,8 @@ def test_four_way_shards_reproduce_whole(full, cuda):
     out = np.full(len(lengths), np.iinfo(np.int32).min, dtype=np.int32)
     totals = []
     for rank in range(4):
-        mine = sharding.shard_indices(lengths, 4, rank)
-        sr, so, sl = sharding.pack_shard(residues, offsets, lengths, mine)
+        mine = np.asarray(sharding.shard_indices(lengths, 4, rank))
+        sr, so, sl = synthetic.pack_subset((residues, offsets, lengths), mine)
         store = cuda.DeviceStore(sr, so, sl, 24, device=0)
         out[mine] = np.frombuffer(store.search(q, GO, GE, full["M"], 0, 3)[0], dtype=np.int32)
         totals.append(int(sl.sum()))
@@ -141,7 +145,7 @@ def test_config5_block_batch(cuda, oracle):
     rows = np.frombuffer(store.search_batch(queries, GO, GE, M, 3), dtype=np.int32).reshape(len(queries), -1)
     rng = np.random.Generator(np.random.PCG64(55))
     idx = np.unique(np.concatenate([rng.choice(len(sl), 1500, replace=False), np.argsort(sl)[-20:], np.argsort(sl)[:20]]))
-    sub_r, sub_o, sub_l = sharding.pack_shard(sr, so, sl, idx)
+    sub_r, sub_o, sub_l = synthetic.pack_subset((sr, so, sl), idx)
     for qi, q in enumerate(queries):
         want = oracle.search_flat(q, sub_r.tobytes() + b"\0", array.array("q", sub_o.tolist()),
                                   array.array("i", sub_l.tolist()), M, 24, GO, GE, "sw", "score", 8)["score"]
@@ -151,10 +155,9 @@ def test_config5_block_batch(cuda, oracle):
 
 
 def test_sharded_database_api_single_rank(cuda, oracle):
-    # sharding.ShardedDatabase at world size 1 (no process group): both ways of sharding, scores in database
-    # order and the batched top-k; the N > 1 gather is covered on CPU by tests/test_sharding_gloo.py
-    import torch
-
+    # sharding.ShardedDatabase at world size 1 (no communicator): both ways of sharding, scores in database order,
+    # the batched call and the batched device top-k; N > 1 is covered by test_multi_gpu.py (NCCL, when the box has
+    # two GPUs) and tests/test_sharding_gloo.py (the deal and the gather's index arithmetic, on CPU)
     residues, offsets, lengths = synthetic.database(77, 3000, 5.0, 0.7, 1, 2500, giants=(6000, 4500))
     M = pyopal.Aligner("BLOSUM62", GO, GE)._int_matrix
     queries = [q.tobytes() for q in synthetic.config5_queries(3)]
@@ -163,14 +166,20 @@ def test_sharded_database_api_single_rank(cuda, oracle):
     want = [oracle.search_flat(q, residues.tobytes() + b"\0", array.array("q", offsets.tolist()),
                                array.array("i", lengths.tolist()), M, 24, GO, GE, "sw", "score", 8)["score"] for q in queries]
     for q, w in zip(queries, want):
-        assert sdb.search_scores(q, GO, GE, M).cpu().tolist() == list(w)
-    vals, idx = sdb.search_topk(queries, GO, GE, M, 10)
+        assert list(sdb.search(q, GO, GE, M, 0, 3)[0]) == list(w)
+    flat = sdb.search_batch(queries, GO, GE, M, 3)
+    n = len(lengths)
     for qi, w in enumerate(want):
-        w = torch.tensor(list(w))
-        assert vals[qi].tolist() == torch.topk(w, 10).values.tolist()
-        assert w[idx[qi].long()].tolist() == vals[qi].tolist()
+        assert list(flat[qi * n: (qi + 1) * n]) == list(w)
+    vals, idx = sdb.search_batch_topk(queries, GO, GE, M, 3, 10)
+    for qi, w in enumerate(want):
+        order = sorted(range(n), key=lambda i: (-w[i], i))[:10]
+        assert list(vals[qi * 10: qi * 10 + 10]) == [w[i] for i in order]
+        assert list(idx[qi * 10: qi * 10 + 10]) == order
+    part = sdb.search(queries[0], GO, GE, M, 0, 3, start=100, end=900)[0]
+    assert list(part) == list(want[0][100:900])
     blk = sharding.ShardedDatabase.from_blocks((residues, offsets, lengths), 1500, 2, device=0)
-    assert blk.search_scores(queries[0], GO, GE, M).cpu().tolist() == list(want[0])
+    assert list(blk.search(queries[0], GO, GE, M, 0, 3)[0]) == list(want[0])
     with pytest.raises(ValueError):
         sharding.ShardedDatabase.from_blocks((residues, offsets, lengths), 1000, 2, device=0)
 
@@ -188,7 +197,7 @@ def test_config4_top_hits_end_and_full(full, oracle, cuda, qi, algo):
     top = np.sort(np.argsort(-sc.astype(np.int64), kind="stable")[:k])
     giants = np.nonzero(lengths >= 30_000)[0][:3]
     top = np.unique(np.concatenate([top, giants]))
-    sr, so, sl = sharding.pack_shard(residues, offsets, lengths, top)
+    sr, so, sl = synthetic.pack_subset((residues, offsets, lengths), top)
     sub = cuda.DeviceStore(sr, so, sl, 24, device=0)
     flat = (sr.tobytes() + b"\0", array.array("q", so.tolist()), array.array("i", sl.tolist()))
     for mode, st in (("end", 1), ("full", 2)):
@@ -219,7 +228,7 @@ def test_whole_database_end_mode(full, oracle, qi, algo):
     rng = np.random.Generator(np.random.PCG64(1234 + qi))
     giants = np.nonzero(lengths >= 10_000)[0]
     idx = np.unique(np.concatenate([rng.choice(len(lengths), 1500, replace=False), giants]))
-    sr, so, sl = sharding.pack_shard(residues, offsets, lengths, idx)
+    sr, so, sl = synthetic.pack_subset((residues, offsets, lengths), idx)
     want = oracle.search_flat(q, sr.tobytes() + b"\0", array.array("q", so.tolist()), array.array("i", sl.tolist()),
                               full["M"], 24, GO, GE, algo, "end", 8)
     assert got_s[idx].tolist() == want["score"]
