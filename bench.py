@@ -206,6 +206,13 @@ class ClockSampler(threading.Thread):
         self.reasons = set()
         self.max_mhz = None
         self.stop_flag = threading.Event()
+        self.ready = threading.Event()
+
+    def begin(self):
+        """Start the thread and wait until NVML is initialised: nvmlInit takes tens of milliseconds during which
+        CUDA launches stall, which must not fall inside the timed region."""
+        self.start()
+        self.ready.wait(20)
 
     def run(self):
         try:
@@ -220,15 +227,22 @@ class ClockSampler(threading.Thread):
                 "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown,
                 "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap,
             }
-            while not self.stop_flag.is_set():
+            nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+            self.ready.set()
+            last = False
+            while not last:
+                # the last sample is taken when the timed region closes, so that a region shorter than one period
+                # still has one taken under load
+                last = self.stop_flag.wait(self.period)
                 self.samples.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
                 r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
                 for name, m in masks.items():
                     if r & m:
                         self.reasons.add(name)
-                self.stop_flag.wait(self.period)
         except Exception as err:  # NVML missing: report no clocks rather than die
             self.error = repr(err)
+        finally:
+            self.ready.set()
 
     def finish(self):
         self.stop_flag.set()
@@ -379,6 +393,8 @@ def run_b200(args):
     cells_step = sum(len(q) for q in qbytes) * total_res
 
     # the repo's multi-GPU handle: this rank's cell-balanced shard on its GPU + the NCCL gather (csrc/multi.cu)
+    # (a one-target store first, so that creating the CUDA context is not charged to the build)
+    cuda.DeviceStore(np.zeros(16, np.uint8), np.zeros(1, np.int64), np.full(1, 16, np.int32), 24, device=local).close()
     t_build = time.perf_counter()
     sdb = sharding.ShardedDatabase.deal(residues, offsets, np.ascontiguousarray(lengths), 24, rank=rank, world=world,
                                         nccl_id=ranks.nccl_id(cuda), device=local)
@@ -397,7 +413,7 @@ def run_b200(args):
         step()
     ranks.barrier()
     sampler = ClockSampler(cuda.device_pci_bus_id(local))
-    sampler.start()
+    sampler.begin()
     launches = 0
     ranks.barrier()
     sdb.time_begin()          # cudaDeviceSynchronize + event on the handle's stream
@@ -542,7 +558,7 @@ def run_config4(args):
     for _ in range(args.warmup):
         step()
     sampler = ClockSampler(cuda.device_pci_bus_id(0))
-    sampler.start()
+    sampler.begin()
     dev_us = 0
     launches = 0
     t0 = time.perf_counter()
@@ -674,7 +690,7 @@ def run_config5(args):
         batch()
     ranks.barrier()
     sampler = ClockSampler(cuda.device_pci_bus_id(local))
-    sampler.start()
+    sampler.begin()
     launches = 0
     ranks.barrier()
     sdb.time_begin()

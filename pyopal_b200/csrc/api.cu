@@ -160,6 +160,7 @@ void Tuning::load() {
     if (const char* v = getenv("PYOPAL_CUDA_SOLO")) solo = atof(v);
     if (const char* v = getenv("PYOPAL_CUDA_GMUL")) gmul = atof(v);
     if (const char* v = getenv("PYOPAL_CUDA_MID")) mid = atof(v);
+    if (const char* v = getenv("PYOPAL_CUDA_LANES")) lanes = atoi(v) >= 2 ? 2 : 1;
     if (const char* v = getenv("PYOPAL_CUDA_PAIR_K")) pair_k = atoi(v);
     if (const char* v = getenv("PYOPAL_CUDA_PAIR_C")) pair_c = atoi(v);
 }
@@ -186,10 +187,10 @@ int Workspace::init(int dev) {
 }
 
 void Workspace::destroy() {
-    ovf.release(); out.release(); gprofile.release(); wprofile.release(); end_out.release();
+    ovf.release(); out.release(); out2.release(); gprofile.release(); wprofile.release(); end_out.release();
     bndH.release(); bndF.release(); bnd32H.release(); bnd32F.release();
     pd_i32.release(); pd_tb.release(); pd_ops.release(); pd_jobs.release(); pd_team.release(); pd_query.release();
-    tk_ws.release(); tk_vals.release(); tk_idx.release();
+    tk_ws.release(); tk_vals.release(); tk_idx.release(); tk_vals2.release(); tk_idx2.release();
     d_par.release();
     for (int i = 0; i < NPARAM; i++) { h_par[i].release(); if (par_done[i]) cudaEventDestroy(par_done[i]); par_done[i] = nullptr; }
     for (cudaEvent_t* e : {&ev_fork, &ev_join, &ev_join2, &ev_free, &ev_aux0, &ev_aux1, &ev0, &ev1}) { if (*e) cudaEventDestroy(*e); *e = nullptr; }
@@ -225,6 +226,12 @@ void pyopal_cuda_db::release(Workspace* ws) {
         free_ws.push_back(ws);
     }
     cv.notify_one();
+}
+
+void pyopal_cuda_db::publish(Workspace* ws) {
+    std::lock_guard<std::mutex> lock(mu);
+    for (int i = 0; i < 12; i++) last_stats[i] = ws->stats[i];
+    last_ws = ws;
 }
 
 // ---------------------------------------------------------------------------
@@ -556,10 +563,13 @@ Plan make_plan(int Lq, int A, const pyopal_cuda_db* db, size_t smem_limit, Giant
         }
         // the giants hold whole SMs at a fraction of the bulk kernel's efficiency
         const double giant_cost = giant_cols * (gp ? gp->col_cost : 0.0);
-        const double midf = tune.mid > 0 ? tune.mid : 0.5;
+        const double midf = tune.mid > 0 ? tune.mid : 0.25;
         const int64_t kmid = mid ? first_pair_at_most(db, std::max(256.0, midf * l_even(G)), kg) : kg;
         const double cols_mid = cols_of(kg, kmid), n_mid = (double)(kmid - kg);
-        const double cols_bulk = cols_of(kmid, db->npairs), n_bulk = (double)(db->npairs - kmid);
+        // without a mid tier the bulk term covers every pair, the giants' columns included: the planner constants
+        // (solo, gmul, the giants' col_cost) were calibrated on shards of config 2 with exactly this expression
+        const double cols_bulk = mid ? cols_of(kmid, db->npairs) : (double)db->ncols;
+        const double n_bulk = mid ? (double)(db->npairs - kmid) : (double)db->npairs;
         const double longest_bulk = kmid < db->npairs ? (double)db->h_pair_len[(size_t)(2 * kmid)] : 0.0;
         const double stretch = std::max(1.0, longest_bulk / std::max(l_even(G), 1.0));
         const double mid_cost = (double)tailp.npass * (cols_mid + 31.0 * n_mid) *
@@ -710,6 +720,7 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
                                     int32_t* d_out, cudaStream_t st, EndPlan* endp) {
     for (int i = 0; i < 12; i++) ws->stats[i] = 0;
     ws->kev_valid[0] = ws->kev_valid[1] = ws->kev_valid[2] = false;
+    ws->d_ovf_count = nullptr;
     const int64_t nout = end - start;
     if (nout <= 0) return 0;
     const bool local = (mode == MODE_SW);
@@ -802,7 +813,7 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
             gpol.cap = (int64_t)db->sm_count * 8;
             gpol.col_cost = 56.0 * 40.0 * (double)std::max(1, (Lq + 127) / 128);
         }
-        const bool allow_mid = !tune.no_mid && !tune.no_tail && !tune.has_plan;
+        const bool allow_mid = tune.mid > 0 && !tune.no_tail && !tune.has_plan;  // opt-in (PYOPAL_CUDA_MID): see DESIGN.md 4.1
         bulk = make_plan(Lq, A, db, SMEM_LIMIT, &gpol, allow_mid, &kmid);
         tail = make_tail_plan(Lq, A, SMEM_LIMIT);
         int smax = INT_MIN, smin = INT_MAX;
@@ -917,6 +928,12 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
     CU(cudaMemcpyAsync(dp, hp, par_bytes, cudaMemcpyHostToDevice, st));
     CU(cudaEventRecord(ws->par_done[slot], st));
     ws->par_used[slot] = true;
+    if (endm && endp->launch_spill && !endp->spill.empty()) {
+        // the targets left to pairdp.cu go first, on their own high-priority stream: launched behind the persistent
+        // CTAs of the 16-bit kernels they would only start when those drain
+        int rc = endp->launch_spill();
+        if (rc) return rc;
+    }
     int32_t* d_counts = reinterpret_cast<int32_t*>(dp + PAR_COUNTS);
     const int32_t* d_wl32 = reinterpret_cast<const int32_t*>(dp + off_wl32);
     const int32_t* d_wl16 = reinterpret_cast<const int32_t*>(dp + off_wl16);
@@ -951,6 +968,7 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
     P.out = d_out; P.out_start = start; P.out_end = end;
     if (endm) { P.out_q = endp->d_endq; P.out_t = endp->d_endt; }
     P.ovf_list = ws->ovf.p; P.ovf_count = d_counts + 2;
+    ws->d_ovf_count = (local && n16 > 0) ? d_counts + 2 : nullptr;
     P.bndH = ws->bndH.p; P.bndF = ws->bndF.p;
     if (endm) { endp->d_ovf = ws->ovf.p; endp->d_ovf_count = d_counts + 2; endp->packed = n16 > 0; }
 
@@ -1174,6 +1192,11 @@ extern "C" int pyopal_cuda_search(pyopal_cuda_db* db, const unsigned char* query
     float ms = 0;
     CU(cudaEventElapsedTime(&ms, ws->ev0, ws->ev1));
     ws->stats[4] = (int64_t)(ms * 1000.0f);
+    if (ws->d_ovf_count) {  // targets escalated 16 -> 32 bit (statistics only)
+        int32_t novf = 0;
+        CU(cudaMemcpy(&novf, ws->d_ovf_count, sizeof(int32_t), cudaMemcpyDeviceToHost));
+        ws->stats[3] = novf;
+    }
     return 0;
 }
 
@@ -1200,17 +1223,24 @@ static int search_batch_impl(pyopal_cuda_db* db, const unsigned char* queries, c
     const int64_t n = db->n;
     if (n == 0 || nq == 0) return 0;
     DeviceGuard guard(db->device);
-    const int NB = 2;
-    Lease l0(db), l1(db);
-    Workspace* wsv[NB] = {l0.ws, l1.ws};
+    // one lane: the searches are stream-ordered back to back (no host round trip between them).  Two lanes let the
+    // next search start while the last CTAs of the previous one drain, but its high-priority giants then queue
+    // behind the resident persistent CTAs and end up last: measured slower, so opt-in.
+    const int NB = db->tune.lanes;
+    Lease l0(db);
+    std::unique_ptr<Lease> l1(NB > 1 ? new Lease(db) : nullptr);
+    Workspace* wsv[2] = {l0.ws, NB > 1 ? l1->ws : l0.ws};
     if (!wsv[0] || !wsv[1]) return PYOPAL_CUDA_ERR_NOMEM;
     const int kk = (int)std::min<int64_t>(k, n);
     std::vector<int32_t> tv, ti;
     if (kk > 0) { tv.resize((size_t)nq * kk); ti.resize((size_t)nq * kk); }
-    for (int b = 0; b < NB; b++) {
-        if (wsv[b]->out.reserve((size_t)n)) return PYOPAL_CUDA_ERR_NOMEM;
-        if (kk > 0 && (wsv[b]->tk_ws.reserve(topk_workspace_words()) || wsv[b]->tk_vals.reserve((size_t)kk) ||
-                       wsv[b]->tk_idx.reserve((size_t)kk)))
+    // two sets of result buffers alternate between consecutive queries whatever the number of lanes
+    DevBuf<int32_t>* rowb[2] = {&wsv[0]->out, NB > 1 ? &wsv[1]->out : &wsv[0]->out2};
+    DevBuf<int32_t>* tvb[2] = {&wsv[0]->tk_vals, NB > 1 ? &wsv[1]->tk_vals : &wsv[0]->tk_vals2};
+    DevBuf<int32_t>* tib[2] = {&wsv[0]->tk_idx, NB > 1 ? &wsv[1]->tk_idx : &wsv[0]->tk_idx2};
+    for (int b = 0; b < 2; b++) {
+        if (rowb[b]->reserve((size_t)n)) return PYOPAL_CUDA_ERR_NOMEM;
+        if (kk > 0 && (wsv[b]->tk_ws.reserve(topk_workspace_words()) || tvb[b]->reserve((size_t)kk) || tib[b]->reserve((size_t)kk)))
             return PYOPAL_CUDA_ERR_NOMEM;
     }
     int rc = 0;
@@ -1218,41 +1248,45 @@ static int search_batch_impl(pyopal_cuda_db* db, const unsigned char* queries, c
     // results of query i are copied out AFTER query i + 1 has been enqueued: a copy into pageable host memory
     // blocks the host until the search before it is done, and by then the next one is already queued on the device
     auto copy_out = [&](int i) -> int {
-        Workspace* ws = wsv[i % NB];
+        Workspace* ws = wsv[i % 2];
+        const int b = i % 2;
         if (kk > 0) {
-            CU(cudaMemcpyAsync(tv.data() + (size_t)i * kk, ws->tk_vals.p, (size_t)kk * 4, cudaMemcpyDeviceToHost, ws->stream));
-            CU(cudaMemcpyAsync(ti.data() + (size_t)i * kk, ws->tk_idx.p, (size_t)kk * 4, cudaMemcpyDeviceToHost, ws->stream));
+            CU(cudaMemcpyAsync(tv.data() + (size_t)i * kk, tvb[b]->p, (size_t)kk * 4, cudaMemcpyDeviceToHost, ws->stream));
+            CU(cudaMemcpyAsync(ti.data() + (size_t)i * kk, tib[b]->p, (size_t)kk * 4, cudaMemcpyDeviceToHost, ws->stream));
         } else if (scores) {
-            CU(cudaMemcpyAsync(scores + (size_t)i * (size_t)n, ws->out.p, (size_t)n * sizeof(int32_t),
+            CU(cudaMemcpyAsync(scores + (size_t)i * (size_t)n, rowb[b]->p, (size_t)n * sizeof(int32_t),
                                cudaMemcpyDeviceToHost, ws->stream));
         }
         CU(cudaEventRecord(ws->ev_free, ws->stream));
         return 0;
     };
     for (int i = 0; i < nq && rc == 0; i++) {
-        Workspace* ws = wsv[i % NB];
+        Workspace* ws = wsv[i % 2];
+        const int b = i % 2;
         int64_t s = 0, e = n;
         const unsigned char* q = queries + q_offsets[i];
         rc = check_search_args(db, q, q_lengths[i], go, ge, M, A, mode, &s, &e);
         if (rc) break;
-        // this workspace's row buffer is overwritten: its previous copy-out ran on the same stream
-        rc = enqueue_score_search(db, ws, q, q_lengths[i], go, ge, M, A, mode, 0, n, ws->out.p, ws->stream);
+        // this buffer set is overwritten: its previous copy-out was issued (and, into pageable memory, completed)
+        // before this point, on a stream this search is ordered after
+        rc = enqueue_score_search(db, ws, q, q_lengths[i], go, ge, M, A, mode, 0, n, rowb[b]->p, ws->stream);
         if (rc) break;
         launches += ws->stats[0];
         if (kk > 0) {
-            rc = topk_device(ws->out.p, n, kk, ws->tk_vals.p, ws->tk_idx.p, ws->tk_ws.p, db->sm_count, ws->stream);
+            rc = topk_device(rowb[b]->p, n, kk, tvb[b]->p, tib[b]->p, wsv[b]->tk_ws.p, db->sm_count, ws->stream);
             if (rc) break;
             launches += 9;
         }
         if (i > 0) rc = copy_out(i - 1);
     }
     if (rc == 0) rc = copy_out(nq - 1);
-    for (int b = 0; b < NB; b++) {
+    for (int b = 0; b < 2; b++) {
         cudaError_t e = cudaStreamSynchronize(wsv[b]->stream);
         if (e != cudaSuccess && rc == 0) rc = fail(PYOPAL_CUDA_ERR_CUDA, std::string("batch: ") + cudaGetErrorString(e));
     }
     wsv[0]->stats[0] = launches;
     wsv[1]->stats[0] = launches;
+    (void)NB;
     if (rc) return rc;
     if (kk > 0) {
         // order the k hits of every query: score descending, ties by ascending database index

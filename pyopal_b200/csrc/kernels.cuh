@@ -370,8 +370,9 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
     const int gpw = 32 >> P.logG;
     const int T = G * K;
     const int ntasks = (nwork + gpw - 1) / gpw;
-    const bool top_free = (P.mode != MODE_NW);
-    const bool left_free = (P.mode == MODE_OV || P.mode == MODE_SW);
+    // local alignment (SW) has both borders free: constants there, so the border arithmetic compiles out
+    const bool top_free = LOCAL || (P.mode != MODE_NW);
+    const bool left_free = LOCAL || (P.mode == MODE_OV);
     const int B = P.bias;
     CellConsts<W> C;
     C.init(P);
@@ -397,6 +398,12 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
         const int len1 = (W == 16) ? lenB : 0;
         const int ncol = len0;
         const int nsteps = __reduce_max_sync(FULL, ncol) + G - 1;
+        // per-task base pointers: the step loop then indexes them with 32-bit columns (one IMAD.WIDE on the FMA
+        // pipe per access instead of 64-bit adds on the ALU pipe)
+        const uint16_t* const sp = P.stream + off;
+        constexpr int BS = (W == 16) ? 1 : 2;   // boundary entries per column
+        uint32_t* const bH = P.bndH + ((W == 16) ? off : (2 * off + half));
+        uint32_t* const bF = P.bndF + ((W == 16) ? off : (2 * off + half));
 
         val_t best = FLOOR;                   // SW: running max of H
         int res0 = INT_MIN, res1 = INT_MIN;   // NW/HW/OV (true values)
@@ -428,11 +435,10 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
             unsigned code_nx = 0;
             val_t bG_nx = FLOOR, bF_nx = NEG;
             if (p == 0 && ncol > 0) {
-                code_nx = P.stream[off];
+                code_nx = sp[0];
                 if (pass != 0) {
-                    const int64_t bi = (W == 16) ? off : (2 * off + half);
-                    bG_nx = (val_t)__ldcg(P.bndH + bi);
-                    bF_nx = (val_t)__ldcg(P.bndF + bi);
+                    bG_nx = (val_t)__ldcg(bH);
+                    bF_nx = (val_t)__ldcg(bF);
                 }
             }
             for (int s = 0; s < nsteps; ++s) {
@@ -444,7 +450,7 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
                     if (sh_d >= G) sh_d = 1;
                 }
                 const int j = s - p;
-                const bool active = (j >= 0) && (j < ncol);
+                const bool active = (unsigned)j < (unsigned)ncol;
                 const unsigned code = code_nx;
                 if (p == 0) {
                     if (pass == 0) {
@@ -458,12 +464,11 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
                 }
                 {
                     const int jn = j + 1;
-                    if (jn >= 0 && jn < ncol) {
-                        code_nx = P.stream[off + jn];
+                    if ((unsigned)jn < (unsigned)ncol) {
+                        code_nx = sp[jn];
                         if (p == 0 && pass != 0) {
-                            const int64_t bi = (W == 16) ? (off + jn) : (2 * (off + jn) + half);
-                            bG_nx = (val_t)__ldcg(P.bndH + bi);
-                            bF_nx = (val_t)__ldcg(P.bndF + bi);
+                            bG_nx = (val_t)__ldcg(bH + BS * jn);
+                            bF_nx = (val_t)__ldcg(bF + BS * jn);
                         }
                     }
                 }
@@ -486,9 +491,8 @@ __global__ void __launch_bounds__(512) search_kernel(const __grid_constant__ KPa
                     upGprev = upG;
                     if (p == G - 1) {
                         if (pass != lastpass) {
-                            const int64_t bi = (W == 16) ? (off + j) : (2 * (off + j) + half);
-                            __stcg(P.bndH + bi, (uint32_t)Gout);
-                            __stcg(P.bndF + bi, (uint32_t)Fout);
+                            __stcg(bH + BS * j, (uint32_t)Gout);
+                            __stcg(bF + BS * j, (uint32_t)Fout);
                         } else if (!LOCAL) {
                             // last query row: H = G + open
                             const int h0 = V::lo(Gout) + P.go - B, h1 = V::hi(Gout) + P.go - B;

@@ -531,22 +531,27 @@ int rank_batch(pyopal_cuda_mdb* m, int L, const BatchArgs& a, bool output, int64
     const int kk = (int)std::min<int64_t>(a.k, nout);
     std::vector<int32_t> tv, ti;
     if (kk > 0 && output) { tv.resize((size_t)a.nq * kk); ti.resize((size_t)a.nq * kk); }
+    // Buffer sets alternate between consecutive queries; with one lane (the default) both run on lane 0's streams,
+    // i.e. the searches are stream-ordered back to back, with two lanes each set has its own streams.
+    const int nlane = l->db->tune.lanes >= 2 ? NLANE : 1;
     auto copy_out = [&](int i) -> int {
         Lane& ln = l->lane[i % NLANE];
+        cudaStream_t gs = l->lane[i % nlane].gstream;
         if (!output) return 0;
         const int32_t* src = m->identity ? ln.d_local + lo : ln.d_final;
         if (kk > 0) {
-            CU(cudaMemcpyAsync(tv.data() + (size_t)i * kk, ln.tk_vals.p, (size_t)kk * 4, cudaMemcpyDeviceToHost, ln.gstream));
-            CU(cudaMemcpyAsync(ti.data() + (size_t)i * kk, ln.tk_idx.p, (size_t)kk * 4, cudaMemcpyDeviceToHost, ln.gstream));
+            CU(cudaMemcpyAsync(tv.data() + (size_t)i * kk, ln.tk_vals.p, (size_t)kk * 4, cudaMemcpyDeviceToHost, gs));
+            CU(cudaMemcpyAsync(ti.data() + (size_t)i * kk, ln.tk_idx.p, (size_t)kk * 4, cudaMemcpyDeviceToHost, gs));
         } else if (a.scores) {
-            CU(cudaMemcpyAsync(a.scores + (size_t)i * (size_t)nout, src, (size_t)nout * sizeof(int32_t), cudaMemcpyDeviceToHost, ln.gstream));
+            CU(cudaMemcpyAsync(a.scores + (size_t)i * (size_t)nout, src, (size_t)nout * sizeof(int32_t), cudaMemcpyDeviceToHost, gs));
         }
-        CU(cudaEventRecord(ln.ev_gather, ln.gstream));
+        CU(cudaEventRecord(ln.ev_gather, gs));
         return 0;
     };
     for (int i = 0; i < a.nq; i++) {
-        Lane& ln = l->lane[i % NLANE];
-        Workspace* ws = ln.ws;
+        Lane& ln = l->lane[i % NLANE];                 // buffers of this query
+        Workspace* ws = l->lane[i % nlane].ws;         // streams / workspace it runs on
+        cudaStream_t gs = l->lane[i % nlane].gstream;
         const unsigned char* q = a.queries + a.q_offsets[i];
         // d_local / d_final of this lane are about to be overwritten: its previous gather and copy-out must be done
         if (ln.gathered_once) CU(cudaStreamWaitEvent(ws->stream, ln.ev_gather, 0));
@@ -554,20 +559,21 @@ int rank_batch(pyopal_cuda_mdb* m, int L, const BatchArgs& a, bool output, int64
             int rc = enqueue_score_search(l->db, ws, q, a.q_lengths[i], a.go, a.ge, a.M, a.A, a.mode, lo, hi, ln.d_local + lo, ws->stream);
             if (rc) return rc;
             *launches += ws->stats[0];
+            l->db->publish(ws);
         }
         CU(cudaEventRecord(ln.ev_search, ws->stream));
-        CU(cudaStreamWaitEvent(ln.gstream, ln.ev_search, 0));
+        CU(cudaStreamWaitEvent(gs, ln.ev_search, 0));
         const int32_t* final_rows = ln.d_local + lo;
         if (!m->identity) {
             if (m->world > 1) {
-                NC(g_nccl.AllGather(ln.d_local, ln.d_gathered, (size_t)m->n_pad, NCCL_INT32, l->comm, ln.gstream));
+                NC(g_nccl.AllGather(ln.d_local, ln.d_gathered, (size_t)m->n_pad, NCCL_INT32, l->comm, gs));
             } else {
-                CU(cudaMemcpyAsync(ln.d_gathered, ln.d_local, (size_t)m->n_pad * sizeof(int32_t), cudaMemcpyDeviceToDevice, ln.gstream));
+                CU(cudaMemcpyAsync(ln.d_gathered, ln.d_local, (size_t)m->n_pad * sizeof(int32_t), cudaMemcpyDeviceToDevice, gs));
             }
             if (output) {  // only the rank that hands the result out puts it in database order
                 const int64_t total = m->n_pad * m->world;
                 const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>((total + 255) / 256, 148 * 8));
-                unpermute_kernel<<<blocks, 256, 0, ln.gstream>>>(ln.d_gathered, l->d_dest, total, a.start, a.end, ln.d_final);
+                unpermute_kernel<<<blocks, 256, 0, gs>>>(ln.d_gathered, l->d_dest, total, a.start, a.end, ln.d_final);
                 CU(cudaGetLastError());
             }
             *launches += (m->world > 1 ? 1 : 0) + (output ? 1 : 0);
@@ -576,11 +582,11 @@ int rank_batch(pyopal_cuda_mdb* m, int L, const BatchArgs& a, bool output, int64
         if (kk > 0 && output) {
             if (ln.tk_ws.reserve(topk_workspace_words()) || ln.tk_vals.reserve((size_t)kk) || ln.tk_idx.reserve((size_t)kk))
                 return PYOPAL_CUDA_ERR_NOMEM;
-            int rc = topk_device(final_rows, nout, kk, ln.tk_vals.p, ln.tk_idx.p, ln.tk_ws.p, l->db->sm_count, ln.gstream);
+            int rc = topk_device(final_rows, nout, kk, ln.tk_vals.p, ln.tk_idx.p, ln.tk_ws.p, l->db->sm_count, gs);
             if (rc) return rc;
             *launches += 9;
         }
-        CU(cudaEventRecord(ln.ev_gather, ln.gstream));
+        CU(cudaEventRecord(ln.ev_gather, gs));
         ln.gathered_once = true;
         if (i > 0) { int rc = copy_out(i - 1); if (rc) return rc; }
     }

@@ -791,17 +791,22 @@ int pyopal_end_full_search(pyopal_cuda_db* db, Workspace* ws, const unsigned cha
             // reserve the job area first: [all-target jobs (full mode) | spill jobs | overflow jobs]
             if (ws->pd_jobs.reserve((size_t)njobs * sizeof(PairJob) * 2 + 4096)) return PYOPAL_CUDA_ERR_NOMEM;
             CU(cudaEventRecord(ws->ev_aux0, st));
-            int rc = enqueue_score_search_ex(db, ws, query, Lq, go, ge, M, A, mode, start, end, d_res, st, &ep);
-            if (rc) return rc;
-            packed_done = true;
-            if (!ep.spill.empty()) {
+            bool spilled = false;
+            ep.launch_spill = [&]() -> int {
                 host_forward_jobs(db, ep.spill.data(), ep.spill.size(), false, Lq, start, hjobs0);
                 CU(cudaStreamWaitEvent(ws->side2, ws->ev_aux0, 0));
-                rc = locate(hjobs0, (size_t)njobs * sizeof(PairJob), d_ctl, ws->side2);
-                if (rc) return rc;
+                int r = locate(hjobs0, (size_t)njobs * sizeof(PairJob), d_ctl, ws->side2);
+                if (r) return r;
                 CU(cudaEventRecord(ws->ev_aux1, ws->side2));
-                CU(cudaStreamWaitEvent(st, ws->ev_aux1, 0));
-            }
+                spilled = true;
+                return 0;
+            };
+            const int64_t launches_before = ws->stats[0];
+            int rc = enqueue_score_search_ex(db, ws, query, Lq, go, ge, M, A, mode, start, end, d_res, st, &ep);
+            if (rc) return rc;
+            (void)launches_before;
+            packed_done = true;
+            if (spilled) CU(cudaStreamWaitEvent(st, ws->ev_aux1, 0));
             if (ep.packed && mode == MODE_SW) {
                 // 16-bit overflows: the list was produced on the device; fetch it and locate those at 32 bit
                 int32_t novf = 0;

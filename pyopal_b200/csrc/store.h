@@ -12,6 +12,7 @@
 #include <algorithm>
 #include <condition_variable>
 #include <cstdint>
+#include <functional>
 #include <memory>
 #include <mutex>
 #include <string>
@@ -107,6 +108,7 @@ struct Tuning {
     int tg_warps = 4, tg_K = 32, tg_split = -1;
     double solo = 0.0, gmul = 1.0, mid = 0.0;
     int pair_k = 0, pair_c = 0;
+    int lanes = 1;   // searches in flight per batched call
     void load();
 };
 
@@ -132,12 +134,13 @@ struct Workspace {
     int par_next = 0;
     DevBuf<unsigned char> d_par;
     // score search
-    DevBuf<int32_t> ovf, out;
+    DevBuf<int32_t> ovf, out, out2;   // out2: second row buffer of the stream-ordered batch
     DevBuf<int8_t> gprofile;
     DevBuf<int32_t> wprofile;
     DevBuf<uint32_t> bndH, bndF, bnd32H, bnd32F;
     DevBuf<int32_t> end_out;  // packed end mode: [score | endQ | endT] rows
     int64_t stats[12] = {0};
+    int32_t* d_ovf_count = nullptr;  // device: number of 16-bit overflows of the last SW search on this workspace
     // end / full modes (pairdp.cu)
     DevBuf<int32_t> pd_i32;     // per-target int results and job tables
     DevBuf<uint8_t> pd_tb;      // traceback direction bytes
@@ -147,7 +150,7 @@ struct Workspace {
     DevBuf<uint8_t> pd_query;   // query + matrix of the end / full passes
     // top-k selection (topk.cu)
     DevBuf<uint32_t> tk_ws;
-    DevBuf<int32_t> tk_vals, tk_idx;
+    DevBuf<int32_t> tk_vals, tk_idx, tk_vals2, tk_idx2;
 
     int init(int device);
     void destroy();
@@ -190,6 +193,7 @@ struct pyopal_cuda_db {
 
     pyopal::Workspace* acquire();       // nullptr + fail() on error
     void release(pyopal::Workspace* ws);
+    void publish(pyopal::Workspace* ws); // make ws's statistics the handle's "last search" without releasing it
 };
 
 namespace pyopal {
@@ -216,6 +220,7 @@ struct EndPlan {
     int32_t* d_ovf = nullptr;           // out: device list of (pair << 1 | half) whose 16-bit score overflowed ...
     int32_t* d_ovf_count = nullptr;     // ... and its device-side length
     bool packed = false;                // out: a 16-bit launch was enqueued
+    std::function<int()> launch_spill;  // in: called once `spill` is known and BEFORE the 16-bit launches
 };
 
 // api.cu: enqueue a SCORE search of [start, end) on `st` with workspace `ws`; scores land in d_out (device).
