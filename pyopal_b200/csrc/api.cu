@@ -727,6 +727,12 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
     const bool endm = endp != nullptr;
     const Tuning& tune = db->tune;
     if (endm) { endp->spill.clear(); endp->d_ovf = nullptr; endp->d_ovf_count = nullptr; endp->packed = false; }
+    // PYOPAL_CUDA_DEBUG: synchronise after every launch and name the one that failed
+    auto dbg = [&](const char* what) {
+        if (!tune.debug) return;
+        const cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) fprintf(stderr, "[pyopal_cuda] after %s: %s\n", what, cudaGetErrorString(e));
+    };
 
     // a workspace is reused across streams: wait for its previous search, mark the end of this one
     if (ws->used) CU(cudaStreamWaitEvent(st, ws->ev_free, 0));
@@ -928,6 +934,7 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
     CU(cudaMemcpyAsync(dp, hp, par_bytes, cudaMemcpyHostToDevice, st));
     CU(cudaEventRecord(ws->par_done[slot], st));
     ws->par_used[slot] = true;
+    dbg("parameter block");
     if (endm && endp->launch_spill && !endp->spill.empty()) {
         // the targets left to pairdp.cu go first, on their own high-priority stream: launched behind the persistent
         // CTAs of the 16-bit kernels they would only start when those drain
@@ -1020,6 +1027,7 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
         CU(cudaGetLastError());
         CU(cudaEventRecord(ws->ev_join2, ws->side2));
         ws->stats[0]++;
+        dbg("tgiants");
     }
     if (ng > 0) {
         search_kernel_t kgiant = get_giant_kernel(gK, local);
@@ -1040,6 +1048,7 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
         kgiant<<<(unsigned)std::min<int64_t>((ng + teams - 1) / teams, gcap), 512, gsmem_all, side>>>(Q);
         CU(cudaGetLastError());
         ws->stats[0]++;
+        dbg("giants");
     }
     if (n32 > 0) {
         KParams Q = P;
@@ -1049,6 +1058,7 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
         Q.bndH = ws->bnd32H.p; Q.bndF = ws->bnd32F.p;
         int rc = launch_search(db, ws, k32, Q, tail.smem, 32, n32, side);
         if (rc) return rc;
+        dbg("static32");
     }
     if (mid_work) {
         search_kernel_t kt = pick_kernel(tail.K, 16, local, tail.psmem, rung.tdadd, endm);
@@ -1067,6 +1077,7 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
                                               (int64_t)(1.15 * share * db->sm_count * 14.0 / (mthreads / 32) + 0.999));
         int rc = launch_search(db, ws, kt, Q, tail.smem, mthreads, ntail, side, cap);
         if (rc) return rc;
+        dbg("mid");
     }
     if (side_work) {
         if (nt > 0) CU(cudaStreamWaitEvent(side, ws->ev_join2, 0));  // joins only after everything is launched
@@ -1097,6 +1108,7 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
         if (rc) return rc;
         CU(cudaEventRecord(ws->kev[3], st));
         ws->kev_valid[1] = true;
+        dbg("bulk");
     }
     if (side_work) CU(cudaStreamWaitEvent(st, ws->ev_join, 0));
 
@@ -1112,6 +1124,7 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
         if (rc) return rc;
         CU(cudaEventRecord(ws->kev[5], st));
         ws->kev_valid[2] = true;
+        dbg("rescue");
     }
     ws->stats[1] = n16 * 2; ws->stats[2] = n32 + ng + nt;
     ws->stats[5] = bulk.G; ws->stats[6] = bulk.K; ws->stats[7] = bulk.npass; ws->stats[11] = bulk.psmem ? 1 : 0;

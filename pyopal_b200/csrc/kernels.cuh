@@ -138,6 +138,7 @@ __device__ __forceinline__ int profile_entry(const KParams& P, int letter, int s
     const int trow = chunk * P.krows + within;
     int qi = trow - P.padtop;
     if (qi < 0 || letter >= P.A) return P.pad_score;
+    if (qi >= P.Lq) return 0;  // slots past the last chunk (pitch rounding): never read, and the query ends here
     return P.matrix[(int)P.query[qi] * P.A + letter] + P.go;
 }
 

@@ -212,7 +212,8 @@ def test_config4_top_hits_end_and_full(full, oracle, cuda, qi, algo):
             for j in range(len(top)):
                 assert bytes(ops[oo[j] : oo[j] + ol[j]]) == want["alignment"][j], (algo, mode, j)
     stats = sub.stats()
-    assert stats["K"] in (4, 8) and stats["passes"] > 1  # the latency-bound shape was chosen
+    if qi >= 2:  # queries of 1000+ aa against a handful of very long hits: the latency-bound shape was chosen
+        assert stats["K"] in (4, 8) and stats["passes"] > 1
 
 
 @pytest.mark.parametrize("qi,algo", [(1, "sw"), (3, "sw"), (3, "hw")])
