@@ -149,6 +149,8 @@ void Tuning::load() {
     no_tail = getenv("PYOPAL_CUDA_NO_TAIL") != nullptr;
     no_end16 = getenv("PYOPAL_CUDA_NO_END16") != nullptr;
     no_mid = getenv("PYOPAL_CUDA_NO_MID") != nullptr;
+    no_stream = getenv("PYOPAL_CUDA_NO_STREAM") != nullptr;
+    if (const char* v = getenv("PYOPAL_CUDA_STREAM")) force_stream = atoi(v) > 0;
     debug = getenv("PYOPAL_CUDA_DEBUG") != nullptr;
     if (const char* ov = getenv("PYOPAL_CUDA_TGIANT")) {  // "warps,K[,split]"
         int a = 0, b = 0, c = -1;
@@ -542,6 +544,7 @@ Plan make_plan(int Lq, int A, const pyopal_cuda_db* db, size_t smem_limit, Giant
         return (double)((k1 < db->npairs ? db->h_pair_off[(size_t)k1] : db->ncols) - (k0 < db->npairs ? db->h_pair_off[(size_t)k0] : db->ncols));
     };
     for (int logG = 2; logG <= 5; logG++) {
+        if (tune.has_plan && logG != tune.plan_logG) continue;  // a forced tile still gets the giants that go with it
         const int G = 1 << logG;
         // calibrated on 1/2, 1/4 and 1/8 shards of config 2 (scratch/shard_sweep.py): groups of 8+ lanes reach the
         // critical path about 25 % earlier than 448 / G groups per SM suggest; 4-lane groups do not
@@ -575,10 +578,14 @@ Plan make_plan(int Lq, int A, const pyopal_cuda_db* db, size_t smem_limit, Giant
         const double mid_cost = (double)tailp.npass * (cols_mid + 31.0 * n_mid) *
                                 (C0 + (tailp.npass > 1 ? 12.0 : 0.0) + C1 * tailp.K) * 32.0;
         for (int K = 4; K <= 40; K += 4) {
+            if (tune.has_plan && K != tune.plan_K) continue;
             const int T = G * K;
             const int npass = (Lq + T - 1) / T;
             // several passes also pay the boundary round trip through L2 every step
-            const double cost = stretch * (double)npass * (cols_bulk + (G - 1) * n_bulk) *
+            // measured on config 2 (round 2, scratch/run_gpu5.sh sweeps): at the 128-register cap the deepest
+            // tiles schedule worse than K = 28 (5262 GCUPS at K = 28, 5107 / 5160 at 32 / 36, 4514 at 40)
+            const double deep = (K == 40) ? 1.10 : (K >= 32) ? 1.06 : 1.0;
+            const double cost = stretch * deep * (double)npass * (cols_bulk + (G - 1) * n_bulk) *
                                     (C0 + (npass > 1 ? 12.0 : 0.0) + C1 * K) * (double)G +
                                 mid_cost + giant_cost;
             if (cost < best_cost - 1e-9) {
@@ -588,11 +595,7 @@ Plan make_plan(int Lq, int A, const pyopal_cuda_db* db, size_t smem_limit, Giant
             }
         }
     }
-    if (tune.has_plan) {  // "logG,K[,threads]": tuning override
-        best.G = 1 << tune.plan_logG; best.logG = tune.plan_logG; best.K = tune.plan_K;
-        best.npass = (Lq + best.G * best.K - 1) / (best.G * best.K);
-        best_kmid = best_kg;
-    }
+    if (tune.has_plan) best_kmid = best_kg;  // "logG,K[,threads]": tuning override, no mid tier
     if (gp) gp->kg = best_kg;
     if (kmid_out) *kmid_out = best_kmid;
     best = finish_plan(best, Lq, A, smem_limit);
@@ -766,7 +769,7 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
     GiantPolicy gpol;
     int gK = 4, gwarps = 1, gteams = 1, gpitch = 0;
     size_t gsmem = 0;
-    bool use_t = false, old_giants_ok = false, bfix = false, wide = false, same_plan = true;
+    bool use_t = false, old_giants_ok = false, bfix = false, wide = false, same_plan = true, stream = false;
     int tK = 32, tNW = 4, tpitch = 0, tsplit_override = -1;
     size_t tsmem = 0;
     const int smem_optin = db->smem_optin;
@@ -819,8 +822,15 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
             gpol.cap = (int64_t)db->sm_count * 8;
             gpol.col_cost = 56.0 * 40.0 * (double)std::max(1, (Lq + 127) / 128);
         }
+        // whole-database score searches run the bulk as one continuous wavefront per group (stream.cuh)
+        stream = !endm && !tune.no_stream && start == 0 && end >= db->n && fits8 && ge <= go && !bfix &&
+                 db->ncols < ((int64_t)1 << 31);
         const bool allow_mid = tune.mid > 0 && !tune.no_tail && !tune.has_plan;  // opt-in (PYOPAL_CUDA_MID): see DESIGN.md 4.1
         bulk = make_plan(Lq, A, db, SMEM_LIMIT, &gpol, allow_mid, &kmid);
+        // ... and only where it pays: wide groups (the fill steps it removes are (G - 1) per pair and pass) of deep
+        // tiles (its longer step prologue is amortised over K rows).  Measured on a 1/8 shard of config 2: + 5.5 % at
+        // G = 32, K = 32; - 12 % at G = 16, K = 20.  PYOPAL_CUDA_STREAM=1 forces it (tests).
+        if (stream && !tune.force_stream && !(bulk.G >= 16 && bulk.K >= 28)) stream = false;
         tail = make_tail_plan(Lq, A, SMEM_LIMIT);
         int smax = INT_MIN, smin = INT_MAX;
         for (int i = 0; i < A * A; i++) { smax = std::max(smax, M[i]); smin = std::min(smin, M[i]); }
@@ -831,6 +841,7 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
             // profile in global memory: one tile shape (32 x 32) for every launch
             bulk = make_forced_plan(Lq);
             tail = bulk;
+            stream = false;
         }
         {
             // 32-bit overflow cannot happen below this bound (scores are exact otherwise)
@@ -844,7 +855,7 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
 
         // ---- split the (length-sorted) pairs ------------------------------------
         // [0, kg): giants; [kg, n32p): 32-bit static; [n32p, tail_end): 16-bit mid tier; rest: 16-bit bulk
-        if (!rung.ok16) n32p = db->npairs;
+        if (!rung.ok16) { n32p = db->npairs; stream = false; }
         else if (!local) n32p = first_pair_at_most(db, (double)rung.max_cols16, 0);
         const bool giants_ok = gpol.ok && bulk.psmem && !wide;
         kg = giants_ok ? gpol.kg : 0;
@@ -1089,20 +1100,26 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
     // ---- bulk -------------------------------------------------------------------
     if (nbulk > 0) {
         search_kernel_t kb = pick_kernel(bulk.K, 16, local, bulk.psmem, rung.tdadd, endm);
+        if (stream && whole) {
+            search_kernel_t ks = local ? get_stream_kernel_l1(bulk.K, rung.tdadd) : get_stream_kernel_l0(bulk.K, rung.tdadd);
+            if (ks) kb = ks; else stream = false;
+        } else stream = false;
         if (!kb) return fail(PYOPAL_CUDA_ERR_INTERNAL, "no 16-bit kernel for this tile");
         KParams Q = P;
         apply_plan(Q, bulk);
         Q.worklist = d_wl_bulk; Q.nwork = d_counts + 0; Q.counter = d_counts + 4;
+        Q.first_pair = (int)(same_plan ? n32p : tail_end);
         Q.neg = rung.neg16; Q.bias = rung.bias16;
         const int gpw = 32 >> bulk.logG;
         // one CTA per SM when the profile is large: use the whole register file with 16 warps
         // (with side-stream CTAs resident, 7-warp CTAs leave them registers: 2 x 224 x 128 < 64K)
         int threads = (bulk.smem > (size_t)110 * 1024) ? (side_work ? 480 : 512) : (side_work ? 224 : 256);
+        if (stream) threads = 512;   // one CTA of 16 warps per SM: + 4.5 % over two of 7 (1/8 shard, 1000-aa query)
         if (tune.plan_threads) threads = tune.plan_threads;
         CU(cudaEventRecord(ws->kev[2], st));
         if (tune.debug)
-            fprintf(stderr, "[pyopal_cuda] Lq=%d %s bulk: G=%d K=%d npass=%d pairs=%lld | mid=%lld (K=%d npass=%d) giants=%lld tgiants=%lld static32=%lld spill=%lld threads=%d smem=%zu\n",
-                    Lq, endm ? "END" : "score", bulk.G, bulk.K, bulk.npass, (long long)nbulk, (long long)(mid_work ? ntail : 0), tail.K,
+            fprintf(stderr, "[pyopal_cuda] Lq=%d %s%s bulk: G=%d K=%d npass=%d pairs=%lld | mid=%lld (K=%d npass=%d) giants=%lld tgiants=%lld static32=%lld spill=%lld threads=%d smem=%zu\n",
+                    Lq, endm ? "END" : "score", stream ? " (stream)" : "", bulk.G, bulk.K, bulk.npass, (long long)nbulk, (long long)(mid_work ? ntail : 0), tail.K,
                     tail.npass, (long long)ng, (long long)nt, (long long)n32, (long long)(endm ? endp->spill.size() : 0), threads, bulk.smem);
         int rc = launch_search(db, ws, kb, Q, bulk.smem, threads, (nbulk + gpw - 1) / gpw, st);
         if (rc) return rc;

@@ -77,6 +77,7 @@ struct KParams {
     // pass boundary (row above the tile): W=16 indexed like `stream`, W=32 at 2*column + half
     uint32_t* bndH;
     uint32_t* bndF;
+    int first_pair;           // stream_kernel (stream.cuh): task t is pair first_pair + t
 };
 
 // ---------------------------------------------------------------------------
@@ -626,6 +627,9 @@ search_kernel_t get_search_kernel_w32_l0(int K, bool psmem);
 search_kernel_t get_search_kernel_wide(bool local);  // K = 32, W = 32
 // NW with gap_extend > gap_open: K = 32, W = 32, profile in global memory (int8, or int32 when `wide`)
 search_kernel_t get_search_kernel_bfix(bool wide);
+// stream.cuh: the 16-bit score kernel as a continuous wavefront (whole-database searches)
+search_kernel_t get_stream_kernel_l1(int K, bool tdadd);
+search_kernel_t get_stream_kernel_l0(int K, bool tdadd);
 // giant.cu: a team of warps per target (KParams.G = warps per team, KParams.npass = teams per CTA), K = 4 or 8
 search_kernel_t get_giant_kernel(int K, bool local);
 size_t giant_smem_bytes(int A, int pitch, int warps_per_team, int teams);

@@ -104,6 +104,8 @@ struct Tuning {
     bool has_plan = false;
     int plan_logG = 0, plan_K = 0, plan_threads = 0;
     bool no_giant = false, no_tgiant = false, no_tail = false, debug = false, no_end16 = false, no_mid = false;
+    bool no_stream = false;   // keep whole-database score searches on search_kernel (one pair per task)
+    bool force_stream = false;  // ... or run them on stream_kernel whatever the tile
     bool has_tgiant = false;
     int tg_warps = 4, tg_K = 32, tg_split = -1;
     double solo = 0.0, gmul = 1.0, mid = 0.0;

@@ -125,6 +125,41 @@ def test_four_way_shards_reproduce_whole(full, cuda):
     assert max(totals) - min(totals) <= int(lengths.max())
 
 
+def test_stream_kernel_equals_classic_on_a_shard(full, cuda, oracle, monkeypatch):
+    # rank 0's 1/8 shard of config 2 (what one GPU of an 8-GPU box searches): the planner picks 32-lane tiles there
+    # and hands them to the continuous-wavefront kernel (csrc/stream.cuh); its scores must equal the classic
+    # kernel's for every query of the step (one and several passes), for NW on the longest query, and the oracle's
+    # on a subsample
+    db = full["db"]
+    mine = np.asarray(sharding.shard_indices(db[2], 8, 0))
+    sr, so, sl = synthetic.pack_subset(db, mine)
+    rows = {}
+    for env in ("PYOPAL_CUDA_NO_STREAM", "PYOPAL_CUDA_STREAM"):
+        monkeypatch.delenv("PYOPAL_CUDA_NO_STREAM", raising=False)
+        monkeypatch.delenv("PYOPAL_CUDA_STREAM", raising=False)
+        monkeypatch.setenv(env, "1")
+        store = cuda.DeviceStore(sr, so, np.ascontiguousarray(sl), 24, device=0)
+        rows[env] = [np.frombuffer(store.search(q, GO, GE, full["M"], 0, 3)[0], dtype=np.int32).copy() for q in full["queries"]]
+        rows[env].append(np.frombuffer(store.search(full["queries"][4], GO, GE, full["M"], 0, 0)[0], dtype=np.int32).copy())
+        rows[env].append(np.frombuffer(store.search(full["queries"][2], GO, GE, full["M"], 0, 2)[0], dtype=np.int32).copy())
+        store.close()
+    for a, b in zip(rows["PYOPAL_CUDA_NO_STREAM"], rows["PYOPAL_CUDA_STREAM"]):
+        assert np.array_equal(a, b)
+    monkeypatch.delenv("PYOPAL_CUDA_STREAM", raising=False)
+    store = cuda.DeviceStore(sr, so, np.ascontiguousarray(sl), 24, device=0)   # the default: the planner's choice
+    rng = np.random.Generator(np.random.PCG64(31))
+    idx = np.unique(np.concatenate([rng.choice(len(sl), 1500, replace=False), np.nonzero(sl >= 10_000)[0]]))
+    sub = synthetic.pack_subset((sr, so, sl), idx)
+    for qi in (2, 4):
+        q = full["queries"][qi]
+        got = np.frombuffer(store.search(q, GO, GE, full["M"], 0, 3)[0], dtype=np.int32)
+        assert np.array_equal(got, rows["PYOPAL_CUDA_STREAM"][qi])
+        want = oracle.search_flat(q, sub[0].tobytes() + b"\0", array.array("q", sub[1].tolist()), array.array("i", sub[2].tolist()),
+                                  full["M"], 24, GO, GE, "sw", "score", 8)["score"]
+        assert got[idx].tolist() == list(want), qi
+    store.close()
+
+
 def test_batch_equals_single_full_size(full):
     qs = full["queries"][:3]
     flat = np.frombuffer(full["store"].search_batch(qs, GO, GE, full["M"], 3), dtype=np.int32)

@@ -220,3 +220,24 @@ def test_fuzz_end_full_long(cuda, oracle, seed):
     for algo in ALGOS:
         for mode in ("end", "full"):
             check_mode(oracle, aligner, query.tobytes(), seqs, algo, mode)
+
+
+@pytest.mark.parametrize("seed", range(max(24, N_SCORE // 3)))
+def test_fuzz_forced_stream(cuda, oracle, monkeypatch, seed):
+    # the continuous-wavefront kernel (csrc/stream.cuh) forced for every whole-database score search
+    # (PYOPAL_CUDA_STREAM=1; by default it only takes wide, deep tiles) under random tiles: several passes with the
+    # boundary rows handed from a group's last lane to its first, segments shorter than a group, more groups than
+    # pairs, every algorithm, matrices with negative folded scores (the packed-adder path)
+    rng = np.random.Generator(np.random.PCG64(7000 + seed))
+    letters, rows, go, ge, query, seqs = _case(3000 + seed)
+    monkeypatch.setenv("PYOPAL_CUDA_STREAM", "1")
+    monkeypatch.setenv("PYOPAL_CUDA_PLAN", f"{int(rng.integers(2, 6))},{4 * int(rng.integers(1, 11))}")
+    alphabet = pyopal.Alphabet(letters)
+    aligner = pyopal.Aligner(pyopal.ScoringMatrix(rows, letters), go, ge)
+    db = make_db(seqs, alphabet)
+    flat = [int(v) for row in rows for v in row]
+    for algo in ALGOS:
+        want = oracle.search(query, seqs, flat, len(letters), go, ge, algo, "score", threads=8)["score"]
+        got = list(aligner.align_scores(alphabet.decode(query), db, algorithm=algo))
+        bad = [i for i, (a, b) in enumerate(zip(got, want)) if a != b]
+        assert not bad, (seed, algo, go, ge, os.environ["PYOPAL_CUDA_PLAN"], [(i, got[i], want[i], len(seqs[i])) for i in bad[:4]])
