@@ -679,9 +679,21 @@ search_kernel_t pick_kernel(int K, int W, bool local, bool psmem, bool tdadd = t
 int launch_search(pyopal_cuda_db* db, Workspace* ws, search_kernel_t fn, const KParams& P, size_t smem, int threads,
                   int64_t max_tasks, cudaStream_t st, int64_t grid_cap = 0) {
     CU(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // Shared-memory carve-out.  Left to the driver, a launch whose CTAs need more shared memory than the
+    // configuration the previous kernel left behind can run with ONE resident CTA per SM where the occupancy query
+    // promises two: persistent CTAs never leave the SM idle, so it is never reconfigured (measured: the 2000-aa
+    // query at 3.4 instead of 5.2 TCUPS inside a batch, a 2 x 59 KB launch at a quarter of its speed).  Asking for
+    // everything costs the L1 that caches the residue stream (- 2 %), so ask for what the resident CTAs need.
+    CU(cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
     int per_sm = 0;
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, threads, smem));
     if (per_sm < 1) return fail(PYOPAL_CUDA_ERR_INTERNAL, "kernel does not fit on an SM");
+    {
+        const size_t need = (size_t)per_sm * (smem + 1024) + 1024;   // 1 KB per CTA is reserved by the system
+        const size_t all = (size_t)db->smem_optin + 1024;
+        const int pct = (int)std::min<size_t>(100, (need * 100 + all - 1) / all);
+        CU(cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+    }
     int64_t grid = (int64_t)db->sm_count * per_sm;
     const int64_t need = (max_tasks + (threads / 32) - 1) / (threads / 32);
     grid = std::min(grid, need);
@@ -830,7 +842,7 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
         // ... and only where it pays: wide groups (the fill steps it removes are (G - 1) per pair and pass) of deep
         // tiles (its longer step prologue is amortised over K rows).  Measured on a 1/8 shard of config 2: + 5.5 % at
         // G = 32, K = 32; - 12 % at G = 16, K = 20.  PYOPAL_CUDA_STREAM=1 forces it (tests).
-        if (stream && !tune.force_stream && !(bulk.G >= 16 && bulk.K >= 28)) stream = false;
+        if (stream && !tune.force_stream && !(bulk.G >= 16 && bulk.K >= 28 && bulk.npass <= 2)) stream = false;
         tail = make_tail_plan(Lq, A, SMEM_LIMIT);
         int smax = INT_MIN, smin = INT_MAX;
         for (int i = 0; i < A * A; i++) { smax = std::max(smax, M[i]); smin = std::min(smin, M[i]); }
@@ -1111,10 +1123,11 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
         Q.first_pair = (int)(same_plan ? n32p : tail_end);
         Q.neg = rung.neg16; Q.bias = rung.bias16;
         const int gpw = 32 >> bulk.logG;
-        // one CTA per SM when the profile is large: use the whole register file with 16 warps
-        // (with side-stream CTAs resident, 7-warp CTAs leave them registers: 2 x 224 x 128 < 64K)
-        int threads = (bulk.smem > (size_t)110 * 1024) ? (side_work ? 480 : 512) : (side_work ? 224 : 256);
-        if (stream) threads = 512;   // one CTA of 16 warps per SM: + 4.5 % over two of 7 (1/8 shard, 1000-aa query)
+        // One CTA per SM that fills the register file (16 warps x 32 lanes x 128 registers): one copy of the profile
+        // per SM and one shared-memory configuration whatever the query length (two 7- or 8-warp CTAs were 0-5 %
+        // slower, and see launch_search on carve-outs); 15 warps when one-warp CTAs of the 32-bit rung or the mid
+        // tier run beside it, so that they find registers on every SM.  The giants take whole SMs either way.
+        int threads = (n32 > 0 || mid_work) ? 480 : 512;
         if (tune.plan_threads) threads = tune.plan_threads;
         CU(cudaEventRecord(ws->kev[2], st));
         if (tune.debug)
