@@ -186,7 +186,9 @@ void pyopal_host_offsets_from_lengths(const int32_t* lengths, int64_t n, int64_t
  * at run time (dlopen libnccl.so.2; PYOPAL_NCCL_LIB or pyopal_cuda_nccl_load() name another copy). */
 typedef struct pyopal_cuda_mdb pyopal_cuda_mdb;
 
-int pyopal_cuda_nccl_load(const char* path);          /* optional: bind this libnccl instead of the default one */
+int pyopal_cuda_nccl_load(const char* path);          /* optional: bind this libnccl instead of the default one; a copy the
+                                                          process has already mapped (e.g. PyTorch's) always wins */
+int pyopal_cuda_nccl_loaded(void);                    /* 1 once NCCL is bound */
 int pyopal_cuda_nccl_version(void);                   /* e.g. 22809, 0 if NCCL cannot be loaded */
 int pyopal_cuda_nccl_unique_id(unsigned char id[128]); /* ncclGetUniqueId: rank 0 creates it, the caller distributes it */
 

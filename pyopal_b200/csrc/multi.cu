@@ -53,13 +53,17 @@ int nccl_load(const char* explicit_path) {
     std::lock_guard<std::mutex> lock(g_nccl_mu);
     if (g_nccl.so) return 0;
     std::vector<std::string> names;
+    // a copy the process has already mapped wins (RTLD_NOLOAD): one NCCL per process, whoever came first
     if (explicit_path && *explicit_path) names.push_back(explicit_path);
     if (const char* e = getenv("PYOPAL_NCCL_LIB")) names.push_back(e);
     names.push_back("libnccl.so.2");
     names.push_back("libnccl.so");
     std::string errs;
+    bool first = true;
     for (const std::string& nm : names) {
-        void* so = dlopen(nm.c_str(), RTLD_NOW | RTLD_GLOBAL);
+        // no RTLD_GLOBAL: this library looks its symbols up with dlsym and must not shadow anybody else's
+        void* so = first ? dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD) : dlopen(nm.c_str(), RTLD_NOW | RTLD_LOCAL);
+        if (first) { first = false; if (!so) so = dlopen(nm.c_str(), RTLD_NOW | RTLD_LOCAL); }
         if (!so) { errs += std::string(dlerror() ? dlerror() : "?") + "; "; continue; }
         Nccl n;
         n.so = so;
@@ -264,6 +268,15 @@ int local_setup(pyopal_cuda_mdb* m, Local* l, const int32_t* dest_all) {
 extern "C" {
 
 int pyopal_cuda_nccl_load(const char* path) { return nccl_load(path); }
+
+int pyopal_cuda_nccl_loaded(void) {
+    std::lock_guard<std::mutex> lock(g_nccl_mu);
+    if (g_nccl.so) return 1;
+    void* so = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);   // mapped by somebody else already?
+    if (!so) return 0;
+    dlclose(so);
+    return 0;   // not bound yet; nccl_load(NULL) will pick the mapped copy up
+}
 
 int pyopal_cuda_nccl_version(void) {
     if (nccl_load(nullptr)) return 0;

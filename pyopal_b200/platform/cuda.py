@@ -501,7 +501,8 @@ class MultiDeviceStore:
         n = len(lengths)
         lengths = as_int32_array(lengths)
         devs = (ctypes.c_int * len(self.devices))(*self.devices)
-        self._ensure_nccl()
+        if len(self.devices) > 1:
+            self._ensure_nccl()
         check(
             lib.pyopal_cuda_mdb_create(devs, len(self.devices), _addr(residues), _addr(offsets), _addr(lengths), n,
                                        alphabet_length, ctypes.byref(self._handle))
@@ -523,10 +524,16 @@ class MultiDeviceStore:
 
     @staticmethod
     def _ensure_nccl():
-        """Bind NCCL: the system copy, else the one shipped with the ``nvidia-nccl-cu12`` wheel (found by path, not
-        imported)."""
+        """Bind NCCL (only handles that span several GPUs need it).
+
+        Order: a copy this process has already mapped (e.g. by an earlier ``import torch``), else the one shipped
+        with the ``nvidia-nccl-cu12`` wheel (found by path, not imported), else the system's.  The wheel goes before
+        the system copy on purpose: libraries are matched by soname, so whichever ``libnccl.so.2`` is mapped first
+        is the one every later ``import`` in the process gets, and an older system NCCL under a newer PyTorch makes
+        ``import torch`` fail with an undefined symbol.
+        """
         lib = load_library()
-        if lib.pyopal_cuda_nccl_version() > 0:
+        if lib.pyopal_cuda_nccl_loaded():
             return
         import sys
 
@@ -534,6 +541,7 @@ class MultiDeviceStore:
             cand = os.path.join(base, "nvidia", "nccl", "lib", "libnccl.so.2")
             if os.path.exists(cand) and lib.pyopal_cuda_nccl_load(cand.encode()) == 0:
                 return
+        lib.pyopal_cuda_nccl_version()  # default search: PYOPAL_NCCL_LIB, libnccl.so.2 on the loader's path
 
     def close(self):
         handle = getattr(self, "_handle", None)

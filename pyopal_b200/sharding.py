@@ -92,9 +92,10 @@ class ShardedDatabase(_cuda.MultiDeviceStore):
     """
 
     @classmethod
-    def _create(cls, fn, args, n_all, alphabet_length, device):
+    def _create(cls, fn, args, n_all, alphabet_length, device, world=1):
         handle = ctypes.c_void_p(None)
-        cls._ensure_nccl()
+        if world > 1:
+            cls._ensure_nccl()
         _cuda.check(fn(*args, ctypes.byref(handle)))
         return cls._wrap(handle, n_all, alphabet_length, [device])
 
@@ -108,7 +109,7 @@ class ShardedDatabase(_cuda.MultiDeviceStore):
             lib.pyopal_cuda_mdb_create_rank_dealt,
             (device, rank, world, _cuda._addr(nccl_id), _cuda._addr(residues), _cuda._addr(offsets), _cuda._addr(lens),
              len(lens), alphabet_length),
-            len(lens), alphabet_length, device,
+            len(lens), alphabet_length, device, world,
         )
         del keep
         self.rank, self.n_all = rank, len(lens)
@@ -135,7 +136,7 @@ class ShardedDatabase(_cuda.MultiDeviceStore):
             lib.pyopal_cuda_mdb_create_rank,
             (device, rank, world, _cuda._addr(nccl_id), _cuda._addr(residues), _cuda._addr(offsets), _cuda._addr(lens),
              len(lens), _cuda._addr(index), n_all, alphabet_length),
-            n_all, alphabet_length, device,
+            n_all, alphabet_length, device, world,
         )
         self.rank, self.n_all = rank, n_all
         return self
