@@ -402,12 +402,14 @@ def run_b200(args):
     res_local = sdb.local_residues(0)
     end_mode = args.mode == "end"
 
+    host_rows = array.array("i", bytes(4 * len(qbytes) * n_all))  # the caller's result buffer of the e2e leg, reused
+
     def step(to_host=False):
         if end_mode:  # score + end cell: the blocking call, host arrays out
             return [sdb.search(q, GAP_OPEN, GAP_EXTEND, M, 1, algo, lengths=lengths) for q in qbytes]
         if args.serial:
             return [sdb.search(q, GAP_OPEN, GAP_EXTEND, M, 0, algo)[0] for q in qbytes]
-        return sdb.search_batch(qbytes, GAP_OPEN, GAP_EXTEND, M, algo, to_host=to_host)
+        return sdb.search_batch(qbytes, GAP_OPEN, GAP_EXTEND, M, algo, to_host=to_host, out=host_rows if to_host else None)
 
     for _ in range(args.warmup):
         step()

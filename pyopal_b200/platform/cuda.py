@@ -590,14 +590,25 @@ class MultiDeviceStore:
         )
         return scores, eq, et, sq, st, ops, oo, ol
 
-    def search_batch(self, queries, gap_open, gap_extend, int_matrix, algorithm, start=0, end=None, to_host=True):
-        """Score-mode search of several encoded queries, two in flight per GPU; one ``array('i')`` of
-        nq * (end - start) scores, or ``None`` with ``to_host=False`` (results stay on the devices: timing)."""
+    def search_batch(self, queries, gap_open, gap_extend, int_matrix, algorithm, start=0, end=None, to_host=True, out=None):
+        """Score-mode search of several encoded queries, stream-ordered on every GPU; one ``array('i')`` of
+        nq * (end - start) scores, or ``None`` with ``to_host=False`` (results stay on the devices: timing).
+        ``out``: a writable int32 buffer of that size to receive the scores instead of a fresh array (a caller that
+        searches at a high rate reuses one: allocating and zero-filling tens of MB per call costs milliseconds)."""
         end = self.size if end is None or end > self.size else end
         blob, qo, ql = _pack_queries(queries)
         matrix = int_matrix if isinstance(int_matrix, array.array) else array.array("i", int_matrix)
         alen = int(round(len(matrix) ** 0.5))
-        scores = array.array("i", bytes(4 * len(queries) * max(end - start, 0))) if to_host else None
+        need = len(queries) * max(end - start, 0)
+        if not to_host:
+            scores = None
+        elif out is not None:
+            view = memoryview(out)
+            if view.readonly or view.nbytes != 4 * need or not view.c_contiguous:
+                raise ValueError("out must be a writable contiguous buffer of nq * (end - start) int32")
+            scores = out
+        else:
+            scores = array.array("i", bytes(4 * need))
         check(
             self._lib.pyopal_cuda_mdb_search_batch(
                 self._handle, _addr(blob), _addr(qo), _addr(ql), len(queries), gap_open, gap_extend, _addr(matrix),
