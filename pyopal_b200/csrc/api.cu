@@ -150,6 +150,9 @@ void Tuning::load() {
     no_end16 = getenv("PYOPAL_CUDA_NO_END16") != nullptr;
     no_mid = getenv("PYOPAL_CUDA_NO_MID") != nullptr;
     no_stream = getenv("PYOPAL_CUDA_NO_STREAM") != nullptr;
+    no_giant16 = getenv("PYOPAL_CUDA_NO_GIANT16") != nullptr;
+    no_dual = getenv("PYOPAL_CUDA_NO_DUAL") != nullptr;
+    if (const char* v = getenv("PYOPAL_CUDA_DUAL")) force_dual = atoi(v) > 0;
     if (const char* v = getenv("PYOPAL_CUDA_STREAM")) force_stream = atoi(v) > 0;
     debug = getenv("PYOPAL_CUDA_DEBUG") != nullptr;
     if (const char* ov = getenv("PYOPAL_CUDA_TGIANT")) {  // "warps,K[,split]"
@@ -189,7 +192,7 @@ int Workspace::init(int dev) {
 }
 
 void Workspace::destroy() {
-    ovf.release(); out.release(); out2.release(); gprofile.release(); wprofile.release(); end_out.release();
+    ovf.release(); ovf2.release(); out.release(); out2.release(); gprofile.release(); wprofile.release(); end_out.release();
     bndH.release(); bndF.release(); bnd32H.release(); bnd32F.release();
     pd_i32.release(); pd_tb.release(); pd_ops.release(); pd_jobs.release(); pd_team.release(); pd_query.release();
     tk_ws.release(); tk_vals.release(); tk_idx.release(); tk_vals2.release(); tk_idx2.release();
@@ -782,6 +785,7 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
     int gK = 4, gwarps = 1, gteams = 1, gpitch = 0;
     size_t gsmem = 0;
     bool use_t = false, old_giants_ok = false, bfix = false, wide = false, same_plan = true, stream = false;
+    bool packed_giants = false;
     int tK = 32, tNW = 4, tpitch = 0, tsplit_override = -1;
     size_t tsmem = 0;
     const int smem_optin = db->smem_optin;
@@ -895,13 +899,19 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
         };
         // giants longer than one slab of the transposed kernel go to tgiant.cu, the others to giant.cu
         const int tsplit = !use_t ? INT32_MAX : tsplit_override >= 0 ? tsplit_override : tNW * 32 * tK;
+        // Smith-Waterman: giant.cu walks the two targets of a pair together at 16 bit (its list holds pair ids then)
+        packed_giants = local && !endm && old_giants_ok && rung.ok16 && !tune.no_giant16;
         for (int64_t k = 0; k < kg; k++) {
+            if (packed_giants && db->h_pair_len[(size_t)(2 * k)] <= tsplit) {
+                if (pair_in_range(k)) wlg.push_back((int32_t)k);
+                continue;
+            }
             for (int h = 0; h < 2; h++) {
                 const int32_t ix = db->h_pair_idx[(size_t)(2 * k + h)];
                 if (ix < 0 || !in_range(ix)) continue;
                 const int32_t e = (int32_t)((k << 1) | h);
                 if (endm) endp->spill.push_back(e);
-                else if (db->h_pair_len[(size_t)(2 * k + h)] > tsplit || !old_giants_ok) wlt.push_back(e);
+                else if (db->h_pair_len[(size_t)(2 * k + h)] > tsplit || !old_giants_ok || packed_giants) wlt.push_back(e);
                 else wlg.push_back(e);
             }
         }
@@ -980,7 +990,8 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
     const int32_t* d_wl_tail = whole ? db->d_identity + n32p : d_wl16;
     const int32_t* d_wl_bulk = whole ? db->d_identity + tail_end : d_wl16 + (same_plan ? 0 : ntail);
     if (same_plan) d_wl_bulk = d_wl_tail;
-    if (local && n16 && ws->ovf.reserve((size_t)(2 * n16))) return PYOPAL_CUDA_ERR_NOMEM;
+    const int64_t n16x = n16 + (packed_giants ? ng : 0);   // pairs scored at 16 bit: bulk, mid and packed giants
+    if (local && n16x && ws->ovf.reserve((size_t)(2 * n16x))) return PYOPAL_CUDA_ERR_NOMEM;
     if (bulk.npass > 1 || tail.npass > 1) {
         if (ws->bndH.reserve((size_t)db->ncols + 16) || ws->bndF.reserve((size_t)db->ncols + 16)) return PYOPAL_CUDA_ERR_NOMEM;
         if (!endm && (n32 > 0 || local))
@@ -998,7 +1009,7 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
     P.out = d_out; P.out_start = start; P.out_end = end;
     if (endm) { P.out_q = endp->d_endq; P.out_t = endp->d_endt; }
     P.ovf_list = ws->ovf.p; P.ovf_count = d_counts + 2;
-    ws->d_ovf_count = (local && n16 > 0) ? d_counts + 2 : nullptr;
+    ws->d_ovf_count = (local && n16x > 0) ? d_counts + 2 : nullptr;
     P.bndH = ws->bndH.p; P.bndF = ws->bndF.p;
     if (endm) { endp->d_ovf = ws->ovf.p; endp->d_ovf_count = d_counts + 2; endp->packed = n16 > 0; }
 
@@ -1053,7 +1064,7 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
         dbg("tgiants");
     }
     if (ng > 0) {
-        search_kernel_t kgiant = get_giant_kernel(gK, local);
+        search_kernel_t kgiant = packed_giants ? get_giant_kernel_packed(gK, rung.tdadd) : get_giant_kernel(gK, local);
         if (!kgiant) return fail(PYOPAL_CUDA_ERR_INTERNAL, "no giant kernel for this tile");
         KParams Q = P;
         // a few teams per CTA keep the column chains short; more CTAs than that would only idle SMs
@@ -1062,6 +1073,7 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
         Q.krows = gK; Q.kstride = (gK == 4) ? 4 : gK + 4;
         Q.worklist = d_wl32 + n32; Q.nwork = d_counts + 8; Q.counter = d_counts + 9;
         Q.neg = -(1 << 29);
+        if (packed_giants) { Q.neg = rung.neg16; Q.bias = rung.bias16; }
         // ask for the whole SM's shared memory: no throughput CTA may share the SM with the giants (giant.cu)
         const size_t gsmem_all = std::max<size_t>(gsmem, (size_t)smem_optin - 1024);
         CU(cudaFuncSetAttribute(kgiant, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsmem_all));
@@ -1143,22 +1155,177 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
     if (side_work) CU(cudaStreamWaitEvent(st, ws->ev_join, 0));
 
     // ---- rescue: 32-bit rescore of what overflowed (list and size live on the device)
-    if (local && n16 > 0 && !endm) {
+    if (local && n16x > 0 && !endm) {
         KParams R = P;
         apply_plan(R, tail);
         R.worklist = ws->ovf.p; R.nwork = d_counts + 2; R.counter = d_counts + 6;
         R.neg = -(1 << 29);
         R.bndH = ws->bnd32H.p; R.bndF = ws->bnd32F.p;
         CU(cudaEventRecord(ws->kev[4], st));
-        int rc = launch_search(db, ws, k32, R, tail.smem, 32, std::min<int64_t>(2 * n16, (int64_t)db->sm_count * 4), st);
+        int rc = launch_search(db, ws, k32, R, tail.smem, 32, std::min<int64_t>(2 * n16x, (int64_t)db->sm_count * 4), st);
         if (rc) return rc;
         CU(cudaEventRecord(ws->kev[5], st));
         ws->kev_valid[2] = true;
         dbg("rescue");
     }
-    ws->stats[1] = n16 * 2; ws->stats[2] = n32 + ng + nt;
+    ws->stats[1] = n16 * 2; ws->stats[2] = n32 + nt + (packed_giants ? 2 * ng : ng);   // targets on the 32-bit rung / the giant kernels
     ws->stats[5] = bulk.G; ws->stats[6] = bulk.K; ws->stats[7] = bulk.npass; ws->stats[11] = bulk.psmem ? 1 : 0;
     return apply_fixes();
+}
+
+// Two Smith-Waterman score searches of the WHOLE database in one pass of dual_kernel (dual.cuh): the two queries
+// share every target column, so their folded scores sit pre-packed in one profile word and a cell pair costs 4.5
+// ALU-pipe instructions instead of 5.5.  Restricted to the case a batch over a large database is in: no target long
+// enough to need the giant kernels under the tile chosen (the whole search is long compared with the longest
+// pair), both queries short enough for the 32-bit profile to fit shared memory.  Returns DUAL_NOT_ELIGIBLE when the
+// pair of queries has to be searched one by one instead (nothing has been enqueued then).
+int pyopal::enqueue_dual_search(pyopal_cuda_db* db, Workspace* ws, const unsigned char* qa, int La, const unsigned char* qb,
+                                int Lb, int go, int ge, const int* M, int A, int32_t* d_out_a, int32_t* d_out_b,
+                                cudaStream_t st) {
+    const Tuning& tune = db->tune;
+    if (tune.no_dual || La <= 0 || Lb <= 0 || db->npairs == 0 || ge > go) return DUAL_NOT_ELIGIBLE;
+    if (tune.has_tgiant || tune.force_stream) return DUAL_NOT_ELIGIBLE;   // a test asked for another kernel
+    const int Lp = std::max(La, Lb);
+    const size_t SMEM_LIMIT = (size_t)200 * 1024;
+    // the tile, planned without giants: what remains above L_even stretches the cost, and more than a little of it
+    // means this database is too small for the restricted launch plan
+    Plan pl = make_plan(Lp, A, db, SMEM_LIMIT, nullptr, false, nullptr);
+    {
+        const double solo = tune.solo > 0 ? tune.solo : (pl.G == 4 ? 448.0 : 560.0);
+        const double l_even = (double)db->ncols * pl.G / (solo * db->sm_count);
+        if ((double)db->h_pair_len[0] > 0.6 * l_even && !tune.force_dual) return DUAL_NOT_ELIGIBLE;
+    }
+    const int T = pl.G * pl.K;
+    const int npass = (Lp + T - 1) / T;
+    Rung rung = make_rung(M, A, go, ge, MODE_SW, npass * T);
+    if (!rung.ok16) return DUAL_NOT_ELIGIBLE;
+    // Profile of 32-bit words, read with LDS.128: the hardware serves a quarter warp (8 lanes x 16 bytes) per phase,
+    // conflict-free when the eight 16-byte units fall into the eight different bank groups.  A lane's chunk is K words
+    // padded to an ODD number of units, so the lanes p = 0..7 of a group sit in eight different groups; every letter
+    // row starts at a multiple of 128 bytes, so the letter (different in every lane) does not move them.  With G = 4 a
+    // quarter warp holds two groups, always in the same pass: half a row of skew per letter (64 bytes) separates them
+    // whenever their letters differ in parity.
+    const int kstride = ((pl.K / 4) % 2 == 1) ? pl.K : pl.K + 4;
+    int pitch = (npass * pl.G * kstride + 31) / 32 * 32;
+    if (pl.G == 4) pitch += 16;
+    const size_t smem = (size_t)(A + 1) * (size_t)pitch * sizeof(uint32_t);
+    if (smem > SMEM_LIMIT) return DUAL_NOT_ELIGIBLE;
+    search_kernel_t kd = get_dual_kernel(pl.K, rung.tdadd);
+    if (!kd) return DUAL_NOT_ELIGIBLE;
+    Plan tail_a = make_tail_plan(La, A, SMEM_LIMIT), tail_b = make_tail_plan(Lb, A, SMEM_LIMIT);
+    if (!tail_a.psmem || !tail_b.psmem) return DUAL_NOT_ELIGIBLE;
+    {
+        int smax = INT_MIN, smin = INT_MAX;
+        for (int i = 0; i < A * A; i++) { smax = std::max(smax, M[i]); smin = std::min(smin, M[i]); }
+        const int64_t mag = std::max<int64_t>({(int64_t)go, (int64_t)ge, 1, std::llabs((long long)smax), std::llabs((long long)smin)});
+        if (mag * ((int64_t)std::max(tail_a.npass * tail_a.G * tail_a.K, tail_b.npass * tail_b.G * tail_b.K) + db->h_pair_len[0] + 8) >= (1LL << 29))
+            return DUAL_NOT_ELIGIBLE;   // the single-query path reports OPAL_ERR_OVERFLOW
+    }
+
+    for (int i = 0; i < 12; i++) ws->stats[i] = 0;
+    ws->kev_valid[0] = ws->kev_valid[1] = ws->kev_valid[2] = false;
+    ws->d_ovf_count = nullptr;
+    if (ws->used) CU(cudaStreamWaitEvent(st, ws->ev_free, 0));
+    ws->used = true;
+    struct Mark {
+        Workspace* w; cudaStream_t s;
+        ~Mark() { cudaEventRecord(w->ev_free, s); }
+    } mark{ws, st};
+
+    // zero-length targets score 0 against either query
+    std::vector<int32_t> fixes;
+    for (int32_t z : db->h_zero_idx) { fixes.push_back(z); fixes.push_back(0); }
+
+    // ---- parameter block: counters, matrix, fix-ups, the two queries ----------------------------------------
+    const size_t off_fix = PAR_LISTS;
+    const size_t off_qa = off_fix + ((fixes.size() * 4 + 15) & ~(size_t)15);
+    const size_t off_qb = off_qa + (((size_t)La + 15) & ~(size_t)15) + 16;
+    const size_t par_bytes = off_qb + (((size_t)Lb + 15) & ~(size_t)15) + 16;
+    const int slot = ws->par_next;
+    ws->par_next = (slot + 1) % Workspace::NPARAM;
+    if (ws->par_used[slot]) CU(cudaEventSynchronize(ws->par_done[slot]));
+    if (ws->h_par[slot].reserve(par_bytes) || ws->d_par.reserve(par_bytes)) return PYOPAL_CUDA_ERR_NOMEM;
+    unsigned char* hp = ws->h_par[slot].p;
+    unsigned char* dp = ws->d_par.p;
+    const int64_t ntargets = 2 * db->npairs;
+    {
+        int32_t* counts = reinterpret_cast<int32_t*>(hp + PAR_COUNTS);
+        memset(counts, 0, 64);
+        counts[0] = (int32_t)ntargets;   // [4] task counter; [2] / [12] overflow counts of A / B; [6] / [13] rescue counters
+        memcpy(hp + PAR_MATRIX, M, (size_t)A * A * sizeof(int32_t));
+        if (!fixes.empty()) memcpy(hp + off_fix, fixes.data(), fixes.size() * 4);
+        memcpy(hp + off_qa, qa, (size_t)La);
+        memcpy(hp + off_qb, qb, (size_t)Lb);
+    }
+    const size_t n_ovf = (size_t)ntargets;
+    if (ws->ovf.reserve(n_ovf) || ws->ovf2.reserve(n_ovf)) return PYOPAL_CUDA_ERR_NOMEM;
+    if (ws->bnd32H.reserve((size_t)db->ncols * 2 + 16) || ws->bnd32F.reserve((size_t)db->ncols * 2 + 16))
+        return PYOPAL_CUDA_ERR_NOMEM;
+    CU(cudaMemcpyAsync(dp, hp, par_bytes, cudaMemcpyHostToDevice, st));
+    CU(cudaEventRecord(ws->par_done[slot], st));
+    ws->par_used[slot] = true;
+    int32_t* d_counts = reinterpret_cast<int32_t*>(dp + PAR_COUNTS);
+
+    KParams P;
+    memset(&P, 0, sizeof(P));
+    P.stream = db->d_stream; P.pair_off = db->d_pair_off; P.pair_len = db->d_pair_len; P.pair_idx = db->d_pair_idx;
+    P.matrix = reinterpret_cast<const int32_t*>(dp + PAR_MATRIX);
+    P.A = A; P.go = go; P.ge = ge; P.mode = MODE_SW;
+    P.pad_score = rung.pad_score; P.ovf_thresh = rung.ovf_thresh;
+    P.one = 1u;
+    P.out_start = 0; P.out_end = db->n;
+
+    // ---- the dual launch ---------------------------------------------------------------------------------------
+    {
+        KParams Q = P;
+        Q.query = dp + off_qa; Q.Lq = La; Q.padtop = npass * T - La;
+        Q.query2 = dp + off_qb; Q.Lq2 = Lb; Q.padtop2 = npass * T - Lb;
+        Q.G = pl.G; Q.logG = pl.logG; Q.npass = npass; Q.pitch = pitch; Q.krows = pl.K; Q.kstride = kstride;
+        Q.neg = rung.neg16; Q.bias = rung.bias16;
+        Q.first_pair = 0;
+        Q.nwork = d_counts + 0; Q.counter = d_counts + 4;
+        Q.out = d_out_a; Q.out2 = d_out_b;
+        Q.ovf_list = ws->ovf.p; Q.ovf_count = d_counts + 2;
+        Q.ovf_list2 = ws->ovf2.p; Q.ovf_count2 = d_counts + 12;
+        Q.bndH = ws->bnd32H.p; Q.bndF = ws->bnd32F.p;
+        const int gpw = 32 >> pl.logG;
+        if (tune.debug)
+            fprintf(stderr, "[pyopal_cuda] Lq=%d+%d score (dual) bulk: G=%d K=%d npass=%d targets=%lld threads=512 smem=%zu\n",
+                    La, Lb, pl.G, pl.K, npass, (long long)ntargets, smem);
+        CU(cudaEventRecord(ws->kev[2], st));
+        int rc = launch_search(db, ws, kd, Q, smem, 512, (ntargets + gpw - 1) / gpw, st);
+        if (rc) return rc;
+        CU(cudaEventRecord(ws->kev[3], st));
+        ws->kev_valid[1] = true;
+    }
+    // ---- rescue of either query's 16-bit overflows at 32 bit (lists and sizes live on the device) --------------
+    struct Side { const Plan* tail; size_t off_q; int Lq; int32_t* out; int32_t* list; int count, counter; };
+    const Side sides[2] = {{&tail_a, off_qa, La, d_out_a, ws->ovf.p, 2, 6}, {&tail_b, off_qb, Lb, d_out_b, ws->ovf2.p, 12, 13}};
+    for (const Side& sd : sides) {
+        search_kernel_t k32 = pick_kernel(sd.tail->K, 32, true, true);
+        if (!k32) return fail(PYOPAL_CUDA_ERR_INTERNAL, "no 32-bit kernel for this tile");
+        KParams R = P;
+        apply_plan(R, *sd.tail);
+        R.query = dp + sd.off_q; R.Lq = sd.Lq;
+        R.worklist = sd.list; R.nwork = d_counts + sd.count; R.counter = d_counts + sd.counter;
+        R.neg = -(1 << 29); R.bias = 0;
+        R.out = sd.out;
+        R.bndH = ws->bnd32H.p; R.bndF = ws->bnd32F.p;
+        int rc = launch_search(db, ws, k32, R, sd.tail->smem, 32, std::min<int64_t>(ntargets, (int64_t)db->sm_count * 4), st);
+        if (rc) return rc;
+    }
+    if (!fixes.empty()) {
+        const int nfix = (int)(fixes.size() / 2);
+        for (int32_t* out : {d_out_a, d_out_b}) {
+            scatter_fixes_kernel<<<(nfix + 255) / 256, 256, 0, st>>>(reinterpret_cast<const int32_t*>(dp + off_fix), nfix, out);
+            CU(cudaGetLastError());
+        }
+        ws->stats[0] += 2;
+    }
+    ws->d_ovf_count = d_counts + 2;
+    ws->stats[1] = ntargets * 2;
+    ws->stats[5] = pl.G; ws->stats[6] = pl.K; ws->stats[7] = npass; ws->stats[11] = 2;   // 2: profile in shared memory, two queries per pass
+    return 0;
 }
 
 int pyopal::enqueue_score_search(pyopal_cuda_db* db, Workspace* ws, const unsigned char* query, int Lq, int go, int ge,
@@ -1258,6 +1425,22 @@ extern "C" int opalSearchDatabaseCharSW(char query[], int queryLength, char** db
 // already queued behind those of query i (its persistent CTAs take over the SMs as the previous search's drain),
 // score rows are copied out on the workspace's own stream, and the host only waits once, at the end.  With
 // `k` > 0 only the k best hits of every query leave the device (topk.cu).
+// Queries of a batch in the order they are searched: by length, neighbours paired.  A pair of Smith-Waterman
+// queries goes down as ONE dual search when the database allows it (enqueue_dual_search), else one after the other.
+void pyopal::plan_batch_units(const pyopal_cuda_db* db, const int32_t* q_lengths, int nq, int mode,
+                              std::vector<std::pair<int, int>>& units) {
+    units.clear();
+    std::vector<int> order((size_t)nq);
+    std::iota(order.begin(), order.end(), 0);
+    const bool pairing = mode == MODE_SW && !db->tune.no_dual && nq > 1;
+    if (pairing) std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return q_lengths[a] > q_lengths[b]; });
+    for (int k = 0; k < nq; k += pairing ? 2 : 1) {
+        const int second = (pairing && k + 1 < nq && q_lengths[order[(size_t)k + 1]] > 0) ? order[(size_t)k + 1] : -1;
+        units.emplace_back(order[(size_t)k], second);
+        if (pairing && second < 0 && k + 1 < nq) units.emplace_back(order[(size_t)k + 1], -1);
+    }
+}
+
 static int search_batch_impl(pyopal_cuda_db* db, const unsigned char* queries, const int64_t* q_offsets,
                              const int32_t* q_lengths, int nq, int go, int ge, const int* M, int A, int mode,
                              int32_t* scores, int k, int32_t* top_scores, int32_t* top_idx) {
@@ -1277,59 +1460,86 @@ static int search_batch_impl(pyopal_cuda_db* db, const unsigned char* queries, c
     const int kk = (int)std::min<int64_t>(k, n);
     std::vector<int32_t> tv, ti;
     if (kk > 0) { tv.resize((size_t)nq * kk); ti.resize((size_t)nq * kk); }
-    // two sets of result buffers alternate between consecutive queries whatever the number of lanes
+    for (int i = 0; i < nq; i++) {
+        int64_t s0 = 0, e0 = n;
+        int rc0 = check_search_args(db, queries + q_offsets[i], q_lengths[i], go, ge, M, A, mode, &s0, &e0);
+        if (rc0) return rc0;
+    }
+    std::vector<std::pair<int, int>> units;
+    plan_batch_units(db, q_lengths, nq, mode, units);
+    // two sets of result buffers alternate between consecutive UNITS (one or two queries: two rows per set)
+    // whatever the number of lanes
     DevBuf<int32_t>* rowb[2] = {&wsv[0]->out, NB > 1 ? &wsv[1]->out : &wsv[0]->out2};
     DevBuf<int32_t>* tvb[2] = {&wsv[0]->tk_vals, NB > 1 ? &wsv[1]->tk_vals : &wsv[0]->tk_vals2};
     DevBuf<int32_t>* tib[2] = {&wsv[0]->tk_idx, NB > 1 ? &wsv[1]->tk_idx : &wsv[0]->tk_idx2};
     for (int b = 0; b < 2; b++) {
-        if (rowb[b]->reserve((size_t)n)) return PYOPAL_CUDA_ERR_NOMEM;
-        if (kk > 0 && (wsv[b]->tk_ws.reserve(topk_workspace_words()) || tvb[b]->reserve((size_t)kk) || tib[b]->reserve((size_t)kk)))
+        if (rowb[b]->reserve((size_t)(2 * n))) return PYOPAL_CUDA_ERR_NOMEM;
+        if (kk > 0 && (wsv[b]->tk_ws.reserve(topk_workspace_words()) || tvb[b]->reserve((size_t)(2 * kk)) || tib[b]->reserve((size_t)(2 * kk))))
             return PYOPAL_CUDA_ERR_NOMEM;
     }
     int rc = 0;
     int64_t launches = 0;
-    // results of query i are copied out AFTER query i + 1 has been enqueued: a copy into pageable host memory
+    // results of unit u are copied out AFTER unit u + 1 has been enqueued: a copy into pageable host memory
     // blocks the host until the search before it is done, and by then the next one is already queued on the device
-    auto copy_out = [&](int i) -> int {
-        Workspace* ws = wsv[i % 2];
-        const int b = i % 2;
-        if (kk > 0) {
-            CU(cudaMemcpyAsync(tv.data() + (size_t)i * kk, tvb[b]->p, (size_t)kk * 4, cudaMemcpyDeviceToHost, ws->stream));
-            CU(cudaMemcpyAsync(ti.data() + (size_t)i * kk, tib[b]->p, (size_t)kk * 4, cudaMemcpyDeviceToHost, ws->stream));
-        } else if (scores) {
-            CU(cudaMemcpyAsync(scores + (size_t)i * (size_t)n, rowb[b]->p, (size_t)n * sizeof(int32_t),
-                               cudaMemcpyDeviceToHost, ws->stream));
+    auto copy_out = [&](int u) -> int {
+        Workspace* ws = wsv[u % 2];
+        const int b = u % 2;
+        const int qi[2] = {units[(size_t)u].first, units[(size_t)u].second};
+        for (int s = 0; s < 2; s++) {
+            if (qi[s] < 0) continue;
+            if (kk > 0) {
+                CU(cudaMemcpyAsync(tv.data() + (size_t)qi[s] * kk, tvb[b]->p + (size_t)s * kk, (size_t)kk * 4, cudaMemcpyDeviceToHost, ws->stream));
+                CU(cudaMemcpyAsync(ti.data() + (size_t)qi[s] * kk, tib[b]->p + (size_t)s * kk, (size_t)kk * 4, cudaMemcpyDeviceToHost, ws->stream));
+            } else if (scores) {
+                CU(cudaMemcpyAsync(scores + (size_t)qi[s] * (size_t)n, rowb[b]->p + (size_t)s * (size_t)n, (size_t)n * sizeof(int32_t),
+                                   cudaMemcpyDeviceToHost, ws->stream));
+            }
         }
         CU(cudaEventRecord(ws->ev_free, ws->stream));
         return 0;
     };
-    for (int i = 0; i < nq && rc == 0; i++) {
-        Workspace* ws = wsv[i % 2];
-        const int b = i % 2;
-        int64_t s = 0, e = n;
-        const unsigned char* q = queries + q_offsets[i];
-        rc = check_search_args(db, q, q_lengths[i], go, ge, M, A, mode, &s, &e);
-        if (rc) break;
+    const int nu = (int)units.size();
+    for (int u = 0; u < nu && rc == 0; u++) {
+        Workspace* ws = wsv[u % 2];
+        const int b = u % 2;
+        const int qa = units[(size_t)u].first, qb = units[(size_t)u].second;
+        int32_t* rows[2] = {rowb[b]->p, rowb[b]->p + n};
         // this buffer set is overwritten: its previous copy-out was issued (and, into pageable memory, completed)
         // before this point, on a stream this search is ordered after
-        rc = enqueue_score_search(db, ws, q, q_lengths[i], go, ge, M, A, mode, 0, n, rowb[b]->p, ws->stream);
-        if (rc) break;
-        launches += ws->stats[0];
-        if (kk > 0) {
-            rc = topk_device(rowb[b]->p, n, kk, tvb[b]->p, tib[b]->p, wsv[b]->tk_ws.p, db->sm_count, ws->stream);
-            if (rc) break;
-            launches += 9;
+        bool done = false;
+        if (qb >= 0) {
+            rc = enqueue_dual_search(db, ws, queries + q_offsets[qa], q_lengths[qa], queries + q_offsets[qb], q_lengths[qb],
+                                     go, ge, M, A, rows[0], rows[1], ws->stream);
+            if (rc == 0) { done = true; launches += ws->stats[0]; }
+            else if (rc != DUAL_NOT_ELIGIBLE) break;
+            rc = 0;
         }
-        if (i > 0) rc = copy_out(i - 1);
+        if (!done) {
+            const int qs[2] = {qa, qb};
+            for (int s = 0; s < 2 && rc == 0; s++) {
+                if (qs[s] < 0) continue;
+                rc = enqueue_score_search(db, ws, queries + q_offsets[qs[s]], q_lengths[qs[s]], go, ge, M, A, mode, 0, n, rows[s], ws->stream);
+                launches += ws->stats[0];
+            }
+            if (rc) break;
+        }
+        if (kk > 0) {
+            for (int s = 0; s < 2 && rc == 0; s++) {
+                if ((s == 0 ? qa : qb) < 0) continue;
+                rc = topk_device(rows[s], n, kk, tvb[b]->p + (size_t)s * kk, tib[b]->p + (size_t)s * kk, wsv[b]->tk_ws.p, db->sm_count, ws->stream);
+                launches += 9;
+            }
+            if (rc) break;
+        }
+        if (u > 0) rc = copy_out(u - 1);
     }
-    if (rc == 0) rc = copy_out(nq - 1);
+    if (rc == 0 && nu > 0) rc = copy_out(nu - 1);
     for (int b = 0; b < 2; b++) {
         cudaError_t e = cudaStreamSynchronize(wsv[b]->stream);
         if (e != cudaSuccess && rc == 0) rc = fail(PYOPAL_CUDA_ERR_CUDA, std::string("batch: ") + cudaGetErrorString(e));
     }
     wsv[0]->stats[0] = launches;
     wsv[1]->stats[0] = launches;
-    (void)NB;
     if (rc) return rc;
     if (kk > 0) {
         // order the k hits of every query: score descending, ties by ascending database index

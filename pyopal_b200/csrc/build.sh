@@ -6,8 +6,8 @@ NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -I. -I../../include"
 mkdir -p build
 pids=()
-for f in kernels_w16_l1 kernels_w16_l0 kernels_w16_l1_end kernels_w16_l0_end kernels_stream_l1 kernels_stream_l0 kernels_w32_l1 kernels_w32_l0 giant tgiant topk api pairdp multi microbench; do
-  if [ ! -f build/$f.o ] || [ $f.cu -nt build/$f.o ] || [ kernels.cuh -nt build/$f.o ] || [ stream.cuh -nt build/$f.o ] || [ store.h -nt build/$f.o ] || [ ../../include/pyopal_cuda.h -nt build/$f.o ]; then
+for f in kernels_w16_l1 kernels_w16_l0 kernels_w16_l1_end kernels_w16_l0_end kernels_dual kernels_stream_l1 kernels_stream_l0 kernels_w32_l1 kernels_w32_l0 giant tgiant topk api pairdp multi microbench; do
+  if [ ! -f build/$f.o ] || [ $f.cu -nt build/$f.o ] || [ kernels.cuh -nt build/$f.o ] || [ stream.cuh -nt build/$f.o ] || [ dual.cuh -nt build/$f.o ] || [ store.h -nt build/$f.o ] || [ ../../include/pyopal_cuda.h -nt build/$f.o ]; then
     $NVCC $FLAGS -c $f.cu -o build/$f.o &
     pids+=($!)
   fi

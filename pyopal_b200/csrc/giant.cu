@@ -23,9 +23,14 @@
 //     a saturated ALU pipe pays a queueing delay on every dependent
 //     instruction.  floor(16 / warps per team) teams share the 512-thread CTA
 //     and the profile; surplus warps exit at once.
-// 32-bit values, one target per team: these are a fraction of a percent of the
-// cells, only their latency matters.  Same cell update (column_update) and
-// profile as search_kernel.
+// W = 32: one target per team, 32-bit values (every algorithm, any score).
+// W = 16 (round 2, Smith-Waterman): the two targets of a PAIR per team in one
+// u16x2 word, exactly the packed arithmetic of search_kernel -- a giant holds a
+// whole SM for milliseconds, so walking two of them for the price of one halves
+// the SM time the longest targets take from the bulk kernel (6 % of a 1/8 shard's
+// SM time for the 5000-aa query).  A pair whose packed score overflows goes to
+// the same rescue list as the bulk kernel's.  Same cell update (column_update)
+// and profile as search_kernel.
 #include "kernels.cuh"
 
 #include <climits>
@@ -60,9 +65,12 @@ __device__ __forceinline__ void team_sync(int team, int nw) {
 // Each lane advances C columns per step (a block): the per-step overhead (shuffles, predicates,
 // loop) is paid once per C columns and the C x K cells of a block give the single resident warp
 // of a scheduler independent instructions to issue back to back.
-template <int K, int C, bool LOCAL>
+template <int K, int C, bool LOCAL, int W = 32, bool TDADD = true>
 __global__ void __launch_bounds__(512, 1) giant_kernel(const __grid_constant__ KParams P) {
     static_assert(C == 2 || C == 4, "block of 2 or 4 columns");
+    static_assert(W == 32 || LOCAL, "packed giants: Smith-Waterman only");
+    typedef Val<W> V;
+    typedef typename V::T val_t;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int nw = P.G, teams = P.npass;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -93,9 +101,10 @@ __global__ void __launch_bounds__(512, 1) giant_kernel(const __grid_constant__ K
     const unsigned FULL = 0xffffffffu;
     const bool top_free = (P.mode != MODE_NW);
     const bool left_free = (P.mode == MODE_OV || P.mode == MODE_SW);
-    CellConsts<32> CC;
+    CellConsts<W> CC;
     CC.init(P);
-    const int NEG = CC.NEG;
+    const val_t NEG = CC.NEG;
+    const int B = P.bias;   // W = 16: values are stored biased; 0 at 32 bit
     const int ttid = w * 32 + lane;
     const int rowbase = ttid * K;
     const bool last_lane = (ttid == nw * 32 - 1);  // holds the last query row
@@ -109,42 +118,44 @@ __global__ void __launch_bounds__(512, 1) giant_kernel(const __grid_constant__ K
         team_sync(team, nw);
         const int task = *task_s;
         if (task >= nwork) break;
+        // W = 32: (pair << 1) | half, one target; W = 16: the pair, both targets (len_a >= len_b columns)
         const int entry = P.worklist[task];
-        const int pair = entry >> 1, half = entry & 1;
+        const int pair = (W == 16) ? entry : (entry >> 1), half = (W == 16) ? 0 : (entry & 1);
         const int ncol = P.pair_len[2 * pair + half];
         // blocks of C columns; the stream is padded with the padding letter to a multiple of 8 columns
         const codes_t* blocks = reinterpret_cast<const codes_t*>(P.stream + P.pair_off[pair]);
         const int nblk = (ncol + C - 1) / C;
         const int nsteps = nblk + 31;
 
-        int Gl[K], E[K];
+        val_t Gl[K], E[K];
 #pragma unroll
         for (int r = 0; r < K; ++r) {
             int qi = rowbase + r - P.padtop;
             int hl = (left_free || qi < 0) ? 0 : -(P.go + qi * P.ge);
-            Gl[r] = hl - P.go;
+            Gl[r] = V::splat(hl - P.go + B);
             E[r] = NEG;
         }
-        int upGprev;
+        val_t upGprev;
         {
             int qi = rowbase - 1 - P.padtop;
             int hl = (left_free || qi < 0) ? 0 : -(P.go + qi * P.ge);
-            upGprev = hl - P.go;
+            upGprev = V::splat(hl - P.go + B);
         }
-        int Gout[C], Fout[C];
+        val_t Gout[C], Fout[C];
 #pragma unroll
-        for (int c = 0; c < C; ++c) { Gout[c] = 0; Fout[c] = NEG; }
-        int best = 0, res = INT_MIN;
+        for (int c = 0; c < C; ++c) { Gout[c] = CC.FLOOR; Fout[c] = NEG; }
+        val_t best = CC.FLOOR;   // SW: running maximum (biased at 16 bit; bias 0 at 32 bit)
+        int res = INT_MIN;
         int cons_seen = 0;
-        int nxG[C], nxF[C];       // lane 0 of a warp > 0: the block the next step needs, prefetched from the ring
+        val_t nxG[C], nxF[C];     // lane 0 of a warp > 0: the block the next step needs, prefetched from the ring
         bool nx_ready = false;
 #pragma unroll
-        for (int c = 0; c < C; ++c) { nxG[c] = 0; nxF[c] = NEG; }
+        for (int c = 0; c < C; ++c) { nxG[c] = CC.FLOOR; nxF[c] = NEG; }
         codes_t code_nx = codes_t();
         if (lane == 0 && nblk > 0) code_nx = blocks[0];
 
         for (int s = 0; s < nsteps; ++s) {
-            int upG[C], upF[C];
+            val_t upG[C], upF[C];
 #pragma unroll
             for (int c = 0; c < C; ++c) {
                 upG[c] = __shfl_up_sync(FULL, Gout[c], 1);
@@ -158,7 +169,7 @@ __global__ void __launch_bounds__(512, 1) giant_kernel(const __grid_constant__ K
 #pragma unroll
                     for (int c = 0; c < C; ++c) {
                         int ht = top_free ? 0 : -(P.go + (b * C + c) * P.ge);
-                        upG[c] = ht - P.go;
+                        upG[c] = V::splat(ht - P.go + B);
                         upF[c] = NEG;
                     }
                 } else {
@@ -168,7 +179,7 @@ __global__ void __launch_bounds__(512, 1) giant_kernel(const __grid_constant__ K
 #pragma unroll
                         for (int c = 0; c < C; ++c) {
                             const int4 v = lds_slot(slots + c);
-                            nxG[c] = v.x; nxF[c] = v.y;
+                            nxG[c] = (val_t)v.x; nxF[c] = (val_t)v.y;
                             nx_ready = nx_ready && (v.z == b + 1);
                         }
                     }
@@ -183,7 +194,7 @@ __global__ void __launch_bounds__(512, 1) giant_kernel(const __grid_constant__ K
 #pragma unroll
                         for (int c = 0; c < C; ++c) {
                             const int4 v = lds_slot(nslots + c);
-                            nxG[c] = v.x; nxF[c] = v.y;
+                            nxG[c] = (val_t)v.x; nxF[c] = (val_t)v.y;
                             ok = ok && (v.z == b + 2);
                         }
                         nx_ready = ok;
@@ -201,12 +212,13 @@ __global__ void __launch_bounds__(512, 1) giant_kernel(const __grid_constant__ K
 #pragma unroll
                 for (int c = 0; c < C; ++c) {
                     const unsigned t0 = (cw[c >> 1] >> (16 * (c & 1) + 8 * half)) & 0xffu;
-                    int F = upF[c], Gup = upG[c];
-                    column_update<K, 32, LOCAL, true, false, true>(P, sp, t0, 0u, ttid * P.kstride, CC, E, Gl, upGprev, F, Gup, best);
+                    const unsigned t1 = (W == 16) ? ((cw[c >> 1] >> (16 * (c & 1) + 8)) & 0xffu) : 0u;
+                    val_t F = upF[c], Gup = upG[c];
+                    column_update<K, W, LOCAL, true, false, TDADD>(P, sp, t0, t1, ttid * P.kstride, CC, E, Gl, upGprev, F, Gup, best);
                     Gout[c] = Gup;
                     Fout[c] = F;
                     upGprev = upG[c];
-                    if (!LOCAL) {
+                    if constexpr (!LOCAL) {
                         const int j = b * C + c;  // columns >= ncol of the last block are padding
                         if (last_lane) {
                             const int h = Gup + P.go;  // last query row
@@ -225,20 +237,46 @@ __global__ void __launch_bounds__(512, 1) giant_kernel(const __grid_constant__ K
                     while (b - cons_seen >= RING) cons_seen = cons[w + 1];
                     int4* slots = ring + (w * RING + (b & (RING - 1))) * C;
 #pragma unroll
-                    for (int c = 0; c < C; ++c) sts_slot(slots + c, Gout[c], Fout[c], b + 1);
+                    for (int c = 0; c < C; ++c) sts_slot(slots + c, (int)Gout[c], (int)Fout[c], b + 1);
                 }
             }
         }
         // reduce over the team
-        int v = LOCAL ? best : res;
-        for (int d = 16; d > 0; d >>= 1) v = max(v, __shfl_xor_sync(FULL, v, d));
-        if (lane == 0) red[w] = v;
-        team_sync(team, nw);
-        if (ttid == 0) {
-            int m = red[0];
-            for (int x = 1; x < nw; ++x) m = max(m, red[x]);
-            const int ix = P.pair_idx[2 * pair + half];
-            if (ix >= P.out_start && ix < P.out_end) P.out[ix - P.out_start] = m;
+        if (W == 16) {
+            uint32_t v = (uint32_t)best;
+            for (int d = 16; d > 0; d >>= 1) v = __vmaxu2(v, __shfl_xor_sync(FULL, v, d));
+            if (lane == 0) red[w] = (int)v;
+            team_sync(team, nw);
+            if (ttid == 0) {
+                uint32_t m = (uint32_t)red[0];
+                for (int x = 1; x < nw; ++x) m = __vmaxu2(m, (uint32_t)red[x]);
+                const int r0 = (int)(m & 0xffffu) - B, r1 = (int)(m >> 16) - B;
+                const int ia = P.pair_idx[2 * pair], ib = P.pair_idx[2 * pair + 1];
+                const bool ina = ia >= P.out_start && ia < P.out_end;
+                const bool inb = ib >= P.out_start && ib < P.out_end;
+                // as in search_kernel: an overflowing LOW half carries into the high half, both are rescored then
+                const bool ova = r0 >= P.ovf_thresh;
+                const bool ovb = r1 >= P.ovf_thresh || ova;
+                if (ina) {
+                    if (ova) P.ovf_list[atomicAdd(P.ovf_count, 1)] = pair << 1;
+                    else P.out[ia - P.out_start] = r0;
+                }
+                if (inb) {
+                    if (ovb) P.ovf_list[atomicAdd(P.ovf_count, 1)] = (pair << 1) | 1;
+                    else P.out[ib - P.out_start] = r1;
+                }
+            }
+        } else {
+            int v = LOCAL ? (int)best : res;
+            for (int d = 16; d > 0; d >>= 1) v = max(v, __shfl_xor_sync(FULL, v, d));
+            if (lane == 0) red[w] = v;
+            team_sync(team, nw);
+            if (ttid == 0) {
+                int m = red[0];
+                for (int x = 1; x < nw; ++x) m = max(m, red[x]);
+                const int ix = P.pair_idx[2 * pair + half];
+                if (ix >= P.out_start && ix < P.out_end) P.out[ix - P.out_start] = m;
+            }
         }
     }
 }
@@ -248,6 +286,16 @@ search_kernel_t get_giant_kernel(int K, bool local) {
         case 4: return local ? giant_kernel<4, GIANT_BLOCK, true> : giant_kernel<4, GIANT_BLOCK, false>;
         case 8: return local ? giant_kernel<8, GIANT_BLOCK, true> : giant_kernel<8, GIANT_BLOCK, false>;
         case 16: return local ? giant_kernel<16, GIANT_BLOCK, true> : giant_kernel<16, GIANT_BLOCK, false>;
+        default: return nullptr;
+    }
+}
+
+// Smith-Waterman, the two targets of a pair packed at 16 bit (P.worklist holds pair ids)
+search_kernel_t get_giant_kernel_packed(int K, bool tdadd) {
+    switch (K) {
+        case 4: return tdadd ? giant_kernel<4, GIANT_BLOCK, true, 16, true> : giant_kernel<4, GIANT_BLOCK, true, 16, false>;
+        case 8: return tdadd ? giant_kernel<8, GIANT_BLOCK, true, 16, true> : giant_kernel<8, GIANT_BLOCK, true, 16, false>;
+        case 16: return tdadd ? giant_kernel<16, GIANT_BLOCK, true, 16, true> : giant_kernel<16, GIANT_BLOCK, true, 16, false>;
         default: return nullptr;
     }
 }

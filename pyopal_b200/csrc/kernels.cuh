@@ -78,6 +78,12 @@ struct KParams {
     uint32_t* bndH;
     uint32_t* bndF;
     int first_pair;           // stream_kernel (stream.cuh): task t is pair first_pair + t
+    // dual_kernel (dual.cuh): a second query in the high halves, its padding, results and overflow list
+    const uint8_t* query2;
+    int Lq2, padtop2;
+    int32_t* out2;
+    int32_t* ovf_list2;
+    int32_t* ovf_count2;
 };
 
 // ---------------------------------------------------------------------------
@@ -241,8 +247,10 @@ __device__ __forceinline__ void end_event(const uint32_t (&Gl)[K], uint32_t cm, 
 // penalised top border (re-opening a gap is then cheaper than extending it, so their E path beats the border
 // value); the thread that holds the LAST padding row (register `fixrow`) overwrites its output with the border
 // H[-1][j] - open (`fixG`) and an empty F, which is exactly what the first query row must see.
+// DUAL (dual.cuh): `prof` holds one 32-bit word per (letter, row) with the folded scores of TWO queries already in the
+// two u16 halves; t0 is the residue of the ONE target both are aligned to.  No widening instruction per cell pair.
 template <int K, int W, bool LOCAL, bool PSMEM, bool WIDE, bool TDADD, bool SHORTF_ = (W == 16), bool BFIX = false,
-          bool END = false>
+          bool END = false, bool DUAL = false>
 __device__ __forceinline__ void column_update(const KParams& P, const int8_t* prof, unsigned t0, unsigned t1, int pslot,
                                               const CellConsts<W>& C, typename Val<W>::T (&E)[K],
                                               typename Val<W>::T (&Gl)[K], typename Val<W>::T upGprev,
@@ -269,6 +277,9 @@ __device__ __forceinline__ void column_update(const KParams& P, const int8_t* pr
         int4 sw = make_int4(0, 0, 0, 0);
         if (WIDE) {
             sw = __ldg(reinterpret_cast<const int4*>(P.wprofile + (size_t)t0 * P.pitch + pslot) + c);
+        } else if (DUAL) {
+            // pitch and pslot count 32-bit words here; lane chunks start on 16-byte boundaries
+            sw = *(reinterpret_cast<const int4*>(reinterpret_cast<const uint32_t*>(prof) + t0 * P.pitch + pslot) + c);
         } else if (PSMEM) {
             wa = *reinterpret_cast<const uint32_t*>(pa + 4 * c);
             if (W == 16) wb = *reinterpret_cast<const uint32_t*>(pb + 4 * c);
@@ -280,7 +291,7 @@ __device__ __forceinline__ void column_update(const KParams& P, const int8_t* pr
         for (int u = 3; u >= 0; --u) {
             const int r = 4 * c + u;
             val_t S;
-            if (WIDE) S = (val_t)(u == 0 ? sw.x : u == 1 ? sw.y : u == 2 ? sw.z : sw.w);
+            if (WIDE || DUAL) S = (val_t)(u == 0 ? sw.x : u == 1 ? sw.y : u == 2 ? sw.z : sw.w);
             else if (W == 16) S = (val_t)widen_pair(wa, wb, u);
             else S = (val_t)widen_one(wa, u);
             const val_t Gd = (r == 0) ? upGprev : Gl[r - 1];
@@ -630,8 +641,11 @@ search_kernel_t get_search_kernel_bfix(bool wide);
 // stream.cuh: the 16-bit score kernel as a continuous wavefront (whole-database searches)
 search_kernel_t get_stream_kernel_l1(int K, bool tdadd);
 search_kernel_t get_stream_kernel_l0(int K, bool tdadd);
+// dual.cuh: two queries against one target per u16x2 word (Smith-Waterman, batched searches)
+search_kernel_t get_dual_kernel(int K, bool tdadd);
 // giant.cu: a team of warps per target (KParams.G = warps per team, KParams.npass = teams per CTA), K = 4 or 8
 search_kernel_t get_giant_kernel(int K, bool local);
+search_kernel_t get_giant_kernel_packed(int K, bool tdadd);   // SW, both targets of a pair at 16 bit (KParams.worklist: pair ids)
 size_t giant_smem_bytes(int A, int pitch, int warps_per_team, int teams);
 // tgiant.cu: the longest targets with the TARGET laid over the lanes of a team (KParams.G = warps), K = 16 or 32
 search_kernel_t get_tgiant_kernel(int K, bool local);

@@ -97,12 +97,16 @@ int nccl_load(const char* explicit_path) {
                                   (g_nccl.GetErrorString ? g_nccl.GetErrorString(r_) : "NCCL error")); \
     } while (0)
 
-// database order <- gathered shard order
+// database order <- gathered shard order.  `rows` score rows per rank travel together (a dual search produces two):
+// gathered[(r * rows + s) * n_pad + k] is row s of rank r's slot k; row s lands at out + s * out_stride.
 __global__ void unpermute_kernel(const int32_t* __restrict__ gathered, const int32_t* __restrict__ dest, int64_t total,
-                                 int64_t start, int64_t end, int32_t* __restrict__ out) {
+                                 int64_t n_pad, int rows, int64_t start, int64_t end, int32_t* __restrict__ out,
+                                 int64_t out_stride) {
     for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < total; j += (int64_t)gridDim.x * blockDim.x) {
         const int64_t d = dest[j];
-        if (d >= start && d < end) out[d - start] = gathered[j];
+        if (d < start || d >= end) continue;
+        const int64_t r = j / n_pad, k = j - r * n_pad;
+        for (int s = 0; s < rows; s++) out[s * out_stride + d - start] = gathered[(r * rows + s) * n_pad + k];
     }
 }
 
@@ -143,9 +147,10 @@ struct Lane {
     cudaStream_t gstream = nullptr;              // high priority: gather, un-permute, top-k, copy-out
     cudaEvent_t ev_search = nullptr, ev_gather = nullptr;
     bool gathered_once = false;
-    int32_t* d_local = nullptr;                  // [width * n_pad] this rank's results, shard order
-    int32_t* d_gathered = nullptr;               // [world * width * n_pad]
-    int32_t* d_final = nullptr;                  // [n_all] database order
+    // two score rows per lane: a unit of a batch is one search or a dual search of two queries (api.cu)
+    int32_t* d_local = nullptr;                  // [2 * n_pad] this rank's results, shard order
+    int32_t* d_gathered = nullptr;               // [world * 2 * n_pad]
+    int32_t* d_final = nullptr;                  // [2 * n_all] database order
     DevBuf<int32_t> tk_vals, tk_idx;
     DevBuf<uint32_t> tk_ws;
 };
@@ -243,11 +248,11 @@ int local_setup(pyopal_cuda_mdb* m, Local* l, const int32_t* dest_all) {
         CU(cudaStreamCreateWithPriority(&ln.gstream, cudaStreamNonBlocking, hi_prio));
         CU(cudaEventCreateWithFlags(&ln.ev_search, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&ln.ev_gather, cudaEventDisableTiming));
-        CU(cudaMalloc(&ln.d_local, npad * sizeof(int32_t)));
-        CU(cudaMemset(ln.d_local, 0, npad * sizeof(int32_t)));
+        CU(cudaMalloc(&ln.d_local, 2 * npad * sizeof(int32_t)));
+        CU(cudaMemset(ln.d_local, 0, 2 * npad * sizeof(int32_t)));
         if (!m->identity) {
-            CU(cudaMalloc(&ln.d_gathered, npad * (size_t)m->world * sizeof(int32_t)));
-            CU(cudaMalloc(&ln.d_final, (size_t)std::max<int64_t>(m->n_all, 1) * sizeof(int32_t)));
+            CU(cudaMalloc(&ln.d_gathered, 2 * npad * (size_t)m->world * sizeof(int32_t)));
+            CU(cudaMalloc(&ln.d_final, 2 * (size_t)std::max<int64_t>(m->n_all, 1) * sizeof(int32_t)));
         }
     }
     if (!m->identity) {
@@ -538,72 +543,100 @@ int rank_batch(pyopal_cuda_mdb* m, int L, const BatchArgs& a, bool output, int64
     Local* l = m->local[(size_t)L].get();
     DeviceGuard guard(l->device);
     const int64_t nout = a.end - a.start;
+    const int64_t npad = std::max<int64_t>(m->n_pad, 1);
     // this shard's part of the slice [start, end): mine[] is ascending
     const int64_t lo = std::lower_bound(l->mine.begin(), l->mine.end(), (int32_t)std::min<int64_t>(a.start, INT32_MAX)) - l->mine.begin();
     const int64_t hi = std::lower_bound(l->mine.begin(), l->mine.end(), (int32_t)std::min<int64_t>(a.end, INT32_MAX)) - l->mine.begin();
+    const bool whole_shard = lo == 0 && hi == l->db->n;
     const int kk = (int)std::min<int64_t>(a.k, nout);
     std::vector<int32_t> tv, ti;
     if (kk > 0 && output) { tv.resize((size_t)a.nq * kk); ti.resize((size_t)a.nq * kk); }
-    // Buffer sets alternate between consecutive queries; with one lane (the default) both run on lane 0's streams,
-    // i.e. the searches are stream-ordered back to back, with two lanes each set has its own streams.
+    // Units (one query, or two searched together: api.cu plan_batch_units) alternate between the two buffer sets;
+    // with one lane (the default) both run on lane 0's streams, i.e. the searches are stream-ordered back to back,
+    // with two lanes each set has its own streams.  Every rank derives the same units (the collectives must match).
+    std::vector<std::pair<int, int>> units;
+    plan_batch_units(l->db, a.q_lengths, a.nq, a.mode, units);
     const int nlane = l->db->tune.lanes >= 2 ? NLANE : 1;
-    auto copy_out = [&](int i) -> int {
-        Lane& ln = l->lane[i % NLANE];
-        cudaStream_t gs = l->lane[i % nlane].gstream;
+    auto copy_out = [&](int u) -> int {
+        Lane& ln = l->lane[u % NLANE];
+        cudaStream_t gs = l->lane[u % nlane].gstream;
         if (!output) return 0;
-        const int32_t* src = m->identity ? ln.d_local + lo : ln.d_final;
-        if (kk > 0) {
-            CU(cudaMemcpyAsync(tv.data() + (size_t)i * kk, ln.tk_vals.p, (size_t)kk * 4, cudaMemcpyDeviceToHost, gs));
-            CU(cudaMemcpyAsync(ti.data() + (size_t)i * kk, ln.tk_idx.p, (size_t)kk * 4, cudaMemcpyDeviceToHost, gs));
-        } else if (a.scores) {
-            CU(cudaMemcpyAsync(a.scores + (size_t)i * (size_t)nout, src, (size_t)nout * sizeof(int32_t), cudaMemcpyDeviceToHost, gs));
+        const int qi[2] = {units[(size_t)u].first, units[(size_t)u].second};
+        for (int s = 0; s < 2; s++) {
+            if (qi[s] < 0) continue;
+            const int32_t* src = m->identity ? ln.d_local + (size_t)s * npad + lo : ln.d_final + (size_t)s * (size_t)m->n_all;
+            if (kk > 0) {
+                CU(cudaMemcpyAsync(tv.data() + (size_t)qi[s] * kk, ln.tk_vals.p + (size_t)s * kk, (size_t)kk * 4, cudaMemcpyDeviceToHost, gs));
+                CU(cudaMemcpyAsync(ti.data() + (size_t)qi[s] * kk, ln.tk_idx.p + (size_t)s * kk, (size_t)kk * 4, cudaMemcpyDeviceToHost, gs));
+            } else if (a.scores) {
+                CU(cudaMemcpyAsync(a.scores + (size_t)qi[s] * (size_t)nout, src, (size_t)nout * sizeof(int32_t), cudaMemcpyDeviceToHost, gs));
+            }
         }
         CU(cudaEventRecord(ln.ev_gather, gs));
         return 0;
     };
-    for (int i = 0; i < a.nq; i++) {
-        Lane& ln = l->lane[i % NLANE];                 // buffers of this query
-        Workspace* ws = l->lane[i % nlane].ws;         // streams / workspace it runs on
-        cudaStream_t gs = l->lane[i % nlane].gstream;
-        const unsigned char* q = a.queries + a.q_offsets[i];
+    const int nu = (int)units.size();
+    for (int u = 0; u < nu; u++) {
+        Lane& ln = l->lane[u % NLANE];                 // buffers of this unit
+        Workspace* ws = l->lane[u % nlane].ws;         // streams / workspace it runs on
+        cudaStream_t gs = l->lane[u % nlane].gstream;
+        const int qa = units[(size_t)u].first, qb = units[(size_t)u].second;
+        const int rows = qb >= 0 ? 2 : 1;
         // d_local / d_final of this lane are about to be overwritten: its previous gather and copy-out must be done
         if (ln.gathered_once) CU(cudaStreamWaitEvent(ws->stream, ln.ev_gather, 0));
         if (hi > lo) {
-            int rc = enqueue_score_search(l->db, ws, q, a.q_lengths[i], a.go, a.ge, a.M, a.A, a.mode, lo, hi, ln.d_local + lo, ws->stream);
-            if (rc) return rc;
-            *launches += ws->stats[0];
-            l->db->publish(ws);
+            bool done = false;
+            if (qb >= 0 && whole_shard) {
+                int rc = enqueue_dual_search(l->db, ws, a.queries + a.q_offsets[qa], a.q_lengths[qa], a.queries + a.q_offsets[qb],
+                                             a.q_lengths[qb], a.go, a.ge, a.M, a.A, ln.d_local, ln.d_local + npad, ws->stream);
+                if (rc == 0) { done = true; *launches += ws->stats[0]; l->db->publish(ws); }
+                else if (rc != DUAL_NOT_ELIGIBLE) return rc;
+            }
+            if (!done) {
+                const int qs[2] = {qa, qb};
+                for (int s = 0; s < 2; s++) {
+                    if (qs[s] < 0) continue;
+                    int rc = enqueue_score_search(l->db, ws, a.queries + a.q_offsets[qs[s]], a.q_lengths[qs[s]], a.go, a.ge, a.M, a.A,
+                                                  a.mode, lo, hi, ln.d_local + (size_t)s * npad + lo, ws->stream);
+                    if (rc) return rc;
+                    *launches += ws->stats[0];
+                    l->db->publish(ws);
+                }
+            }
         }
         CU(cudaEventRecord(ln.ev_search, ws->stream));
         CU(cudaStreamWaitEvent(gs, ln.ev_search, 0));
-        const int32_t* final_rows = ln.d_local + lo;
         if (!m->identity) {
+            // rows of one rank are contiguous ([s][n_pad]), so both rows of a dual search travel in ONE all-gather
             if (m->world > 1) {
-                NC(g_nccl.AllGather(ln.d_local, ln.d_gathered, (size_t)m->n_pad, NCCL_INT32, l->comm, gs));
+                NC(g_nccl.AllGather(ln.d_local, ln.d_gathered, (size_t)(rows * npad), NCCL_INT32, l->comm, gs));
             } else {
-                CU(cudaMemcpyAsync(ln.d_gathered, ln.d_local, (size_t)m->n_pad * sizeof(int32_t), cudaMemcpyDeviceToDevice, gs));
+                CU(cudaMemcpyAsync(ln.d_gathered, ln.d_local, (size_t)(rows * npad) * sizeof(int32_t), cudaMemcpyDeviceToDevice, gs));
             }
             if (output) {  // only the rank that hands the result out puts it in database order
-                const int64_t total = m->n_pad * m->world;
+                const int64_t total = npad * m->world;
                 const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>((total + 255) / 256, 148 * 8));
-                unpermute_kernel<<<blocks, 256, 0, gs>>>(ln.d_gathered, l->d_dest, total, a.start, a.end, ln.d_final);
+                unpermute_kernel<<<blocks, 256, 0, gs>>>(ln.d_gathered, l->d_dest, total, npad, rows, a.start, a.end, ln.d_final, m->n_all);
                 CU(cudaGetLastError());
             }
             *launches += (m->world > 1 ? 1 : 0) + (output ? 1 : 0);
-            final_rows = ln.d_final;
         }
         if (kk > 0 && output) {
-            if (ln.tk_ws.reserve(topk_workspace_words()) || ln.tk_vals.reserve((size_t)kk) || ln.tk_idx.reserve((size_t)kk))
+            if (ln.tk_ws.reserve(topk_workspace_words()) || ln.tk_vals.reserve((size_t)(2 * kk)) || ln.tk_idx.reserve((size_t)(2 * kk)))
                 return PYOPAL_CUDA_ERR_NOMEM;
-            int rc = topk_device(final_rows, nout, kk, ln.tk_vals.p, ln.tk_idx.p, ln.tk_ws.p, l->db->sm_count, gs);
-            if (rc) return rc;
-            *launches += 9;
+            for (int s = 0; s < rows; s++) {
+                const int32_t* final_row = m->identity ? ln.d_local + (size_t)s * npad + lo : ln.d_final + (size_t)s * (size_t)m->n_all;
+                int rc = topk_device(final_row, nout, kk, ln.tk_vals.p + (size_t)s * kk, ln.tk_idx.p + (size_t)s * kk, ln.tk_ws.p,
+                                     l->db->sm_count, gs);
+                if (rc) return rc;
+                *launches += 9;
+            }
         }
         CU(cudaEventRecord(ln.ev_gather, gs));
         ln.gathered_once = true;
-        if (i > 0) { int rc = copy_out(i - 1); if (rc) return rc; }
+        if (u > 0) { int rc = copy_out(u - 1); if (rc) return rc; }
     }
-    if (a.nq > 0) { int rc = copy_out(a.nq - 1); if (rc) return rc; }
+    if (nu > 0) { int rc = copy_out(nu - 1); if (rc) return rc; }
     for (Lane& ln : l->lane) CU(cudaStreamSynchronize(ln.gstream));
     if (kk > 0 && output) {
         std::vector<int32_t> order((size_t)kk);

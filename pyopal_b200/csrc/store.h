@@ -16,6 +16,7 @@
 #include <memory>
 #include <mutex>
 #include <string>
+#include <utility>
 #include <vector>
 
 namespace pyopal {
@@ -105,6 +106,9 @@ struct Tuning {
     int plan_logG = 0, plan_K = 0, plan_threads = 0;
     bool no_giant = false, no_tgiant = false, no_tail = false, debug = false, no_end16 = false, no_mid = false;
     bool no_stream = false;   // keep whole-database score searches on search_kernel (one pair per task)
+    bool force_dual = false;    // ... or always, whatever the size of the database (tests)
+    bool no_dual = false;       // batched searches: one query per pass of the score kernel, never two (dual.cuh)
+    bool no_giant16 = false;    // giant.cu at 32 bit, one target per team, also for Smith-Waterman
     bool force_stream = false;  // ... or run them on stream_kernel whatever the tile
     bool has_tgiant = false;
     int tg_warps = 4, tg_K = 32, tg_split = -1;
@@ -136,7 +140,7 @@ struct Workspace {
     int par_next = 0;
     DevBuf<unsigned char> d_par;
     // score search
-    DevBuf<int32_t> ovf, out, out2;   // out2: second row buffer of the stream-ordered batch
+    DevBuf<int32_t> ovf, ovf2, out, out2;   // ovf2: second query of a dual search; out2: second row buffer of the stream-ordered batch
     DevBuf<int8_t> gprofile;
     DevBuf<int32_t> wprofile;
     DevBuf<uint32_t> bndH, bndF, bnd32H, bnd32F;
@@ -232,6 +236,14 @@ int enqueue_score_search(pyopal_cuda_db* db, Workspace* ws, const unsigned char*
 int enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const unsigned char* query, int Lq, int go, int ge,
                             const int* M, int A, int mode, int64_t start, int64_t end, int32_t* d_out, cudaStream_t st,
                             EndPlan* endp);
+
+// api.cu: two SW score searches of the whole database in one pass (dual.cuh); DUAL_NOT_ELIGIBLE = search them one by one
+constexpr int DUAL_NOT_ELIGIBLE = -1;
+int enqueue_dual_search(pyopal_cuda_db* db, Workspace* ws, const unsigned char* qa, int La, const unsigned char* qb, int Lb,
+                        int go, int ge, const int* M, int A, int32_t* d_out_a, int32_t* d_out_b, cudaStream_t st);
+
+// api.cu: the order and pairing in which the queries of a batch are searched: (first, second or -1) per unit
+void plan_batch_units(const pyopal_cuda_db* db, const int32_t* q_lengths, int nq, int mode, std::vector<std::pair<int, int>>& units);
 
 int check_search_args(pyopal_cuda_db* db, const unsigned char* query, int Lq, int go, int ge, const int* M, int A,
                       int mode, int64_t* start, int64_t* end);

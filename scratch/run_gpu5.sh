@@ -1,16 +1,17 @@
 #!/bin/bash
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
-{
-echo "== whole default (U8 residue loads)"; python scratch/prof_c2.py 100 300 1000 2000 5000 --reps 3
-for plan in "2,28,640" "2,24,640" "2,20,640"; do
-  echo "== PLAN=$plan"; PYOPAL_CUDA_PLAN=$plan python scratch/prof_c2.py 1000 2000 --reps 3
+timeout 600 python -m pytest tests/test_gpu_score.py -x -q -m gpu -k "giant or batch" > gpurun_out/test_gpu_score.log 2>&1; echo "score rc=$?"; tail -2 gpurun_out/test_gpu_score.log
+timeout 600 python -m pytest tests/test_gpu_fuzz.py -x -q -m gpu -k "dual" > gpurun_out/test_gpu_fuzz.log 2>&1; echo "fuzz rc=$?"; tail -2 gpurun_out/test_gpu_fuzz.log
+PYOPAL_CUDA_DEBUG=1 timeout 900 python bench.py --workload config5 --steps 1 --warmup 1 --no-cpu-baseline --blocks-per-gpu 2 > gpurun_out/c5_dual.json 2> gpurun_out/c5_dual.err; echo "c5 dual rc=$?"
+grep "dual" gpurun_out/c5_dual.err | sort | uniq -c | sort -rn | head -40
+for plan in "3,40" "3,28" "2,28" "3,36" "4,20"; do
+PYOPAL_CUDA_PLAN=$plan timeout 900 python bench.py --workload config5 --steps 1 --warmup 1 --no-cpu-baseline --blocks-per-gpu 2 > gpurun_out/c5_dual_$plan.json 2> /dev/null
 done
-echo "== 1/8 default"; python scratch/prof_c2.py 100 300 1000 2000 5000 --reps 3 --shard 8
-for plan in "2,28,512" "3,16,512" "2,16,512" "3,28,512"; do
-  echo "== 1/8 PLAN=$plan"; PYOPAL_CUDA_PLAN=$plan python scratch/prof_c2.py 100 300 --reps 3 --shard 8
-done
-echo "== c1 default"; python scratch/prof_c2.py 300 --reps 3 --config1
-echo "== c1 end"; python scratch/prof_c2.py 300 --reps 3 --config1 --end
-} > gpurun_out/sweep3.log 2>&1
-cat gpurun_out/sweep3.log
+python - <<'PY'
+import json,glob
+for f in sorted(glob.glob("gpurun_out/c5_dual*.json")):
+    try:
+        d=json.loads(open(f).read().strip().splitlines()[-1]); print(f, d["value"], d["ms_per_step"], d["top_hits_checksum"])
+    except Exception as e: print(f,"ERR",e)
+PY

@@ -189,6 +189,42 @@ def test_config5_block_batch(cuda, oracle):
         assert np.array_equal(single, rows[qi])
 
 
+def test_dual_query_batch_equals_single_searches(cuda, oracle, monkeypatch):
+    # config 5's shape again, the batch searched two queries at a time by dual_kernel (forced: this 120k-protein
+    # stand-in is small enough to have "giants"): every score row equals the single-query search's, a subsample the
+    # oracle's; through the one-GPU handle and through the multi-GPU handle's batch path (world 1)
+    block = 60_000
+    sr, so, sl, _ = synthetic.config5_shard(0, 2, 4, block)
+    M = pyopal.Aligner("BLOSUM62", GO, GE)._int_matrix
+    queries = [q.tobytes() for q in synthetic.config5_queries(7)]
+    monkeypatch.setenv("PYOPAL_CUDA_NO_DUAL", "1")
+    store = cuda.DeviceStore(sr, so, np.ascontiguousarray(sl), 24, device=0)
+    want = np.frombuffer(store.search_batch(queries, GO, GE, M, 3), dtype=np.int32).reshape(len(queries), -1).copy()
+    store.close()
+    monkeypatch.delenv("PYOPAL_CUDA_NO_DUAL")
+    monkeypatch.setenv("PYOPAL_CUDA_DUAL", "1")
+    store = cuda.DeviceStore(sr, so, np.ascontiguousarray(sl), 24, device=0)
+    got = np.frombuffer(store.search_batch(queries, GO, GE, M, 3), dtype=np.int32).reshape(len(queries), -1)
+    assert np.array_equal(got, want)
+    vals, idx = store.search_batch_topk(queries, GO, GE, M, 3, 50)
+    for qi in range(len(queries)):
+        order = np.lexsort((np.arange(want.shape[1]), -want[qi].astype(np.int64)))[:50]
+        assert list(idx[qi * 50: qi * 50 + 50]) == order.tolist()
+        assert list(vals[qi * 50: qi * 50 + 50]) == want[qi][order].tolist()
+    store.close()
+    sdb = sharding.ShardedDatabase.from_blocks((sr, so, np.ascontiguousarray(sl)), block, 2, device=0)
+    flat = np.frombuffer(sdb.search_batch(queries, GO, GE, M, 3), dtype=np.int32).reshape(len(queries), -1)
+    assert np.array_equal(flat, want)
+    sdb.close()
+    rng = np.random.Generator(np.random.PCG64(56))
+    pick = np.unique(np.concatenate([rng.choice(len(sl), 1200, replace=False), np.argsort(sl)[-10:]]))
+    sub = synthetic.pack_subset((sr, so, sl), pick)
+    for qi in (0, 3, 6):
+        ref = oracle.search_flat(queries[qi], sub[0].tobytes() + b"\0", array.array("q", sub[1].tolist()),
+                                 array.array("i", sub[2].tolist()), M, 24, GO, GE, "sw", "score", 8)["score"]
+        assert want[qi][pick].tolist() == list(ref)
+
+
 def test_sharded_database_api_single_rank(cuda, oracle):
     # sharding.ShardedDatabase at world size 1 (no communicator): both ways of sharding, scores in database order,
     # the batched call and the batched device top-k; N > 1 is covered by test_multi_gpu.py (NCCL, when the box has

@@ -241,3 +241,44 @@ def test_fuzz_forced_stream(cuda, oracle, monkeypatch, seed):
         got = list(aligner.align_scores(alphabet.decode(query), db, algorithm=algo))
         bad = [i for i, (a, b) in enumerate(zip(got, want)) if a != b]
         assert not bad, (seed, algo, go, ge, os.environ["PYOPAL_CUDA_PLAN"], [(i, got[i], want[i], len(seqs[i])) for i in bad[:4]])
+
+
+@pytest.mark.parametrize("seed", range(max(24, N_SCORE // 3)))
+def test_fuzz_dual_query_batches(cuda, oracle, monkeypatch, seed):
+    # batched Smith-Waterman searches: queries are paired by length and each pair goes down as ONE pass of
+    # dual_kernel (csrc/dual.cuh: two queries in the halves of a register against one target, pre-packed profile),
+    # forced here on small databases (PYOPAL_CUDA_DUAL=1; by default only databases without giants take it) under
+    # random tiles -- queries of very different length in one pair, several passes, odd batch sizes (one query left
+    # single), matrices with negative folded scores, top-k of every query
+    rng = np.random.Generator(np.random.PCG64(11000 + seed))
+    letters, rows, go, ge, query, seqs = _case(4000 + seed)
+    if ge > go:
+        ge = go   # the 16-bit rung needs ext <= open; the single-query path covers the other case
+    monkeypatch.setenv("PYOPAL_CUDA_DUAL", "1")
+    if rng.random() < 0.7:
+        monkeypatch.setenv("PYOPAL_CUDA_PLAN", f"{int(rng.integers(2, 6))},{4 * int(rng.integers(1, 11))}")
+    alphabet = pyopal.Alphabet(letters)
+    aligner = pyopal.Aligner(pyopal.ScoringMatrix(rows, letters), go, ge)
+    db = make_db(seqs, alphabet)
+    flat = [int(v) for row in rows for v in row]
+    A = len(letters)
+    nq = int(rng.integers(2, 6))
+    queries = [query]
+    for _ in range(nq - 1):
+        lq = int(rng.choice([1, 7, 60, 300, 700, 1400]))
+        q = rng.integers(0, A, size=lq, dtype=np.uint8)
+        if rng.random() < 0.5 and len(seqs):   # a homolog of some target: real scores, possibly an overflow
+            src = np.frombuffer(seqs[int(rng.integers(0, len(seqs)))], dtype=np.uint8)
+            if len(src):
+                q = np.resize(src, lq).copy()
+        queries.append(q.tobytes())
+    got = aligner.align_batch([alphabet.decode(q) for q in queries], db)
+    want = [oracle.search(q, seqs, flat, A, go, ge, "sw", "score", threads=8)["score"] for q in queries]
+    for qi, (g, w) in enumerate(zip(got, want)):
+        bad = [i for i, (x, y) in enumerate(zip(g, w)) if x != y]
+        assert not bad, (seed, qi, len(queries[qi]), go, ge, os.environ.get("PYOPAL_CUDA_PLAN"), [(i, g[i], w[i], len(seqs[i])) for i in bad[:4]])
+    k = int(rng.integers(1, len(seqs) + 1))
+    tops = aligner.align_batch_topk([alphabet.decode(q) for q in queries], db, k)
+    for hits, w in zip(tops, want):
+        order = sorted(range(len(w)), key=lambda i: (-w[i], i))[:k]
+        assert [(h.target_index, h.score) for h in hits] == [(i, w[i]) for i in order]

@@ -117,6 +117,39 @@ def test_giant_teams(cuda, oracle, algo, lq):
     assert db._device_store().stats()["targets32"] >= 4
 
 
+@pytest.mark.parametrize("lq", [50, 700, 2500, 4500])
+def test_giant_teams_one_target_per_team(cuda, oracle, monkeypatch, lq):
+    # Smith-Waterman giants are walked two to a team at 16 bit by default (the two targets of a pair);
+    # PYOPAL_CUDA_NO_GIANT16 keeps the 32-bit, one-target-per-team kernel that NW / HW / OV always use
+    monkeypatch.setenv("PYOPAL_CUDA_NO_GIANT16", "1")
+    seqs = synthetic.as_sequences(synthetic.database(71, 400, 5.0, 0.6, 1, 1500, giants=(5003, 4001, 3002, 2999)))
+    aligner = pyopal.Aligner("BLOSUM62", 11, 1)
+    db = check(oracle, aligner, rand_query(70 + lq, lq), seqs, "sw")
+    assert db._device_store().stats()["targets32"] >= 4
+
+
+def test_packed_giants_overflow_is_rescored(cuda, oracle):
+    # a pair of long targets one of which is a near copy of the query under a matrix with a 100-point match: its
+    # packed 16-bit score overflows inside giant.cu, both targets of the pair go to the 32-bit rescue list, scores
+    # stay exact
+    rng = np.random.Generator(np.random.PCG64(4321))
+    base = pyopal.ScoringMatrix.from_name("BLOSUM62")
+    rows = base.matrix
+    w = base.alphabet.index("W")
+    rows[w][w] = 100
+    aligner = pyopal.Aligner(pyopal.ScoringMatrix(rows, base.alphabet), 11, 1)
+    seqs = synthetic.as_sequences(synthetic.database(72, 300, 5.0, 0.6, 1, 1200))
+    twin = np.full(3000, w, dtype=np.uint8)
+    twin[::97] = 0
+    seqs += [twin.tobytes(), synthetic.random_residues(rng, 2990).tobytes()]
+    query = bytes([w]) * 900
+    db = check(oracle, aligner, query, seqs, "sw")
+    got = list(aligner.align_scores(query_str(aligner, query), db))
+    assert max(got) > 65535
+    st = db._device_store().stats()
+    assert st["targets32"] >= 2 and st["escalated"] >= 1, st
+
+
 @pytest.mark.parametrize("algo", ALGOS)
 @pytest.mark.parametrize("shape", ["1,16,0", "2,16,0", "3,32,0", "4,32,0", "8,16,0", "4,32"])
 @pytest.mark.parametrize("lq", [1, 37, 300, 1100])
