@@ -1259,8 +1259,9 @@ int pyopal::enqueue_dual_search(pyopal_cuda_db* db, Workspace* ws, const unsigne
     }
     const size_t n_ovf = (size_t)ntargets;
     if (ws->ovf.reserve(n_ovf) || ws->ovf2.reserve(n_ovf)) return PYOPAL_CUDA_ERR_NOMEM;
-    if (ws->bnd32H.reserve((size_t)db->ncols * 2 + 16) || ws->bnd32F.reserve((size_t)db->ncols * 2 + 16))
-        return PYOPAL_CUDA_ERR_NOMEM;
+    if (npass > 1 || tail_a.npass > 1 || tail_b.npass > 1)   // pass boundaries, one entry per target and column
+        if (ws->bnd32H.reserve((size_t)db->ncols * 2 + 16) || ws->bnd32F.reserve((size_t)db->ncols * 2 + 16))
+            return PYOPAL_CUDA_ERR_NOMEM;
     CU(cudaMemcpyAsync(dp, hp, par_bytes, cudaMemcpyHostToDevice, st));
     CU(cudaEventRecord(ws->par_done[slot], st));
     ws->par_used[slot] = true;
