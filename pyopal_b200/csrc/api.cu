@@ -121,6 +121,14 @@ int pyopal_cuda_last_stats(const pyopal_cuda_db* db, int64_t* stats, int n) {
     return 0;
 }
 
+int pyopal_host_batch_units(const int32_t* q_lengths, int nq, int pair_queries, int32_t* units) {
+    if (nq < 0 || (nq > 0 && (!q_lengths || !units))) return -1;
+    std::vector<std::pair<int, int>> u;
+    pyopal::batch_units(q_lengths, nq, pair_queries != 0, u);
+    for (size_t i = 0; i < u.size(); i++) { units[2 * i] = u[i].first; units[2 * i + 1] = u[i].second; }
+    return (int)u.size();
+}
+
 void pyopal_host_offsets_from_lengths(const int32_t* lengths, int64_t n, int64_t* offsets, int64_t* total) {
     int64_t t = 0;
     for (int64_t i = 0; i < n; i++) {
@@ -1430,10 +1438,15 @@ extern "C" int opalSearchDatabaseCharSW(char query[], int queryLength, char** db
 // queries goes down as ONE dual search when the database allows it (enqueue_dual_search), else one after the other.
 void pyopal::plan_batch_units(const pyopal_cuda_db* db, const int32_t* q_lengths, int nq, int mode,
                               std::vector<std::pair<int, int>>& units) {
+    batch_units(q_lengths, nq, mode == MODE_SW && !db->tune.no_dual, units);
+}
+
+// Pure host code (every rank of a multi-GPU handle must derive the same units: the collectives have to match).
+void pyopal::batch_units(const int32_t* q_lengths, int nq, bool pair_queries, std::vector<std::pair<int, int>>& units) {
     units.clear();
     std::vector<int> order((size_t)nq);
     std::iota(order.begin(), order.end(), 0);
-    const bool pairing = mode == MODE_SW && !db->tune.no_dual && nq > 1;
+    const bool pairing = pair_queries && nq > 1;
     if (pairing) std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return q_lengths[a] > q_lengths[b]; });
     for (int k = 0; k < nq; k += pairing ? 2 : 1) {
         const int second = (pairing && k + 1 < nq && q_lengths[order[(size_t)k + 1]] > 0) ? order[(size_t)k + 1] : -1;

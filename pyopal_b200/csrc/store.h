@@ -244,6 +244,7 @@ int enqueue_dual_search(pyopal_cuda_db* db, Workspace* ws, const unsigned char* 
 
 // api.cu: the order and pairing in which the queries of a batch are searched: (first, second or -1) per unit
 void plan_batch_units(const pyopal_cuda_db* db, const int32_t* q_lengths, int nq, int mode, std::vector<std::pair<int, int>>& units);
+void batch_units(const int32_t* q_lengths, int nq, bool pair_queries, std::vector<std::pair<int, int>>& units);
 
 int check_search_args(pyopal_cuda_db* db, const unsigned char* query, int Lq, int go, int ge, const int* M, int A,
                       int mode, int64_t* start, int64_t* end);

@@ -221,6 +221,32 @@ def test_library_exports_every_declared_symbol():
         assert getattr(lib, name) is not None
 
 
+def test_batch_units_pair_queries_by_length():
+    # the order / pairing in which a batch is searched (csrc/api.cu batch_units): host code every rank repeats, so
+    # it must be a pure function of the query lengths
+    import array
+    import ctypes
+
+    lib = cuda.load_library()
+    lib.pyopal_host_batch_units.restype = ctypes.c_int
+    lib.pyopal_host_batch_units.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+
+    def units(lengths, pair):
+        ql = array.array("i", lengths)
+        out = array.array("i", [-7] * (2 * max(len(ql), 1)))
+        n = lib.pyopal_host_batch_units(ql.buffer_info()[0] if len(ql) else None, len(ql), int(pair), out.buffer_info()[0])
+        return [(out[2 * i], out[2 * i + 1]) for i in range(n)]
+
+    assert units([], True) == []
+    assert units([300], True) == [(0, -1)]
+    assert units([100, 300, 1000, 2000, 5000], False) == [(i, -1) for i in range(5)]      # caller's order, one by one
+    assert units([100, 300, 1000, 2000, 5000], True) == [(4, 3), (2, 1), (0, -1)]        # neighbours in length
+    assert units([50, 0, 70, 0], True) == [(2, 0), (1, -1), (3, -1)]                       # empty queries stay single
+    got = units([5, 9, 9, 1, 7, 3, 8], True)
+    assert sorted(q for u in got for q in u if q >= 0) == list(range(7))                  # every query exactly once
+    assert all(b == -1 or (a != b) for a, b in got)
+
+
 def test_constants_match_header():
     header = open(os.path.join(ROOT, "include", "pyopal_cuda.h")).read()
     for name, value in re.findall(r"#define\s+((?:OPAL|PYOPAL_CUDA)_\w+)\s+(\d+)", header):
