@@ -177,8 +177,9 @@ int pyopal_cuda_topk_device(pyopal_cuda_db* db, const int32_t* d_scores, int64_t
 int pyopal_cuda_last_stats(const pyopal_cuda_db* db, int64_t* stats, int n);
 
 /* Host helper for packed databases: offsets[i] = sum of lengths[0..i), *total = sum of all (either may be NULL). */
-/* Order in which a batch of queries is searched: sorted by length (descending), neighbours paired when
- * pair_queries != 0 (Smith-Waterman batches: a pair goes down as one pass of the two-queries-per-register kernel).
+/* Order in which a batch of queries is searched: the caller's, or with pair_queries != 0 (Smith-Waterman batches)
+ * sorted by length (descending) with neighbours within 0.7 of each other paired: a pair goes down as one pass of the
+ * two-queries-per-register kernel, which costs the longer query twice over.
  * units[2 * u], units[2 * u + 1] = the query indices of unit u (second = -1: searched alone); returns the number of
  * units (<= nq).  Pure host code; every rank of a multi-GPU handle derives the same units. */
 int pyopal_host_batch_units(const int32_t* q_lengths, int nq, int pair_queries, int32_t* units);

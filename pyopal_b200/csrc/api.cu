@@ -231,6 +231,22 @@ Workspace* pyopal_cuda_db::acquire() {
     }
 }
 
+Workspace* pyopal_cuda_db::try_acquire() {
+    std::unique_lock<std::mutex> lock(mu);
+    if (!free_ws.empty()) {
+        Workspace* ws = free_ws.back();
+        free_ws.pop_back();
+        return ws;
+    }
+    if ((int)pool.size() >= max_ws) return nullptr;
+    std::unique_ptr<Workspace> ws(new (std::nothrow) Workspace());
+    if (!ws) return nullptr;
+    DeviceGuard guard(device);
+    if (ws->init(device)) { ws->destroy(); return nullptr; }
+    pool.push_back(std::move(ws));
+    return pool.back().get();
+}
+
 void pyopal_cuda_db::release(Workspace* ws) {
     {
         std::lock_guard<std::mutex> lock(mu);
@@ -743,10 +759,16 @@ constexpr size_t PAR_LISTS = PAR_MATRIX + 4096;   // work lists, fix-ups, query
 //            device by bulk/mid.
 int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const unsigned char* query, int Lq, int go,
                                     int ge, const int* M, int A, int mode, int64_t start, int64_t end,
-                                    int32_t* d_out, cudaStream_t st, EndPlan* endp) {
-    for (int i = 0; i < 12; i++) ws->stats[i] = 0;
-    ws->kev_valid[0] = ws->kev_valid[1] = ws->kev_valid[2] = false;
-    ws->d_ovf_count = nullptr;
+                                    int32_t* d_out, cudaStream_t st, EndPlan* endp, SearchOpts* opts) {
+    // opts (enqueue_dual_search): plan with the length of the longer query of a pair, report the plan without
+    // enqueuing anything, or enqueue everything BUT the 16-bit bulk
+    const bool plan_only = opts && opts->plan_only, no_bulk = opts && opts->no_bulk;
+    const int LqP = (opts && opts->plan_Lq > 0) ? opts->plan_Lq : Lq;
+    if (!plan_only) {
+        for (int i = 0; i < 12; i++) ws->stats[i] = 0;
+        ws->kev_valid[0] = ws->kev_valid[1] = ws->kev_valid[2] = false;
+        ws->d_ovf_count = nullptr;
+    }
     const int64_t nout = end - start;
     if (nout <= 0) return 0;
     const bool local = (mode == MODE_SW);
@@ -761,12 +783,14 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
     };
 
     // a workspace is reused across streams: wait for its previous search, mark the end of this one
-    if (ws->used) CU(cudaStreamWaitEvent(st, ws->ev_free, 0));
-    ws->used = true;
+    if (!plan_only) {
+        if (ws->used) CU(cudaStreamWaitEvent(st, ws->ev_free, 0));
+        ws->used = true;
+    }
     struct Mark {
         Workspace* w; cudaStream_t s;
-        ~Mark() { cudaEventRecord(w->ev_free, s); }
-    } mark{ws, st};
+        ~Mark() { if (w) cudaEventRecord(w->ev_free, s); }
+    } mark{plan_only ? nullptr : ws, st};
 
     // host-side fix-ups: zero-length targets, or everything when the query is empty (score mode; the end-mode
     // caller fills these from closed forms on the host)
@@ -810,9 +834,9 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
         // giant kernels do not carry it, so everything stays on search_kernel then
         bfix = (mode == MODE_NW && ge > go);
         const bool fits8 = make_rung(M, A, go, ge, mode, 0).fits8;
-        if (fits8 && Lq <= 8192 && !bfix && !tune.no_giant && !endm) {
-            gK = (Lq <= 2048) ? 4 : (Lq <= 4096) ? 8 : 16;            // rows per lane
-            gwarps = ((Lq + gK - 1) / gK + 31) / 32;                  // warps per team (<= 16): the whole query in one pass
+        if (fits8 && LqP <= 8192 && !bfix && !tune.no_giant && !endm) {
+            gK = (LqP <= 2048) ? 4 : (LqP <= 4096) ? 8 : 16;          // rows per lane
+            gwarps = ((LqP + gK - 1) / gK + 31) / 32;                 // warps per team (<= 16): the whole query in one pass
             gteams = (gwarps == 1) ? 16 : std::min(15, 16 / gwarps);  // teams per 512-thread CTA (15 named barriers)
             gpitch = (gwarps * 32 * (gK + 4) + 15) / 16 * 16;         // gK = 4, 8, 16 words-even: chunks of gK + 4 bytes
             gsmem = giant_smem_bytes(A, gpitch, gwarps, gteams);
@@ -828,16 +852,16 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
         if (fits8 && ge <= go && !tune.no_tgiant && !tune.no_giant && !endm) {
             if (tune.has_tgiant) { tNW = tune.tg_warps; tK = tune.tg_K; tsplit_override = tune.tg_split; }
             tpitch = tNW * 32 * (tK + 4);
-            tsmem = tgiant_smem_bytes(A, tpitch, tNW, Lq);
+            tsmem = tgiant_smem_bytes(A, tpitch, tNW, LqP);
             // one warp per scheduler issues a 32-row step in ~820 clocks: faster than giant.cu up to ~1500 rows
-            use_t = tsmem + 1024 <= (size_t)smem_optin && (Lq <= 1536 || tune.has_tgiant);
+            use_t = tsmem + 1024 <= (size_t)smem_optin && (LqP <= 1536 || tune.has_tgiant);
             if (use_t && !old_giants_ok) {
                 gpol.ok = true;
                 gpol.cap = (int64_t)db->sm_count * 8;
                 // a revolution of Lq + 32 * warps - 1 steps covers 32 * warps * K target columns; a step costs
                 // about 25 clocks per row held by a lane (measured); 56 cost units per SM clock
                 const double step_clk = 25.0 * tK + 20.0;
-                gpol.col_cost = 56.0 * step_clk * (double)(Lq + tNW * 32 - 1) / (double)(tNW * 32 * tK);
+                gpol.col_cost = 56.0 * step_clk * (double)(LqP + tNW * 32 - 1) / (double)(tNW * 32 * tK);
             }
         }
         if (endm && fits8 && !tune.no_giant) {
@@ -850,7 +874,7 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
         stream = !endm && !tune.no_stream && start == 0 && end >= db->n && fits8 && ge <= go && !bfix &&
                  db->ncols < ((int64_t)1 << 31);
         const bool allow_mid = tune.mid > 0 && !tune.no_tail && !tune.has_plan;  // opt-in (PYOPAL_CUDA_MID): see DESIGN.md 4.1
-        bulk = make_plan(Lq, A, db, SMEM_LIMIT, &gpol, allow_mid, &kmid);
+        bulk = make_plan(LqP, A, db, SMEM_LIMIT, &gpol, allow_mid, &kmid);
         // ... and only where it pays: wide groups (the fill steps it removes are (G - 1) per pair and pass) of deep
         // tiles (its longer step prologue is amortised over K rows).  Measured on a 1/8 shard of config 2: + 5.5 % at
         // G = 32, K = 32; - 12 % at G = 16, K = 20.  PYOPAL_CUDA_STREAM=1 forces it (tests).
@@ -946,8 +970,18 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
         wl32.insert(wl32.end(), wlg.begin(), wlg.end());  // one list: [static 32-bit | giants | transposed giants]
         wl32.insert(wl32.end(), wlt.begin(), wlt.end());
     }
-    const int64_t n16 = ntail + nbulk;
-    if (same_plan) { nbulk = n16; ntail = 0; }
+    const int64_t n16_all = ntail + nbulk;
+    if (same_plan) { nbulk = n16_all; ntail = 0; }
+    if (opts) {
+        opts->bulk_G = bulk.G; opts->bulk_logG = bulk.logG; opts->bulk_K = bulk.K;
+        opts->first_bulk = same_plan ? n32p : tail_end;
+        // "clean": everything below the giants is one 16-bit bulk launch over a contiguous range of pairs
+        opts->clean = device_dp && whole && local && !endm && rung.ok16 && !wide && !bfix && bulk.psmem && ntail == 0 &&
+                      n32 == 0 && (same_plan ? n32p : tail_end) == kg;
+    }
+    if (plan_only) return 0;
+    if (no_bulk) { nbulk = 0; ntail = 0; }
+    const int64_t n16 = no_bulk ? 0 : n16_all;
 
     // ---- the parameter block: counters, matrix, lists, fix-ups, query: one pinned copy, one H2D ------------
     const size_t off_wl32 = PAR_LISTS;
@@ -987,7 +1021,7 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
     const int32_t* d_wl16 = reinterpret_cast<const int32_t*>(dp + off_wl16);
 
     auto apply_fixes = [&]() -> int {
-        if (fixes.empty()) return 0;
+        if (fixes.empty() || no_bulk) return 0;   // no_bulk: the dual search writes them, once per query
         const int nfix = (int)(fixes.size() / 2);
         scatter_fixes_kernel<<<(nfix + 255) / 256, 256, 0, st>>>(reinterpret_cast<const int32_t*>(dp + off_fix), nfix, d_out);
         CU(cudaGetLastError());
@@ -1000,7 +1034,7 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
     if (same_plan) d_wl_bulk = d_wl_tail;
     const int64_t n16x = n16 + (packed_giants ? ng : 0);   // pairs scored at 16 bit: bulk, mid and packed giants
     if (local && n16x && ws->ovf.reserve((size_t)(2 * n16x))) return PYOPAL_CUDA_ERR_NOMEM;
-    if (bulk.npass > 1 || tail.npass > 1) {
+    if ((bulk.npass > 1 && !no_bulk) || tail.npass > 1) {
         if (ws->bndH.reserve((size_t)db->ncols + 16) || ws->bndF.reserve((size_t)db->ncols + 16)) return PYOPAL_CUDA_ERR_NOMEM;
         if (!endm && (n32 > 0 || local))
             if (ws->bnd32H.reserve((size_t)db->ncols * 2 + 16) || ws->bnd32F.reserve((size_t)db->ncols * 2 + 16))
@@ -1181,12 +1215,14 @@ int pyopal::enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const uns
     return apply_fixes();
 }
 
-// Two Smith-Waterman score searches of the WHOLE database in one pass of dual_kernel (dual.cuh): the two queries
-// share every target column, so their folded scores sit pre-packed in one profile word and a cell pair costs 4.5
-// ALU-pipe instructions instead of 5.5.  Restricted to the case a batch over a large database is in: no target long
-// enough to need the giant kernels under the tile chosen (the whole search is long compared with the longest
-// pair), both queries short enough for the 32-bit profile to fit shared memory.  Returns DUAL_NOT_ELIGIBLE when the
-// pair of queries has to be searched one by one instead (nothing has been enqueued then).
+// Two Smith-Waterman score searches of the WHOLE database with ONE pass of dual_kernel (dual.cuh) over everything
+// below the giants: the two queries share every target column, so their folded scores sit pre-packed in one profile
+// word and a cell pair costs 4.5 ALU-pipe instructions instead of 5.5.  The launch plan is the single-query one for
+// the LONGER query (same tile, same giants); each query's giants run through the single-query path with the bulk
+// switched off, on two more workspaces so that they overlap each other and the dual launch.  Returns
+// DUAL_NOT_ELIGIBLE when the pair has to be searched one query after the other (nothing has been enqueued then):
+// profile words that do not fit shared memory, a plan with more than giants + one 16-bit bulk launch, no spare
+// workspace.
 int pyopal::enqueue_dual_search(pyopal_cuda_db* db, Workspace* ws, const unsigned char* qa, int La, const unsigned char* qb,
                                 int Lb, int go, int ge, const int* M, int A, int32_t* d_out_a, int32_t* d_out_b,
                                 cudaStream_t st) {
@@ -1195,14 +1231,17 @@ int pyopal::enqueue_dual_search(pyopal_cuda_db* db, Workspace* ws, const unsigne
     if (tune.has_tgiant || tune.force_stream) return DUAL_NOT_ELIGIBLE;   // a test asked for another kernel
     const int Lp = std::max(La, Lb);
     const size_t SMEM_LIMIT = (size_t)200 * 1024;
-    // the tile, planned without giants: what remains above L_even stretches the cost, and more than a little of it
-    // means this database is too small for the restricted launch plan
-    Plan pl = make_plan(Lp, A, db, SMEM_LIMIT, nullptr, false, nullptr);
-    {
-        const double solo = tune.solo > 0 ? tune.solo : (pl.G == 4 ? 448.0 : 560.0);
-        const double l_even = (double)db->ncols * pl.G / (solo * db->sm_count);
-        if ((double)db->h_pair_len[0] > 0.6 * l_even && !tune.force_dual) return DUAL_NOT_ELIGIBLE;
-    }
+    // the single-query plan of the longer query: tile, giants
+    SearchOpts po;
+    po.plan_only = true; po.plan_Lq = Lp;
+    if (enqueue_score_search_ex(db, ws, qa, La, go, ge, M, A, MODE_SW, 0, db->n, d_out_a, st, nullptr, &po) || !po.clean)
+        return DUAL_NOT_ELIGIBLE;
+    Plan pl;
+    pl.G = po.bulk_G; pl.logG = po.bulk_logG; pl.K = po.bulk_K;
+    const int64_t first = po.first_bulk;
+    if (first >= db->npairs) return DUAL_NOT_ELIGIBLE;   // nothing but giants
+    // small databases are latency-bound by their giants: two queries per pass only pays when the bulk dominates
+    if (first > 0 && !tune.force_dual && db->ncols < (int64_t)4 << 20) return DUAL_NOT_ELIGIBLE;
     const int T = pl.G * pl.K;
     const int npass = (Lp + T - 1) / T;
     Rung rung = make_rung(M, A, go, ge, MODE_SW, npass * T);
@@ -1230,6 +1269,17 @@ int pyopal::enqueue_dual_search(pyopal_cuda_db* db, Workspace* ws, const unsigne
             return DUAL_NOT_ELIGIBLE;   // the single-query path reports OPAL_ERR_OVERFLOW
     }
 
+    // the giants of either query: two more workspaces (never waited for: a pool that is busy means "not eligible")
+    struct TryLease {
+        pyopal_cuda_db* d; Workspace* w;
+        ~TryLease() { if (w) d->release(w); }
+    } ga{db, nullptr}, gb{db, nullptr};
+    if (first > 0) {
+        ga.w = db->try_acquire();
+        gb.w = db->try_acquire();
+        if (!ga.w || !gb.w) return DUAL_NOT_ELIGIBLE;
+    }
+
     for (int i = 0; i < 12; i++) ws->stats[i] = 0;
     ws->kev_valid[0] = ws->kev_valid[1] = ws->kev_valid[2] = false;
     ws->d_ovf_count = nullptr;
@@ -1239,6 +1289,23 @@ int pyopal::enqueue_dual_search(pyopal_cuda_db* db, Workspace* ws, const unsigne
         Workspace* w; cudaStream_t s;
         ~Mark() { cudaEventRecord(w->ev_free, s); }
     } mark{ws, st};
+
+    int64_t giant_launches = 0;
+    if (first > 0) {
+        // fork: the giants start where `st` stands (the result rows are free), on their own streams
+        CU(cudaEventRecord(ws->ev_aux0, st));
+        SearchOpts ob;
+        ob.no_bulk = true; ob.plan_Lq = Lp;
+        struct Half { Workspace* w; const unsigned char* q; int L; int32_t* out; };
+        const Half halves[2] = {{ga.w, qa, La, d_out_a}, {gb.w, qb, Lb, d_out_b}};
+        for (const Half& h : halves) {
+            CU(cudaStreamWaitEvent(h.w->stream, ws->ev_aux0, 0));
+            int rc = enqueue_score_search_ex(db, h.w, h.q, h.L, go, ge, M, A, MODE_SW, 0, db->n, h.out, h.w->stream, nullptr, &ob);
+            if (rc) return rc;
+            giant_launches += h.w->stats[0];
+            CU(cudaEventRecord(h.w->ev_aux1, h.w->stream));
+        }
+    }
 
     // zero-length targets score 0 against either query
     std::vector<int32_t> fixes;
@@ -1255,7 +1322,7 @@ int pyopal::enqueue_dual_search(pyopal_cuda_db* db, Workspace* ws, const unsigne
     if (ws->h_par[slot].reserve(par_bytes) || ws->d_par.reserve(par_bytes)) return PYOPAL_CUDA_ERR_NOMEM;
     unsigned char* hp = ws->h_par[slot].p;
     unsigned char* dp = ws->d_par.p;
-    const int64_t ntargets = 2 * db->npairs;
+    const int64_t ntargets = 2 * (db->npairs - first);
     {
         int32_t* counts = reinterpret_cast<int32_t*>(hp + PAR_COUNTS);
         memset(counts, 0, 64);
@@ -1291,7 +1358,7 @@ int pyopal::enqueue_dual_search(pyopal_cuda_db* db, Workspace* ws, const unsigne
         Q.query2 = dp + off_qb; Q.Lq2 = Lb; Q.padtop2 = npass * T - Lb;
         Q.G = pl.G; Q.logG = pl.logG; Q.npass = npass; Q.pitch = pitch; Q.krows = pl.K; Q.kstride = kstride;
         Q.neg = rung.neg16; Q.bias = rung.bias16;
-        Q.first_pair = 0;
+        Q.first_pair = (int)first;
         Q.nwork = d_counts + 0; Q.counter = d_counts + 4;
         Q.out = d_out_a; Q.out2 = d_out_b;
         Q.ovf_list = ws->ovf.p; Q.ovf_count = d_counts + 2;
@@ -1299,8 +1366,8 @@ int pyopal::enqueue_dual_search(pyopal_cuda_db* db, Workspace* ws, const unsigne
         Q.bndH = ws->bnd32H.p; Q.bndF = ws->bnd32F.p;
         const int gpw = 32 >> pl.logG;
         if (tune.debug)
-            fprintf(stderr, "[pyopal_cuda] Lq=%d+%d score (dual) bulk: G=%d K=%d npass=%d targets=%lld threads=512 smem=%zu\n",
-                    La, Lb, pl.G, pl.K, npass, (long long)ntargets, smem);
+            fprintf(stderr, "[pyopal_cuda] Lq=%d+%d score (dual) bulk: G=%d K=%d npass=%d targets=%lld giant pairs=%lld threads=512 smem=%zu\n",
+                    La, Lb, pl.G, pl.K, npass, (long long)ntargets, (long long)first, smem);
         CU(cudaEventRecord(ws->kev[2], st));
         int rc = launch_search(db, ws, kd, Q, smem, 512, (ntargets + gpw - 1) / gpw, st);
         if (rc) return rc;
@@ -1330,6 +1397,11 @@ int pyopal::enqueue_dual_search(pyopal_cuda_db* db, Workspace* ws, const unsigne
             CU(cudaGetLastError());
         }
         ws->stats[0] += 2;
+    }
+    if (first > 0) {   // join: `st` is the stream the caller orders everything else after
+        CU(cudaStreamWaitEvent(st, ga.w->ev_aux1, 0));
+        CU(cudaStreamWaitEvent(st, gb.w->ev_aux1, 0));
+        ws->stats[0] += giant_launches;
     }
     ws->d_ovf_count = d_counts + 2;
     ws->stats[1] = ntargets * 2;
@@ -1442,16 +1514,28 @@ void pyopal::plan_batch_units(const pyopal_cuda_db* db, const int32_t* q_lengths
 }
 
 // Pure host code (every rank of a multi-GPU handle must derive the same units: the collectives have to match).
+// A dual pass costs 2 x max(La, Lb) x 4.5 ALU instructions per pair column (it walks the two targets of a pair one
+// after the other), two single searches (La + Lb) x 5.5: pairing pays when the shorter query is at least 0.64 of the
+// longer one, so neighbours in length are paired from 0.7 up and everything else is searched alone.
 void pyopal::batch_units(const int32_t* q_lengths, int nq, bool pair_queries, std::vector<std::pair<int, int>>& units) {
     units.clear();
     std::vector<int> order((size_t)nq);
     std::iota(order.begin(), order.end(), 0);
-    const bool pairing = pair_queries && nq > 1;
-    if (pairing) std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return q_lengths[a] > q_lengths[b]; });
-    for (int k = 0; k < nq; k += pairing ? 2 : 1) {
-        const int second = (pairing && k + 1 < nq && q_lengths[order[(size_t)k + 1]] > 0) ? order[(size_t)k + 1] : -1;
-        units.emplace_back(order[(size_t)k], second);
-        if (pairing && second < 0 && k + 1 < nq) units.emplace_back(order[(size_t)k + 1], -1);
+    if (!pair_queries || nq < 2) {
+        for (int i = 0; i < nq; i++) units.emplace_back(i, -1);
+        return;
+    }
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return q_lengths[a] > q_lengths[b]; });
+    for (int k = 0; k < nq;) {
+        const int a = order[(size_t)k];
+        const int b = k + 1 < nq ? order[(size_t)k + 1] : -1;
+        if (b >= 0 && q_lengths[b] > 0 && 10 * (int64_t)q_lengths[b] >= 7 * (int64_t)q_lengths[a]) {
+            units.emplace_back(a, b);
+            k += 2;
+        } else {
+            units.emplace_back(a, -1);
+            k += 1;
+        }
     }
 }
 

@@ -198,6 +198,7 @@ struct pyopal_cuda_db {
     pyopal::Workspace* last_ws = nullptr;
 
     pyopal::Workspace* acquire();       // nullptr + fail() on error
+    pyopal::Workspace* try_acquire();   // nullptr when none is free and the pool is full (never waits)
     void release(pyopal::Workspace* ws);
     void publish(pyopal::Workspace* ws); // make ws's statistics the handle's "last search" without releasing it
 };
@@ -229,13 +230,23 @@ struct EndPlan {
     std::function<int()> launch_spill;  // in: called once `spill` is known and BEFORE the 16-bit launches
 };
 
+// Options of enqueue_score_search_ex for its use as one half of a dual search (api.cu, enqueue_dual_search).
+struct SearchOpts {
+    int plan_Lq = 0;          // in: plan tiles and giants as if the query had this many rows (the longer query of the pair)
+    bool plan_only = false;   // in: report the plan below, enqueue nothing, touch nothing
+    bool no_bulk = false;     // in: enqueue the giants (and the rescue of their overflows) only
+    int bulk_G = 0, bulk_logG = 0, bulk_K = 0;   // out: the bulk tile
+    int64_t first_bulk = 0;   // out: first pair of the bulk launch (the pairs before it are the giants)
+    bool clean = false;       // out: giants + ONE 16-bit bulk launch over the pairs [first_bulk, npairs), nothing else
+};
+
 // api.cu: enqueue a SCORE search of [start, end) on `st` with workspace `ws`; scores land in d_out (device).
 int enqueue_score_search(pyopal_cuda_db* db, Workspace* ws, const unsigned char* query, int Lq, int go, int ge,
                          const int* M, int A, int mode, int64_t start, int64_t end, int32_t* d_out, cudaStream_t st);
 // the same with `endp` != nullptr: END mode in the 16-bit kernels (score + end cell)
 int enqueue_score_search_ex(pyopal_cuda_db* db, Workspace* ws, const unsigned char* query, int Lq, int go, int ge,
                             const int* M, int A, int mode, int64_t start, int64_t end, int32_t* d_out, cudaStream_t st,
-                            EndPlan* endp);
+                            EndPlan* endp, SearchOpts* opts = nullptr);
 
 // api.cu: two SW score searches of the whole database in one pass (dual.cuh); DUAL_NOT_ELIGIBLE = search them one by one
 constexpr int DUAL_NOT_ELIGIBLE = -1;

@@ -248,8 +248,9 @@ def test_fuzz_dual_query_batches(cuda, oracle, monkeypatch, seed):
     # batched Smith-Waterman searches: queries are paired by length and each pair goes down as ONE pass of
     # dual_kernel (csrc/dual.cuh: two queries in the halves of a register against one target, pre-packed profile),
     # forced here on small databases (PYOPAL_CUDA_DUAL=1; by default only databases without giants take it) under
-    # random tiles -- queries of very different length in one pair, several passes, odd batch sizes (one query left
-    # single), matrices with negative folded scores, top-k of every query
+    # random tiles -- queries of different length in one pair (the shorter one padded above row 0), several passes,
+    # queries left single, matrices with negative folded scores, giants of either query beside the dual launch,
+    # top-k of every query
     rng = np.random.Generator(np.random.PCG64(11000 + seed))
     letters, rows, go, ge, query, seqs = _case(4000 + seed)
     if ge > go:
@@ -265,7 +266,10 @@ def test_fuzz_dual_query_batches(cuda, oracle, monkeypatch, seed):
     nq = int(rng.integers(2, 6))
     queries = [query]
     for _ in range(nq - 1):
-        lq = int(rng.choice([1, 7, 60, 300, 700, 1400]))
+        if rng.random() < 0.7:   # within 0.7 of a query already drawn: the two are paired (csrc/api.cu batch_units)
+            lq = max(1, int(len(queries[int(rng.integers(0, len(queries)))]) * rng.uniform(0.72, 1.0)))
+        else:
+            lq = int(rng.choice([1, 7, 60, 300, 700, 1400]))
         q = rng.integers(0, A, size=lq, dtype=np.uint8)
         if rng.random() < 0.5 and len(seqs):   # a homolog of some target: real scores, possibly an overflow
             src = np.frombuffer(seqs[int(rng.integers(0, len(seqs)))], dtype=np.uint8)

@@ -240,11 +240,13 @@ def test_batch_units_pair_queries_by_length():
     assert units([], True) == []
     assert units([300], True) == [(0, -1)]
     assert units([100, 300, 1000, 2000, 5000], False) == [(i, -1) for i in range(5)]      # caller's order, one by one
-    assert units([100, 300, 1000, 2000, 5000], True) == [(4, 3), (2, 1), (0, -1)]        # neighbours in length
+    # a dual pass costs the longer query twice over: only queries within 0.7 of each other are paired
+    assert units([100, 300, 1000, 2000, 5000], True) == [(4, -1), (3, -1), (2, -1), (1, -1), (0, -1)]
+    assert units([300, 290, 1000, 800, 100], True) == [(2, 3), (0, 1), (4, -1)]
     assert units([50, 0, 70, 0], True) == [(2, 0), (1, -1), (3, -1)]                       # empty queries stay single
     got = units([5, 9, 9, 1, 7, 3, 8], True)
+    assert got == [(1, 2), (6, 4), (0, -1), (5, -1), (3, -1)]
     assert sorted(q for u in got for q in u if q >= 0) == list(range(7))                  # every query exactly once
-    assert all(b == -1 or (a != b) for a, b in got)
 
 
 def test_constants_match_header():
