@@ -5,7 +5,7 @@ Default workload (config 2 of BASELINE.json): Swiss-Prot-shaped synthetic databa
 (570k proteins, ~2.04e8 residues, 32 planted giants up to 35213 aa), BLOSUM62,
 gap open 11 / extend 1, Smith-Waterman score mode, queries of 100, 300, 1000,
 2000 and 5000 aa.  One STEP = the five queries searched against the whole
-database through ONE batched call of the C-ABI (two searches in flight per GPU;
+database through ONE batched call of the C-ABI (searches stream-ordered back to back;
 the reference's pattern for several queries is a ThreadPool over Aligner.align,
 README.md:116-144).  N > 1: the database is dealt by cumulative cell count over
 the ranks (one process per GPU), each rank scores its shard and the per-shard
@@ -476,7 +476,7 @@ def run_b200(args):
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "u16x2 (s32 rescore)", "data": "synthetic", "config": cfg,
             "run": {"parallelism": f"db dealt by cells over {world} GPU(s), ncclAllGather of the per-shard scores inside libpyopal_cuda.so",
-                    "call": "one blocking search per query" if (args.serial or end_mode) else "one batched call per step, two searches in flight per GPU",
+                    "call": "one blocking search per query" if (args.serial or end_mode) else "one batched call per step, searches stream-ordered back to back on every GPU",
                     "store_build_s": round(t_build, 3), "wall_ms_per_step": round(1e3 * wall / args.steps, 3),
                     "nccl_version": cuda.load_library().pyopal_cuda_nccl_version() if world > 1 else None},
             "clocks": clocks,

@@ -230,8 +230,8 @@ int pyopal_cuda_mdb_search(pyopal_cuda_mdb* m, const unsigned char* query, int q
                            const int* scoreMatrix, int alphabetLength, int searchType, int mode, int overflowMethod,
                            int64_t start, int64_t end, int32_t* scores, int32_t* endQ, int32_t* endT, int32_t* startQ,
                            int32_t* startT, unsigned char* ops, const int64_t* ops_offsets, int32_t* ops_len);
-/* Batched SCORE search, two queries in flight per GPU: scores = HOST nq * (end - start) int32 (row-major by query)
- * or NULL to leave the results on the devices (timing). */
+/* Batched SCORE search, stream-ordered on every GPU (Smith-Waterman queries of similar length two per pass):
+ * scores = HOST nq * (end - start) int32 (row-major by query) or NULL to leave the results on the devices (timing). */
 int pyopal_cuda_mdb_search_batch(pyopal_cuda_mdb* m, const unsigned char* queries, const int64_t* q_offsets,
                                  const int32_t* q_lengths, int nq, int gapOpen, int gapExt, const int* scoreMatrix,
                                  int alphabetLength, int mode, int64_t start, int64_t end, int32_t* scores);

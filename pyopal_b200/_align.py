@@ -63,8 +63,9 @@ def align_batch(queries, database, scoring_matrix=None, *, gap_open=3, gap_exten
     """Score several queries against the database in one device-side pipeline (additive).
 
     The reference's pattern for many queries is a ``ThreadPool`` over `Aligner.align` calls
-    (/root/reference/README.md:116-144); here the queries go down in ONE call, two searches are in flight per
-    GPU at any time and nothing waits on the host in between.  Yields, per query and in order, an ``array('i')``
+    (/root/reference/README.md:116-144); here the queries go down in ONE call, the searches are
+    stream-ordered on every GPU with nothing waiting on the host in between, and Smith-Waterman queries of similar
+    length are searched two per pass of the score kernel (csrc/dual.cuh).  Yields, per query and in order, an ``array('i')``
     of scores in database order -- or, with ``k``, the list of the ``k`` best `ScoreResult` (selected on the
     device; score descending, ties by target index).
     """
