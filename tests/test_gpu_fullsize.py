@@ -242,6 +242,12 @@ def test_sharded_database_api_single_rank(cuda, oracle):
     n = len(lengths)
     for qi, w in enumerate(want):
         assert list(flat[qi * n: (qi + 1) * n]) == list(w)
+    # the caller's own result buffer (a high-rate caller reuses one instead of allocating rows per call)
+    mine = np.full(len(queries) * n, -1, dtype=np.int32)
+    assert sdb.search_batch(queries, GO, GE, M, 3, out=mine) is mine
+    assert mine.tolist() == list(flat)
+    with pytest.raises(ValueError):
+        sdb.search_batch(queries, GO, GE, M, 3, out=np.zeros(5, dtype=np.int32))
     vals, idx = sdb.search_batch_topk(queries, GO, GE, M, 3, 10)
     for qi, w in enumerate(want):
         order = sorted(range(n), key=lambda i: (-w[i], i))[:10]
