@@ -77,6 +77,13 @@ def test_align_uses_every_gpu_and_matches_one(cuda, oracle, monkeypatch):
         assert [(h.target_index, h.score) for h in t] == [(i, r[i]) for i in order]
 
 
+def _queries():
+    # lengths 551, 851, 63, 270 plus two truncated copies (800, 500): sorted by length the batch is two pairs within
+    # 0.7 of each other and two single queries (csrc/api.cu batch_units)
+    base = [q.tobytes() for q in synthetic.config5_queries(4)]
+    return base + [base[1][:800], base[0][:500]]
+
+
 def _rank(rank, world, port, ret):
     os.environ["MASTER_PORT"] = str(port)
     os.environ["PYOPAL_CUDA_DEVICE"] = str(rank)
@@ -87,12 +94,22 @@ def _rank(rank, world, port, ret):
     M = pyopal.Aligner("BLOSUM62", GO, GE)._int_matrix
     nid = sh.exchange_nccl_id(rank)
     sdb = sh.ShardedDatabase.deal(residues, offsets, np.ascontiguousarray(lengths), 24, rank=rank, world=world, nccl_id=nid, device=rank)
-    queries = [q.tobytes() for q in synthetic.config5_queries(4)]
+    queries = _queries()
     rows = sdb.search_batch(queries, GO, GE, M, 3)
     one = sdb.search(queries[1], GO, GE, M, 0, 1)[0]  # HW, the blocking call
     vals, idx = sdb.search_batch_topk(queries, GO, GE, M, 3, 20)
-    ret[rank] = (bytes(rows), bytes(one), bytes(vals), bytes(idx))
     sdb.close()
+    # the same batch with the two-queries-per-pass kernel forced (this database is small enough to be searched one
+    # query at a time by default): both rows of a dual search travel in one all-gather
+    os.environ["PYOPAL_CUDA_DUAL"] = "1"
+    nid2 = sh.exchange_nccl_id(rank, key=f"{port}_dual")
+    sdb2 = sh.ShardedDatabase.deal(residues, offsets, np.ascontiguousarray(lengths), 24, rank=rank, world=world, nccl_id=nid2, device=rank)
+    rows2 = sdb2.search_batch(queries, GO, GE, M, 3)
+    vals2, idx2 = sdb2.search_batch_topk(queries, GO, GE, M, 3, 20)
+    sdb2.search_batch([queries[1], queries[4]], GO, GE, M, 3, to_host=False)   # one unit: a pair
+    dual_used = sdb2.stats()["profile_in_smem"] == 2
+    sdb2.close()
+    ret[rank] = (bytes(rows), bytes(one), bytes(vals), bytes(idx), bytes(rows2) == bytes(rows) and bytes(idx2) == bytes(idx), dual_used)
 
 
 def test_two_nccl_ranks_match_single_gpu(cuda, oracle):
@@ -115,18 +132,21 @@ def test_two_nccl_ranks_match_single_gpu(cuda, oracle):
         got = dict(ret)
     sharding.discard_nccl_id(key=f"{port}_{os.getpid()}")
     assert got[0] == got[1]  # every rank holds the same database-order result
+    assert got[0][4] and got[1][4]   # two queries per pass == one per pass, on both ranks
+    assert got[0][5] and got[1][5]   # ... and the dual kernel did run
+    sharding.discard_nccl_id(key=f"{port}_dual")
     db = synthetic.database(515, 30_000, 5.3, 0.7, 0, 5000, giants=(15_000,))
     residues, offsets, lengths = db
     M = pyopal.Aligner("BLOSUM62", GO, GE)._int_matrix
     store = cuda.DeviceStore(residues, offsets, np.ascontiguousarray(lengths), 24, device=0)
-    queries = [q.tobytes() for q in synthetic.config5_queries(4)]
-    rows = np.frombuffer(got[0][0], dtype=np.int32).reshape(4, -1)
+    queries = _queries()
+    rows = np.frombuffer(got[0][0], dtype=np.int32).reshape(len(queries), -1)
     for qi, q in enumerate(queries):
         assert np.array_equal(rows[qi], np.frombuffer(store.search(q, GO, GE, M, 0, 3)[0], dtype=np.int32)), qi
     assert np.array_equal(np.frombuffer(got[0][1], dtype=np.int32), np.frombuffer(store.search(queries[1], GO, GE, M, 0, 1)[0], dtype=np.int32))
-    vals = np.frombuffer(got[0][2], dtype=np.int32).reshape(4, 20)
-    idx = np.frombuffer(got[0][3], dtype=np.int32).reshape(4, 20)
-    for qi in range(4):
+    vals = np.frombuffer(got[0][2], dtype=np.int32).reshape(len(queries), 20)
+    idx = np.frombuffer(got[0][3], dtype=np.int32).reshape(len(queries), 20)
+    for qi in range(len(queries)):
         order = sorted(range(rows.shape[1]), key=lambda i: (-int(rows[qi][i]), i))[:20]
         assert idx[qi].tolist() == order and vals[qi].tolist() == [int(rows[qi][i]) for i in order]
     want = oracle.search_flat(queries[0], residues.tobytes() + b"\0", array.array("q", offsets.tolist()),
