@@ -7,10 +7,4 @@ python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; 
 timeout 1500 python -m pytest tests -x -q -m gpu > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/summary.txt
 tail -3 gpurun_out/pytest_gpu.log >> gpurun_out/summary.txt
 timeout 900 python bench.py > gpurun_out/r2_bench_n1.json 2> gpurun_out/r2_bench_n1.err; echo "bench rc=$?" >> gpurun_out/summary.txt
-timeout 900 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/r2_bench_reference_arm.json 2> gpurun_out/ref.err; echo "reference arm rc=$?" >> gpurun_out/summary.txt
 cat gpurun_out/summary.txt
-python - <<'PY'
-import json
-d=json.loads([l for l in open("gpurun_out/r2_bench_n1.json").read().strip().splitlines() if l.startswith("{")][-1])
-print(round(d["value"],1), round(d["ms_per_step"],3), "e2e", round(d["e2e"]["value"],1), "frac", round(d["roofline"]["frac"],4), d.get("verified"), d["cpu_baseline"]["value"], d["gpu_launches"])
-PY

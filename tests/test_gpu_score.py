@@ -284,7 +284,8 @@ def test_mutation_invalidates_device_store(cuda):
 
 def test_concurrent_aligners_share_a_database(cuda, oracle):
     # the reference's documented pattern (README.md:116-144): a ThreadPool of queries against ONE Database;
-    # the store's workspace is serialised inside the library, results must equal the sequential ones
+    # every call leases its own workspace (streams, parameter block, buffers) from the handle's pool, results must
+    # equal the sequential ones
     from multiprocessing.pool import ThreadPool
 
     seqs = rand_seqs(301, 900, 5.0, 0.6, 1, 1500) + [rand_query(302, 5000)]
@@ -305,6 +306,37 @@ def test_concurrent_aligners_share_a_database(cuda, oracle):
     # result objects from threads as well (pyopal.align(threads=...) maps onto the same call)
     res = list(pyopal.align(query_str(aligner, queries[2]), db, "BLOSUM62", gap_open=11, gap_extend=1, algorithm=algos[2], threads=3, ordered=True))
     assert [r.score for r in res] == want[2]
+
+
+def test_concurrent_searches_overlap(cuda, oracle):
+    # searches from several host threads on ONE handle overlap on the device (a pool of per-search workspaces, no
+    # mutex around the search: SURVEY.md 8(b) "Threading").  The workload is latency-bound on purpose - one
+    # 30 000-aa target walked by a single team of warps while the other SMs idle - so four threads must finish
+    # their 24 searches in well under the time 24 solo searches take.
+    import time
+    from multiprocessing.pool import ThreadPool
+
+    seqs = rand_seqs(331, 40, 5.0, 0.5, 1, 600) + [rand_query(332, 30_000)]
+    aligner = pyopal.Aligner("BLOSUM62", 11, 1)
+    db = make_db(seqs, aligner.alphabet)
+    queries = [rand_query(340 + i, 1000) for i in range(4)]
+    want = [oracle.search(q, seqs, aligner._int_matrix, 24, 11, 1, "sw", "score", threads=8)["score"] for q in queries]
+
+    def one(i):
+        return list(aligner.align_scores(query_str(aligner, queries[i % 4]), db))
+
+    for i in range(4):
+        assert one(i) == want[i]          # builds the store, warms the workspaces
+    with ThreadPool(4) as pool:
+        pool.map(one, range(8))           # ... of every thread
+        t0 = time.perf_counter()
+        solo = [one(i) for i in range(24)]
+        t_solo = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        both = pool.map(one, range(24))
+        t_pool = time.perf_counter() - t0
+    assert all(r == want[i % 4] for i, r in enumerate(solo)) and all(r == want[i % 4] for i, r in enumerate(both))
+    assert t_pool < 0.85 * t_solo, (t_pool, t_solo)
 
 
 def _expected_topk(scores, k):
